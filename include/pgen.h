@@ -1,0 +1,146 @@
+/* libpgen_cuda.so -- C ABI of the B200-native pointer-generator beam-search decode.
+ *
+ * This is the drop-in boundary for the hot path behind TFModel.transform
+ * (reference: src/main/java/org/apache/flink/table/ml/lib/tensorflow/TFModel.java:55-81).
+ * In the reference, TFUtils.inference (TFModel.java:76) adds a flatMap operator whose body
+ * hands each row to a Python/TensorFlow worker process (run_summarization.py:402-426).  Here
+ * the operator body calls these entry points instead (JNI / cgo / ctypes stubs are shown in
+ * INTEGRATION.md).  Plain C types only: pointers, sizes, ints.  No CPU fallback exists:
+ * every entry point that needs the GPU fails with PGEN_ERR_CUDA when there is none.
+ *
+ * Threading: a handle is single-owner -- all calls on one handle come from one thread (the
+ * Flink subtask's task thread).  Different handles are independent.
+ *
+ * Paths in the citations are relative to /root/reference/src/main/python/pointer-generator/
+ * unless they start with "src/".
+ */
+#ifndef PGEN_H_
+#define PGEN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PGEN_API __attribute__((visibility("default")))
+#else
+#define PGEN_API
+#endif
+
+#define PGEN_OK            0
+#define PGEN_ERR_ARG       1   /* bad argument / bad flag value                           */
+#define PGEN_ERR_IO        2   /* vocab / log dir / weights archive missing or malformed   */
+#define PGEN_ERR_CUDA      3   /* no device, CUDA runtime error                            */
+#define PGEN_ERR_STATE     4   /* call sequence error (e.g. download before run)           */
+#define PGEN_ERR_UNSUPPORTED 5 /* mode != decode, dims the kernels do not cover            */
+
+typedef struct pgen pgen_t;
+
+/* One output row {uuid, article, summary, reference}: the schema FlinkWriter.write_result emits
+ * (flink_writer.py:25-34; column order from src/test/java/.../TensorFlowTest.java:232-233).
+ * Byte strings, not NUL-terminated contract-wise (a trailing NUL is present for convenience). */
+typedef struct {
+  const char* uuid;      size_t uuid_len;
+  const char* article;   size_t article_len;
+  const char* summary;   size_t summary_len;
+  const char* reference; size_t reference_len;
+} pgen_row_t;
+
+typedef struct {
+  pgen_row_t* rows;
+  size_t n_rows;
+  void* owner_;          /* library-private; released by pgen_rows_free */
+} pgen_rows_t;
+
+/* Counters in place of the reference's tf.logging lines (decode.py:185, batcher.py:574-575). */
+typedef struct {
+  uint64_t rows_in, rows_out, batches, tokens_in, tokens_out;
+  uint64_t decode_steps;       /* beam-search steps launched (per batch, summed)             */
+  uint64_t article_steps;      /* sum over articles of the steps each stayed active         */
+  uint64_t early_stops;        /* articles that ended with beam_size finished hypotheses     */
+  uint64_t kernel_launches;    /* CUDA kernels launched by this handle                       */
+  double ms_host_text;         /* tokenise + id maps + detokenise                            */
+  double ms_h2d, ms_encoder, ms_decoder, ms_d2h;   /* CUDA-event times of the last batch    */
+  double ms_attention, ms_vocab;   /* summed over the steps of the last batch run with option profile=1 */
+  double prof_steps;               /* number of steps those two sums cover */
+} pgen_stats_t;
+
+/* Replaces main_on_flink/inference_on_flink/default_setup (run_summarization.py:402-426,
+ * 384-399, 295-330) and BeamSearchDecoder.__init__ (decode.py:42-86): parses the space-joined
+ * hyper-parameter string TFModel stores under its hyper-params key (TFModel.java:47; token 0 is a
+ * dummy program name, unknown flags are ignored like known_only=True), loads the vocabulary
+ * (data.py:40-75) and the weights from <log_root>/<exp_name>/train (util.py:29-41; here
+ * model.pgenw, no retry loop: a missing file is an immediate PGEN_ERR_IO), and binds the handle to
+ * CUDA device `device_ordinal` (one GPU per Flink subtask).  On failure *out is NULL and
+ * pgen_last_error(NULL) holds the message for the calling thread. */
+PGEN_API int pgen_create(const char* hyperparams, int device_ordinal, pgen_t** out);
+
+/* Replaces MLMapFunction.flatMap's write of one row into the Python input queue and
+ * FlinkInferenceBatcher.next_batch (batcher.py:565-585) + Example/Batch construction
+ * (batcher.py:36-81, 141-187).  Inputs are borrowed for the call only.  When
+ * `articles_per_batch` rows are buffered the batch is decoded. */
+PGEN_API int pgen_submit(pgen_t* h, const char* uuid, size_t uuid_len, const char* article, size_t article_len,
+                const char* reference, size_t reference_len);
+
+/* Replaces draining the Python output queue (FlinkWriter.write_result, flink_writer.py:25-34;
+ * decode_one_batch + write_for_flink, decode.py:95-129, 159-185).  Returns finished rows in
+ * submission order.  flush != 0 (or the flush deadline having passed) decodes a partial batch,
+ * so a lone row is never held waiting for the next one (the reference's known defect,
+ * doc/Flink-AI-Extended Integration Report.md:341-376). */
+PGEN_API int pgen_poll(pgen_t* h, int flush, pgen_rows_t* out);
+PGEN_API void pgen_rows_free(pgen_rows_t* rows);
+
+PGEN_API int pgen_stats(pgen_t* h, pgen_stats_t* out);
+/* Message of the last failure on `h`; with h == NULL, of the last failed pgen_create on this thread. */
+PGEN_API const char* pgen_last_error(pgen_t* h);
+/* Replaces the end of BeamSearchDecoder.decode when the stream is exhausted (decode.py:139-142). */
+PGEN_API void pgen_destroy(pgen_t* h);
+
+/* Parsed hyper-parameters (run_summarization.py:48-88 names).  Returns the value of an integer or
+ * boolean flag after the decode-mode overrides (batch_size := beam_size, :312-313), or -1. */
+PGEN_API int64_t pgen_flag_int(pgen_t* h, const char* name);
+
+/* Host text path alone, for parity tests against data.py:144-168 / batcher.py:51-56:
+ * article bytes -> enc ids (OOV -> [UNK]) and extended ids (j-th distinct OOV -> vocab_size+j). */
+PGEN_API int pgen_text_encode(pgen_t* h, const char* article, size_t article_len, int32_t* enc_ids,
+                     int32_t* ext_ids, int cap, int32_t* enc_len, int32_t* n_oov);
+/* ids -> summary string (data.py:196-219, decode.py:109-118, 167-182) for the article last passed
+ * to pgen_text_encode on this handle.  Writes at most cap bytes, returns the full length in *len. */
+PGEN_API int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out, size_t cap, size_t* len);
+
+/* Tensor-level decode = run_beam_search (beam_search.py:82-168) over run_encoder / decode_onestep
+ * (model.py:347-443) for n_articles independent articles, host buffers in and out:
+ *   enc_ids, enc_ext_ids  [n_articles, ld]  (row b valid for enc_lens[b] <= max_enc_steps entries)
+ *   out_tokens, out_logprobs [n_articles, max_dec_steps]  tokens after [START]; a finished
+ *                            hypothesis ends with [STOP]; out_lens[b] entries are valid
+ *   out_avg [n_articles]  avg_log_prob of the returned hypothesis (beam_search.py:77-79)
+ * Articles are processed in device batches of at most articles_per_batch. */
+PGEN_API int pgen_decode_ids(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
+                    const int32_t* enc_lens, const int32_t* n_oovs, int32_t* out_tokens, int32_t* out_lens,
+                    float* out_logprobs, double* out_avg);
+
+/* The same path split at the PCIe boundary, so that a harness can time the device-resident part
+ * alone: upload (H2D of ids), run (encoder + beam search, asynchronous on the handle's stream),
+ * sync, download (D2H of the best hypotheses).  n_articles <= articles_per_batch. */
+PGEN_API int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
+                      const int32_t* enc_lens, const int32_t* n_oovs);
+PGEN_API int pgen_stage_run(pgen_t* h);
+PGEN_API int pgen_stage_sync(pgen_t* h);
+PGEN_API int pgen_stage_download(pgen_t* h, int32_t* out_tokens, int32_t* out_lens, float* out_logprobs, double* out_avg);
+/* The handle's cudaStream_t (as void*), so that a harness can record CUDA events on it. */
+PGEN_API void* pgen_stream(pgen_t* h);
+
+/* Test hooks: copy a named device buffer of the last staged batch to the host.  Names:
+ * "enc_states" [B,T,2H], "enc_feat" [B,T,2H], "dec_c0" / "dec_h0" [B,H], "trace_tokens" /
+ * "trace_parents" [B,S,K] (int32), "trace_logp" [B,S,K].  Returns the element count in *n. */
+PGEN_API int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n);
+/* Test hook: choose kernel variants at run time (e.g. "vocab=simt", "vocab=tc", "profile=1"). */
+PGEN_API int pgen_set_option(pgen_t* h, const char* key_value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* PGEN_H_ */

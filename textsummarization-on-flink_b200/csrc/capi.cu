@@ -1,0 +1,258 @@
+// extern "C" boundary of libpgen_cuda.so (see include/pgen.h for the reference interfaces replaced).
+#include <chrono>
+#include <cstring>
+#include <deque>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/pgen.h"
+#include "engine.h"
+#include "text.h"
+
+using namespace pgn;
+
+namespace {
+thread_local std::string g_create_error;
+
+struct PendingRow {
+  std::string uuid, article, reference;
+  EncodedArticle enc;
+  std::chrono::steady_clock::time_point t_in;
+};
+struct DoneRow { std::string uuid, article, summary, reference; };
+struct RowsOwner { std::vector<DoneRow> rows; std::vector<pgen_row_t> views; };
+
+double ms_since(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+}  // namespace
+
+struct pgen {
+  HyperParams hp;
+  Vocab vocab;
+  Engine eng;
+  std::string err;
+  std::deque<PendingRow> pending;
+  std::deque<DoneRow> done;
+  EncodedArticle last_text;          // pgen_text_encode -> pgen_text_summary
+  uint64_t rows_in = 0, rows_out = 0, tokens_in = 0, tokens_out = 0;
+  double ms_host_text = 0;
+  std::vector<int32_t> b_ids, b_ext, b_lens, b_noov, b_tok, b_len;
+  std::vector<float> b_lp;
+  std::vector<double> b_avg;
+};
+
+static int fail(pgen_t* h, int code, const std::string& msg) {
+  if (h) h->err = msg; else g_create_error = msg;
+  return code;
+}
+
+// decode the first n pending rows as one device batch and move them to `done`
+static int run_pending(pgen_t* h, size_t n) {
+  const int T = (int)h->hp.max_enc_steps, S = (int)h->hp.max_dec_steps;
+  h->b_ids.assign(n * T, 0); h->b_ext.assign(n * T, 0); h->b_lens.assign(n, 0); h->b_noov.assign(n, 0);
+  for (size_t b = 0; b < n; ++b) {
+    const EncodedArticle& e = h->pending[b].enc;
+    h->b_lens[b] = (int)e.enc_ids.size();
+    h->b_noov[b] = (int)e.oovs.size();
+    memcpy(&h->b_ids[b * T], e.enc_ids.data(), e.enc_ids.size() * 4);
+    memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
+  }
+  h->b_tok.resize(n * S); h->b_len.resize(n); h->b_lp.resize(n * S); h->b_avg.resize(n);
+  std::string err = h->eng.upload((int)n, h->b_ids.data(), h->b_ext.data(), T, h->b_lens.data(), h->b_noov.data());
+  if (err.empty()) err = h->eng.run();
+  if (err.empty()) err = h->eng.sync();
+  if (err.empty()) err = h->eng.download(h->b_tok.data(), h->b_len.data(), h->b_lp.data(), h->b_avg.data());
+  if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);
+  auto t0 = std::chrono::steady_clock::now();
+  for (size_t b = 0; b < n; ++b) {
+    PendingRow& p = h->pending.front();
+    DoneRow d;
+    if (!summary_from_ids(h->vocab, p.enc.oovs, &h->b_tok[b * S], h->b_len[b], &d.summary))
+      return fail(h, PGEN_ERR_STATE, "decoder produced a token id outside the article's extended vocabulary");
+    h->tokens_out += h->b_len[b];
+    d.uuid = std::move(p.uuid); d.article = std::move(p.article); d.reference = std::move(p.reference);
+    h->done.push_back(std::move(d));
+    h->pending.pop_front();
+  }
+  h->ms_host_text += ms_since(t0);
+  return PGEN_OK;
+}
+
+extern "C" {
+
+int pgen_create(const char* hyperparams, int device_ordinal, pgen_t** out) {
+  if (!out) return fail(nullptr, PGEN_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  if (!hyperparams) return fail(nullptr, PGEN_ERR_ARG, "hyperparams is NULL");
+  std::unique_ptr<pgen> h(new pgen());
+  std::string err = parse_hyperparams(hyperparams, &h->hp);
+  if (!err.empty()) return fail(nullptr, PGEN_ERR_ARG, err);
+  const HyperParams& hp = h->hp;
+  if (hp.mode != "decode") {
+    if (hp.mode == "train" || hp.mode == "eval")
+      return fail(nullptr, PGEN_ERR_UNSUPPORTED, "mode=" + hp.mode + ": libpgen_cuda serves mode=decode only");
+    return fail(nullptr, PGEN_ERR_ARG, "The 'mode' flag must be one of train/eval/decode");   // run_summarization.py:426
+  }
+  err = h->vocab.load(hp.vocab_path, hp.vocab_size);                                          // :307
+  if (!err.empty()) return fail(nullptr, PGEN_ERR_IO, err);
+  int code = PGEN_OK;
+  err = h->eng.init(hp, h->vocab.size(), device_ordinal, &code);
+  if (!err.empty()) return fail(nullptr, code, err);
+  *out = h.release();
+  return PGEN_OK;
+}
+
+void pgen_destroy(pgen_t* h) { delete h; }
+
+const char* pgen_last_error(pgen_t* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int64_t pgen_flag_int(pgen_t* h, const char* name) { return (h && name) ? flag_int(h->hp, name) : -1; }
+
+int pgen_submit(pgen_t* h, const char* uuid, size_t uuid_len, const char* article, size_t article_len,
+                const char* reference, size_t reference_len) {
+  if (!h) return PGEN_ERR_ARG;
+  if ((!uuid && uuid_len) || (!article && article_len) || (!reference && reference_len))
+    return fail(h, PGEN_ERR_ARG, "NULL buffer with non-zero length");
+  auto t0 = std::chrono::steady_clock::now();
+  PendingRow p;
+  p.uuid.assign(uuid ? uuid : "", uuid_len);
+  p.article.assign(article ? article : "", article_len);
+  p.reference.assign(reference ? reference : "", reference_len);
+  encode_article(h->vocab, p.article, (int)h->hp.max_enc_steps, &p.enc);
+  p.t_in = t0;
+  h->tokens_in += p.enc.enc_ids.size();
+  ++h->rows_in;
+  h->pending.push_back(std::move(p));
+  h->ms_host_text += ms_since(t0);
+  if ((int64_t)h->pending.size() >= h->hp.articles_per_batch) return run_pending(h, (size_t)h->hp.articles_per_batch);
+  return PGEN_OK;
+}
+
+int pgen_poll(pgen_t* h, int flush, pgen_rows_t* out) {
+  if (!h || !out) return PGEN_ERR_ARG;
+  out->rows = nullptr; out->n_rows = 0; out->owner_ = nullptr;
+  if (!h->pending.empty()) {
+    const bool late = h->hp.flush_ms >= 0 && ms_since(h->pending.front().t_in) >= (double)h->hp.flush_ms;
+    if (flush || late) {
+      while (!h->pending.empty()) {
+        const size_t n = std::min<size_t>(h->pending.size(), (size_t)h->hp.articles_per_batch);
+        int rc = run_pending(h, n);
+        if (rc != PGEN_OK) return rc;
+      }
+    }
+  }
+  if (h->done.empty()) return PGEN_OK;
+  auto* own = new RowsOwner();
+  own->rows.assign(std::make_move_iterator(h->done.begin()), std::make_move_iterator(h->done.end()));
+  h->done.clear();
+  own->views.resize(own->rows.size());
+  for (size_t i = 0; i < own->rows.size(); ++i) {
+    const DoneRow& d = own->rows[i];
+    own->views[i] = {d.uuid.c_str(), d.uuid.size(), d.article.c_str(), d.article.size(),
+                     d.summary.c_str(), d.summary.size(), d.reference.c_str(), d.reference.size()};
+  }
+  h->rows_out += own->rows.size();
+  out->rows = own->views.data(); out->n_rows = own->views.size(); out->owner_ = own;
+  return PGEN_OK;
+}
+
+void pgen_rows_free(pgen_rows_t* rows) {
+  if (!rows) return;
+  delete static_cast<RowsOwner*>(rows->owner_);
+  rows->rows = nullptr; rows->n_rows = 0; rows->owner_ = nullptr;
+}
+
+int pgen_stats(pgen_t* h, pgen_stats_t* out) {
+  if (!h || !out) return PGEN_ERR_ARG;
+  memset(out, 0, sizeof *out);
+  const EngineStats& s = h->eng.stats;
+  out->rows_in = h->rows_in; out->rows_out = h->rows_out; out->batches = s.batches;
+  out->tokens_in = h->tokens_in; out->tokens_out = h->tokens_out; out->decode_steps = s.decode_steps;
+  out->article_steps = s.article_steps; out->early_stops = s.early_stops; out->kernel_launches = s.kernel_launches;
+  out->ms_host_text = h->ms_host_text; out->ms_h2d = s.ms_h2d; out->ms_encoder = s.ms_encoder;
+  out->ms_decoder = s.ms_decoder; out->ms_d2h = s.ms_d2h;
+  out->ms_attention = s.ms_attention; out->ms_vocab = s.ms_vocab; out->prof_steps = (double)s.prof_steps;
+  return PGEN_OK;
+}
+
+int pgen_text_encode(pgen_t* h, const char* article, size_t article_len, int32_t* enc_ids, int32_t* ext_ids,
+                     int cap, int32_t* enc_len, int32_t* n_oov) {
+  if (!h || (!article && article_len)) return PGEN_ERR_ARG;
+  encode_article(h->vocab, std::string_view(article ? article : "", article_len), (int)h->hp.max_enc_steps, &h->last_text);
+  const int n = (int)h->last_text.enc_ids.size();
+  if (enc_len) *enc_len = n;
+  if (n_oov) *n_oov = (int)h->last_text.oovs.size();
+  if (n > cap) return fail(h, PGEN_ERR_ARG, "pgen_text_encode: cap smaller than the encoded length");
+  if (enc_ids) memcpy(enc_ids, h->last_text.enc_ids.data(), (size_t)n * 4);
+  if (ext_ids) memcpy(ext_ids, h->last_text.ext_ids.data(), (size_t)n * 4);
+  return PGEN_OK;
+}
+
+int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out, size_t cap, size_t* len) {
+  if (!h || (!tokens && n_tokens) || n_tokens < 0) return PGEN_ERR_ARG;
+  std::string s;
+  if (!summary_from_ids(h->vocab, h->last_text.oovs, tokens, n_tokens, &s))
+    return fail(h, PGEN_ERR_ARG, "token id outside the extended vocabulary of the last encoded article");
+  if (len) *len = s.size();
+  if (out && cap) memcpy(out, s.data(), std::min(cap, s.size()));
+  return PGEN_OK;
+}
+
+int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
+                      const int32_t* enc_lens, const int32_t* n_oovs) {
+  if (!h || n_articles < 0 || (n_articles && (!enc_ids || !enc_ext_ids || !enc_lens))) return h ? fail(h, PGEN_ERR_ARG, "bad arguments") : PGEN_ERR_ARG;
+  std::string err = h->eng.upload(n_articles, enc_ids, enc_ext_ids, ld, enc_lens, n_oovs);
+  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
+}
+int pgen_stage_run(pgen_t* h) {
+  if (!h) return PGEN_ERR_ARG;
+  std::string err = h->eng.run();
+  return err.empty() ? PGEN_OK : fail(h, err.find("before") != std::string::npos ? PGEN_ERR_STATE : PGEN_ERR_CUDA, err);
+}
+int pgen_stage_sync(pgen_t* h) {
+  if (!h) return PGEN_ERR_ARG;
+  std::string err = h->eng.sync();
+  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
+}
+int pgen_stage_download(pgen_t* h, int32_t* out_tokens, int32_t* out_lens, float* out_logprobs, double* out_avg) {
+  if (!h) return PGEN_ERR_ARG;
+  std::string err = h->eng.download(out_tokens, out_lens, out_logprobs, out_avg);
+  return err.empty() ? PGEN_OK : fail(h, err.find("before") != std::string::npos ? PGEN_ERR_STATE : PGEN_ERR_CUDA, err);
+}
+void* pgen_stream(pgen_t* h) { return h ? (void*)h->eng.stream() : nullptr; }
+
+int pgen_decode_ids(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
+                    const int32_t* enc_lens, const int32_t* n_oovs, int32_t* out_tokens, int32_t* out_lens,
+                    float* out_logprobs, double* out_avg) {
+  if (!h) return PGEN_ERR_ARG;
+  if (n_articles < 0 || (n_articles && (!enc_ids || !enc_ext_ids || !enc_lens))) return fail(h, PGEN_ERR_ARG, "bad arguments");
+  const int cap = h->eng.capacity(), S = (int)h->hp.max_dec_steps;
+  for (int b0 = 0; b0 < n_articles; b0 += cap) {
+    const int n = std::min(cap, n_articles - b0);
+    int rc = pgen_stage_upload(h, n, enc_ids + (size_t)b0 * ld, enc_ext_ids + (size_t)b0 * ld, ld, enc_lens + b0,
+                               n_oovs ? n_oovs + b0 : nullptr);
+    if (rc == PGEN_OK) rc = pgen_stage_run(h);
+    if (rc == PGEN_OK) rc = pgen_stage_sync(h);
+    if (rc == PGEN_OK)
+      rc = pgen_stage_download(h, out_tokens ? out_tokens + (size_t)b0 * S : nullptr, out_lens ? out_lens + b0 : nullptr,
+                               out_logprobs ? out_logprobs + (size_t)b0 * S : nullptr, out_avg ? out_avg + b0 : nullptr);
+    if (rc != PGEN_OK) return rc;
+  }
+  return PGEN_OK;
+}
+
+int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n) {
+  if (!h || !name || !out || !n) return PGEN_ERR_ARG;
+  std::string err = h->eng.fetch(name, out, cap_bytes, n);
+  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
+}
+
+int pgen_set_option(pgen_t* h, const char* key_value) {
+  if (!h || !key_value) return PGEN_ERR_ARG;
+  std::string err = h->eng.set_option(key_value);
+  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
+}
+
+}  // extern "C"

@@ -1,0 +1,513 @@
+#include "engine.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+
+#include "../../include/pgen.h"
+
+namespace pgn {
+
+#define CK(call)                                                                        \
+  do {                                                                                  \
+    cudaError_t e__ = (call);                                                           \
+    if (e__ != cudaSuccess) return std::string(#call) + ": " + cudaGetErrorString(e__); \
+  } while (0)
+
+std::string Engine::check(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return std::string(what) + ": " + cudaGetErrorString(e);
+  return "";
+}
+
+template <class T>
+T* Engine::dalloc(size_t n) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) return nullptr;
+  cudaMemset(p, 0, std::max<size_t>(n, 1) * sizeof(T));
+  allocs_.push_back(p);
+  return (T*)p;
+}
+
+Engine::~Engine() {
+  if (device_ >= 0) cudaSetDevice(device_);
+  for (void* p : allocs_) cudaFree(p);
+  for (void* p : {(void*)h_ids_, (void*)h_ext_, (void*)h_lens_, (void*)h_noov_, (void*)h_uniq_, (void*)h_ucnt_,
+                  (void*)h_pstart_, (void*)h_plist_, (void*)h_nactive_, (void*)h_out_tok_, (void*)h_out_len_,
+                  (void*)h_out_lp_, (void*)h_out_avg_, (void*)h_steps_, (void*)h_rescnt_})
+    if (p) cudaFreeHost(p);
+  for (auto& e : ev_) if (e) cudaEventDestroy(e);
+  for (auto& e : pev_) if (e) cudaEventDestroy(e);
+  if (st_) cudaStreamDestroy(st_);
+}
+
+// --------------------------------------------------------------------------------------
+// .pgenw archive (see weights_io.py) -> device, every matrix stored [N_out, K_in]
+// --------------------------------------------------------------------------------------
+namespace {
+struct HostTensor { std::vector<uint32_t> dims; const float* data; size_t n; };
+
+std::string read_archive(const std::string& path, std::vector<char>* buf, std::map<std::string, HostTensor>* out) {
+  std::ifstream f(path, std::ios::binary | std::ios::ate);
+  if (!f) return "cannot open weights archive '" + path + "'";
+  const size_t sz = (size_t)f.tellg();
+  buf->resize(sz);
+  f.seekg(0);
+  f.read(buf->data(), sz);
+  if (sz < 12 || memcmp(buf->data(), "PGENW001", 8) != 0) return "'" + path + "' is not a .pgenw archive";
+  uint32_t n;
+  memcpy(&n, buf->data() + 8, 4);
+  size_t p = 12;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (p + 2 > sz) return "truncated weights archive";
+    uint16_t ln;
+    memcpy(&ln, buf->data() + p, 2); p += 2;
+    if (p + ln + 2 > sz) return "truncated weights archive";
+    std::string name(buf->data() + p, ln); p += ln;
+    uint8_t dtype = (uint8_t)(*buf)[p], ndim = (uint8_t)(*buf)[p + 1]; p += 2;
+    if (dtype != 0) return "tensor '" + name + "': unsupported dtype";
+    HostTensor t;
+    t.dims.resize(ndim);
+    if (p + 4 * ndim + 16 > sz) return "truncated weights archive";
+    memcpy(t.dims.data(), buf->data() + p, 4 * ndim); p += 4 * ndim;
+    uint64_t off, nb;
+    memcpy(&off, buf->data() + p, 8); memcpy(&nb, buf->data() + p + 8, 8); p += 16;
+    if (off + nb > sz || off % 4) return "tensor '" + name + "': bad offset";
+    t.data = reinterpret_cast<const float*>(buf->data() + off);
+    t.n = nb / 4;
+    (*out)[name] = t;
+  }
+  return "";
+}
+}  // namespace
+
+std::string Engine::load_weights(const std::string& path) {
+  std::vector<char> buf;
+  std::map<std::string, HostTensor> ts;
+  std::string err = read_archive(path, &buf, &ts);
+  if (!err.empty()) return err;
+  const int H = d_.H, E = d_.E, A = d_.A, V = d_.V;
+  const std::string P = "seq2seq/", D = P + "decoder/attention_decoder/";
+  auto need = [&](const std::string& name, size_t n, const float** out) -> std::string {
+    auto it = ts.find(name);
+    if (it == ts.end()) return "weights archive lacks variable '" + name + "'";
+    if (it->second.n != n) {
+      char m[256];
+      snprintf(m, sizeof m, "variable '%s' has %zu elements, the flags imply %zu", name.c_str(), it->second.n, n);
+      return m;
+    }
+    *out = it->second.data;
+    return "";
+  };
+  // upload helpers: as-is, or transposed [rows, cols] -> [cols, rows], optionally a row range first
+  auto up = [&](const float* src, size_t n, float** dst) -> std::string {
+    *dst = dalloc<float>(n);
+    if (!*dst) return "cudaMalloc failed for weights";
+    CK(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
+    return "";
+  };
+  auto upT = [&](const float* src, int rows, int cols, float** dst) -> std::string {
+    std::vector<float> t((size_t)rows * cols);
+    for (int r = 0; r < rows; ++r)
+      for (int c = 0; c < cols; ++c) t[(size_t)c * rows + r] = src[(size_t)r * cols + c];
+    return up(t.data(), t.size(), dst);
+  };
+  const float* p;
+#define NEED(name, n) do { err = need(name, n, &p); if (!err.empty()) return err; } while (0)
+#define UP(dst, n) do { err = up(p, n, dst); if (!err.empty()) return err; } while (0)
+#define UPT(dst, r, c) do { err = upT(p, r, c, dst); if (!err.empty()) return err; } while (0)
+  NEED(P + "embedding/embedding", (size_t)V * E); UP(&w_.emb, (size_t)V * E);
+  const char* dn[2] = {"fw", "bw"};
+  for (int dir = 0; dir < 2; ++dir) {
+    const std::string b = P + "encoder/bidirectional_rnn/" + dn[dir] + "/lstm_cell/";
+    NEED(b + "kernel", (size_t)(E + H) * 4 * H);
+    const float* k = p;
+    p = k; UPT(&w_.enc_kxT[dir], E, 4 * H);                       // rows 0..E-1 : x part  -> [4H, E]
+    p = k + (size_t)E * 4 * H; UP(&w_.enc_kh[dir], (size_t)H * 4 * H);   // rows E.. : h part, kept [H, 4H]
+    NEED(b + "bias", (size_t)4 * H); UP(&w_.enc_b[dir], (size_t)4 * H);
+  }
+  // the two directions' recurrent kernels must be contiguous for the step kernel: re-pack
+  {
+    float* both = dalloc<float>((size_t)2 * H * 4 * H);
+    if (!both) return "cudaMalloc failed for weights";
+    for (int dir = 0; dir < 2; ++dir)
+      CK(cudaMemcpy(both + (size_t)dir * H * 4 * H, w_.enc_kh[dir], (size_t)H * 4 * H * sizeof(float), cudaMemcpyDeviceToDevice));
+    w_.enc_kh[0] = both; w_.enc_kh[1] = both + (size_t)H * 4 * H;
+  }
+  NEED(P + "reduce_final_st/w_reduce_c", (size_t)A * H); UPT(&w_.red_wcT, A, H);
+  NEED(P + "reduce_final_st/w_reduce_h", (size_t)A * H); UPT(&w_.red_whT, A, H);
+  NEED(P + "reduce_final_st/bias_reduce_c", (size_t)H); UP(&w_.red_bc, (size_t)H);
+  NEED(P + "reduce_final_st/bias_reduce_h", (size_t)H); UP(&w_.red_bh, (size_t)H);
+  NEED(D + "W_h", (size_t)A * A); UPT(&w_.WhT, A, A);
+  NEED(D + "v", (size_t)A); UP(&w_.v, (size_t)A);
+  if (d_.use_cov) { NEED(D + "coverage/w_c", (size_t)A); UP(&w_.w_c, (size_t)A); }
+  else w_.w_c = w_.v;
+  NEED(D + "Attention/Linear/Matrix", (size_t)2 * H * A); UPT(&w_.att_MT, 2 * H, A);
+  NEED(D + "Attention/Linear/Bias", (size_t)A); UP(&w_.att_b, (size_t)A);
+  NEED(D + "Linear/Matrix", (size_t)(E + A) * E); UPT(&w_.x_MT, E + A, E);
+  NEED(D + "Linear/Bias", (size_t)E); UP(&w_.x_b, (size_t)E);
+  NEED(D + "lstm_cell/kernel", (size_t)(E + H) * 4 * H); UPT(&w_.dec_kT, E + H, 4 * H);
+  NEED(D + "lstm_cell/bias", (size_t)4 * H); UP(&w_.dec_b, (size_t)4 * H);
+  if (d_.pointer_gen) {
+    NEED(D + "calculate_pgen/Linear/Matrix", (size_t)d_.SW); UP(&w_.pg_w, (size_t)d_.SW);
+    NEED(D + "calculate_pgen/Linear/Bias", (size_t)1); UP(&w_.pg_b, (size_t)1);
+  }
+  NEED(D + "AttnOutputProjection/Linear/Matrix", (size_t)(H + A) * H); UPT(&w_.out_MT, H + A, H);
+  NEED(D + "AttnOutputProjection/Linear/Bias", (size_t)H); UP(&w_.out_b, (size_t)H);
+  NEED(P + "output_projection/w", (size_t)H * V); UPT(&w_.proj_wT, H, V);
+  NEED(P + "output_projection/v", (size_t)V); UP(&w_.proj_v, (size_t)V);
+#undef NEED
+#undef UP
+#undef UPT
+  return "";
+}
+
+std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int* code) {
+  *code = PGEN_ERR_CUDA;
+  device_ = device;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return "no CUDA device available (libpgen_cuda has no CPU fallback)";
+  }
+  if (device < 0 || device >= ndev) {
+    *code = PGEN_ERR_ARG;
+    return "device ordinal " + std::to_string(device) + " out of range (" + std::to_string(ndev) + " visible)";
+  }
+  CK(cudaSetDevice(device));
+  *code = PGEN_ERR_UNSUPPORTED;
+  d_.H = (int)hp.hidden_dim; d_.E = (int)hp.emb_dim; d_.A = 2 * d_.H; d_.V = vocab_size;
+  d_.K = (int)hp.beam_size; d_.K2 = 2 * d_.K; d_.T = (int)hp.max_enc_steps; d_.S = (int)hp.max_dec_steps;
+  d_.SW = d_.A + 2 * d_.H + d_.E; d_.min_dec_steps = (int)hp.min_dec_steps;
+  d_.use_cov = hp.coverage ? 1 : 0; d_.pointer_gen = hp.pointer_gen ? 1 : 0;
+  if (d_.H < 32 || d_.H % 32) return "hidden_dim must be a positive multiple of 32";
+  if (d_.E < 16 || d_.E % 16) return "emb_dim must be a positive multiple of 16";
+  if (d_.K < 1 || d_.K > 16) return "beam_size must be in 1..16";
+  if (d_.T < 1 || d_.S < 1) return "max_enc_steps and max_dec_steps must be positive";
+  if (d_.V < 2 * d_.K + 4) return "vocabulary smaller than 2*beam_size";
+  if (hp.articles_per_batch < 1 || hp.articles_per_batch > 4096) { *code = PGEN_ERR_ARG; return "articles_per_batch must be in 1..4096"; }
+  Bcap_ = (int)hp.articles_per_batch;
+  R_ = Bcap_ * d_.K;
+  *code = PGEN_ERR_CUDA;
+  CK(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
+  for (auto& e : ev_) CK(cudaEventCreate(&e));
+
+  *code = PGEN_ERR_IO;
+  std::string wpath = hp.weights_path;
+  if (wpath.empty()) wpath = hp.log_root + "/" + hp.exp_name + "/train/model.pgenw";   // util.py:34
+  std::string err = load_weights(wpath);
+  if (!err.empty()) return err;
+
+  *code = PGEN_ERR_CUDA;
+  const size_t B = Bcap_, T = d_.T, K = d_.K, R = R_, H = d_.H, A = d_.A, E = d_.E, S = d_.S, V = d_.V;
+#define HOSTALLOC(p, n) CK(cudaMallocHost((void**)&p, std::max<size_t>((n), 1) * sizeof(*p)))
+  HOSTALLOC(h_ids_, B * T); HOSTALLOC(h_ext_, B * T); HOSTALLOC(h_lens_, B); HOSTALLOC(h_noov_, B);
+  HOSTALLOC(h_uniq_, B * T); HOSTALLOC(h_ucnt_, B); HOSTALLOC(h_pstart_, B * (T + 1)); HOSTALLOC(h_plist_, B * T);
+  HOSTALLOC(h_nactive_, 1); HOSTALLOC(h_out_tok_, B * S); HOSTALLOC(h_out_len_, B); HOSTALLOC(h_out_lp_, B * S);
+  HOSTALLOC(h_out_avg_, B); HOSTALLOC(h_steps_, B); HOSTALLOC(h_rescnt_, B);
+#undef HOSTALLOC
+#define DALLOC(p, type, n) do { p = dalloc<type>(n); if (!p) return std::string("cudaMalloc failed for " #p); } while (0)
+  DALLOC(ids_, int, B * T); DALLOC(ext_, int, B * T); DALLOC(lens_, int, B); DALLOC(noov_, int, B);
+  DALLOC(uniq_, int, B * T); DALLOC(ucnt_, int, B); DALLOC(pstart_, int, B * (T + 1)); DALLOC(plist_, int, B * T);
+  DALLOC(zx_, float, 2 * B * T * 4 * H); DALLOC(enc_states_, float, B * T * A); DALLOC(enc_feat_, float, B * T * A);
+  DALLOC(h_enc_[0], float, 2 * B * H); DALLOC(h_enc_[1], float, 2 * B * H); DALLOC(c_enc_, float, 2 * B * H);
+  for (int i = 0; i < 2; ++i) {
+    DALLOC(state_[i], float, R * d_.SW); DALLOC(attn_[i], float, R * T); DALLOC(cov_[i], float, R * T);
+  }
+  DALLOC(xin_, float, R * (E + A)); DALLOC(hprev_, float, R * H); DALLOC(cprev_, float, R * H);
+  DALLOC(z_, float, R * 4 * H); DALLOC(dfeat_, float, R * A); DALLOC(e_, float, R * T); DALLOC(out_, float, R * H);
+  DALLOC(pgen_, float, R); DALLOC(logits_, float, R * V); DALLOC(rowmax_, float, R); DALLOC(rowsum_, float, R);
+  DALLOC(topk_ids_, int, R * 2 * K); DALLOC(topk_logp_, float, R * 2 * K);
+  DALLOC(bb_.active, int, B); DALLOC(bb_.sel_parent, int, R); DALLOC(bb_.sel_token, int, R);
+  DALLOC(bb_.beam_sum, double, R); DALLOC(bb_.res_count, int, B); DALLOC(bb_.res_sum, double, R);
+  DALLOC(bb_.res_len, int, R); DALLOC(bb_.res_step, int, R); DALLOC(bb_.res_parent, int, R); DALLOC(bb_.res_lp, float, R);
+  DALLOC(bb_.hist_tok, int, B * S * K); DALLOC(bb_.hist_par, int, B * S * K); DALLOC(bb_.hist_logp, float, B * S * K);
+  DALLOC(bb_.steps_done, int, B); DALLOC(bb_.n_active, int, 1); DALLOC(bb_.best_kind, int, B); DALLOC(bb_.best_idx, int, B);
+  DALLOC(out_tok_, int, B * S); DALLOC(out_len_, int, B); DALLOC(out_lp_, float, B * S); DALLOC(out_avg_, double, B);
+#undef DALLOC
+  CK(cudaDeviceSynchronize());
+  *code = PGEN_OK;
+  return "";
+}
+
+std::string Engine::set_option(const std::string& kv) {
+  const size_t eq = kv.find('=');
+  if (eq == std::string::npos) return "option must be key=value";
+  const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
+  if (k == "check_every") { check_every_ = std::max(1, atoi(v.c_str())); return ""; }
+  if (k == "profile") {
+    profile_ = atoi(v.c_str()) != 0;
+    if (profile_ && pev_.empty()) {
+      pev_.resize((size_t)4 * d_.S);
+      for (auto& e : pev_) CK(cudaEventCreate(&e));
+    }
+    return "";
+  }
+  return "unknown option '" + k + "'";
+}
+
+// --------------------------------------------------------------------------------------
+// Stage: H2D
+// --------------------------------------------------------------------------------------
+std::string Engine::upload(int n, const int32_t* enc_ids, const int32_t* ext_ids, int ld, const int32_t* lens,
+                           const int32_t* n_oovs) {
+  if (n < 0 || n > Bcap_) return "n_articles exceeds articles_per_batch";
+  CK(cudaSetDevice(device_));
+  const int T = d_.T;
+  nB_ = n;
+  max_len_ = 0;
+  std::vector<std::pair<int, int>> tmp;
+  for (int b = 0; b < n; ++b) {
+    const int len = lens[b];
+    if (len < 0 || len > T || len > ld) return "enc_lens[" + std::to_string(b) + "] outside 0..max_enc_steps";
+    const int no = n_oovs ? n_oovs[b] : 0;
+    h_lens_[b] = len;
+    h_noov_[b] = no;
+    max_len_ = std::max(max_len_, len);
+    int32_t* hi = h_ids_ + (size_t)b * T;
+    int32_t* he = h_ext_ + (size_t)b * T;
+    tmp.clear();
+    for (int t = 0; t < len; ++t) {
+      const int id = enc_ids[(size_t)b * ld + t], ex = ext_ids[(size_t)b * ld + t];
+      if (id < 0 || id >= d_.V) return "enc_ids out of range";
+      if (ex < 0 || ex >= d_.V + no) return "enc_ext_ids outside the extended vocabulary";
+      hi[t] = id; he[t] = ex;
+      tmp.emplace_back(ex, t);
+    }
+    for (int t = len; t < T; ++t) { hi[t] = 0; he[t] = 0; }
+    // unique extended ids (ascending) with their positions in ascending t: the order in which
+    // tf.scatter_nd accumulates duplicates (model.py:170-176)
+    std::sort(tmp.begin(), tmp.end());
+    int32_t* hu = h_uniq_ + (size_t)b * T;
+    int32_t* hs = h_pstart_ + (size_t)b * (T + 1);
+    int32_t* hp = h_plist_ + (size_t)b * T;
+    int nu = 0;
+    for (int q = 0; q < len; ++q) {
+      if (q == 0 || tmp[q].first != tmp[q - 1].first) { hu[nu] = tmp[q].first; hs[nu] = q; ++nu; }
+      hp[q] = tmp[q].second;
+    }
+    hs[nu] = len;
+    h_ucnt_[b] = nu;
+  }
+  CK(cudaEventRecord(ev_[0], st_));
+  const size_t nT = (size_t)n * T;
+  if (n > 0) {
+    CK(cudaMemcpyAsync(ids_, h_ids_, nT * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(ext_, h_ext_, nT * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(lens_, h_lens_, (size_t)n * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(noov_, h_noov_, (size_t)n * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(uniq_, h_uniq_, nT * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(ucnt_, h_ucnt_, (size_t)n * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(pstart_, h_pstart_, (size_t)n * (T + 1) * 4, cudaMemcpyHostToDevice, st_));
+    CK(cudaMemcpyAsync(plist_, h_plist_, nT * 4, cudaMemcpyHostToDevice, st_));
+  }
+  CK(cudaEventRecord(ev_[1], st_));
+  staged_ = true; ran_ = false; synced_ = false;
+  return "";
+}
+
+// --------------------------------------------------------------------------------------
+// Encoder: embedding gather fused into the input projection, BiLSTM, state reduce, W_h features
+// --------------------------------------------------------------------------------------
+void Engine::encoder() {
+  const int B = nB_, T = d_.T, H = d_.H, A = d_.A, E = d_.E, K = d_.K;
+  uint64_t& nl = stats.kernel_launches;
+  cudaMemsetAsync(enc_states_, 0, (size_t)B * T * A * sizeof(float), st_);   // outputs past enc_len are zero
+  cudaMemsetAsync(h_enc_[0], 0, (size_t)2 * B * H * sizeof(float), st_);
+  cudaMemsetAsync(c_enc_, 0, (size_t)2 * B * H * sizeof(float), st_);
+  for (int dir = 0; dir < 2; ++dir) {                  // zx = emb[ids] . Kx + bias   (model.py:213, LSTMCell)
+    GemmArgs g;
+    g.A0 = w_.emb; g.lda0 = E; g.k0 = E; g.gather0 = ids_;
+    g.B = w_.enc_kxT[dir]; g.ldb = E; g.bias = w_.enc_b[dir];
+    g.C = zx_ + (size_t)dir * B * T * 4 * H; g.ldc = 4 * H; g.M = B * T; g.N = 4 * H;
+    nl += launch_gemm_nt(g, st_);
+  }
+  for (int s = 0; s < max_len_; ++s)                   // model.py:90-93
+    nl += launch_enc_lstm_step(d_, B, s, lens_, zx_, w_.enc_kh[0], h_enc_[s & 1], h_enc_[(s + 1) & 1], c_enc_,
+                               enc_states_, st_);
+  const float* hfin = h_enc_[max_len_ & 1];
+  {                                                    // model.py:117-120 -> row b*K of the "old" state
+    GemmArgs g;
+    g.A0 = c_enc_; g.lda0 = H; g.k0 = H; g.A1 = c_enc_ + (size_t)B * H; g.lda1 = H; g.k1 = H;
+    g.B = w_.red_wcT; g.ldb = A; g.bias = w_.red_bc; g.act = 1;
+    g.C = state_[0] + A; g.ldc = K * d_.SW; g.M = B; g.N = H;
+    nl += launch_gemm_nt(g, st_);
+    g.A0 = hfin; g.A1 = hfin + (size_t)B * H; g.B = w_.red_whT; g.bias = w_.red_bh; g.C = state_[0] + A + H;
+    nl += launch_gemm_nt(g, st_);
+  }
+  {                                                    // attention_decoder.py:67, once per article
+    GemmArgs g;
+    g.A0 = enc_states_; g.lda0 = A; g.k0 = A; g.B = w_.WhT; g.ldb = A;
+    g.C = enc_feat_; g.ldc = A; g.M = B * T; g.N = A;
+    nl += launch_gemm_nt(g, st_);
+  }
+}
+
+// --------------------------------------------------------------------------------------
+// Decoder: initial attention pass + step loop
+// --------------------------------------------------------------------------------------
+void Engine::decoder() {
+  const int B = nB_, T = d_.T, H = d_.H, A = d_.A, E = d_.E, K = d_.K, R = B * K, SW = d_.SW;
+  uint64_t& nl = stats.kernel_launches;
+  nl += launch_init_beam(d_, B, lens_, bb_, st_);
+  if (d_.use_cov) cudaMemsetAsync(cov_[0], 0, (size_t)R * T * sizeof(float), st_);   // beam_search.py:105
+  {  // attention_decoder.py:138-140: context of the initial state (row b*K only; all K hyps are identical)
+    GemmArgs g;
+    g.A0 = state_[0] + A; g.lda0 = K * SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
+    g.C = dfeat_; g.ldc = K * A; g.M = B; g.N = A;
+    nl += launch_gemm_nt(g, st_);
+    nl += launch_attn_energy(d_, B, 1, lens_, bb_.active, enc_feat_, dfeat_, cov_[0], w_.v, w_.w_c, e_, st_);
+    nl += launch_attn_context(d_, B, 1, lens_, bb_.active, enc_states_, e_, attn_[0], state_[0], st_);
+  }
+  int steps = 0;
+  for (int s = 0; s < d_.S; ++s) {
+    const int o = s & 1, n = o ^ 1;
+    StepBufs sb;
+    sb.lens = lens_; sb.n_oov = noov_; sb.active = bb_.active; sb.sel_parent = bb_.sel_parent; sb.sel_token = bb_.sel_token;
+    sb.emb = w_.emb; sb.state_old = state_[o]; sb.state_new = state_[n]; sb.attn_old = attn_[o]; sb.attn_new = attn_[n];
+    sb.cov_old = cov_[o]; sb.cov_new = cov_[n]; sb.xin = xin_; sb.hprev = hprev_; sb.cprev = cprev_;
+    nl += launch_gather_step(d_, B, sb, st_);
+    GemmArgs g;
+    // x = [emb(y); ctx] . Linear/Matrix + Bias                                  (attention_decoder.py:150)
+    g = GemmArgs(); g.A0 = xin_; g.lda0 = E + A; g.k0 = E + A; g.B = w_.x_MT; g.ldb = E + A; g.bias = w_.x_b;
+    g.C = state_[n] + A + 2 * H; g.ldc = SW; g.M = R; g.N = E;
+    nl += launch_gemm_nt(g, st_);
+    // LSTM cell                                                                   (:153)
+    g = GemmArgs(); g.A0 = state_[n] + A + 2 * H; g.lda0 = SW; g.k0 = E; g.A1 = hprev_; g.lda1 = H; g.k1 = H;
+    g.B = w_.dec_kT; g.ldb = E + H; g.bias = w_.dec_b; g.C = z_; g.ldc = 4 * H; g.M = R; g.N = 4 * H;
+    nl += launch_gemm_nt(g, st_);
+    nl += launch_lstm_pointwise(d_, R, z_, cprev_, state_[n], bb_.active, st_);
+    // attention on the new state, coverage not updated                            (:156-158)
+    g = GemmArgs(); g.A0 = state_[n] + A; g.lda0 = SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
+    g.C = dfeat_; g.ldc = A; g.M = R; g.N = A;
+    nl += launch_gemm_nt(g, st_);
+    if (profile_) cudaEventRecord(pev_[4 * s + 0], st_);
+    nl += launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[n], w_.v, w_.w_c, e_, st_);
+    nl += launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[n], state_[n], st_);
+    if (profile_) cudaEventRecord(pev_[4 * s + 1], st_);
+    if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, st_);   // :166-167
+    // output = [h; ctx] . AttnOutputProjection + b                                (:173)
+    g = GemmArgs(); g.A0 = state_[n] + A + H; g.lda0 = SW; g.k0 = H; g.A1 = state_[n]; g.lda1 = SW; g.k1 = A;
+    g.B = w_.out_MT; g.ldb = H + A; g.bias = w_.out_b; g.C = out_; g.ldc = H; g.M = R; g.N = H;
+    nl += launch_gemm_nt(g, st_);
+    // vocabulary scores                                                           (model.py:236)
+    g = GemmArgs(); g.A0 = out_; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;
+    g.C = logits_; g.ldc = d_.V; g.M = R; g.N = d_.V;
+    if (profile_) cudaEventRecord(pev_[4 * s + 2], st_);
+    nl += launch_gemm_nt(g, st_);
+    if (profile_) cudaEventRecord(pev_[4 * s + 3], st_);
+    nl += launch_softmax_stats(d_, R, logits_, rowmax_, rowsum_, bb_.active, st_);
+    FinalArgs fa;
+    fa.logits = logits_; fa.rowmax = rowmax_; fa.rowsum = rowsum_; fa.pgen = pgen_; fa.attn = attn_[n];
+    fa.uniq_ids = uniq_; fa.uniq_cnt = ucnt_; fa.pos_start = pstart_; fa.pos_list = plist_; fa.n_oov = noov_;
+    fa.active = bb_.active; fa.topk_ids = topk_ids_; fa.topk_logp = topk_logp_;
+    nl += launch_final_topk(d_, B, fa, st_);
+    nl += launch_beam_step(d_, B, s, topk_ids_, topk_logp_, bb_, st_);
+    ++steps;
+    if (s + 1 < d_.S && s + 1 > d_.min_dec_steps && (s + 1) % check_every_ == 0) {
+      cudaMemcpyAsync(h_nactive_, bb_.n_active, sizeof(int), cudaMemcpyDeviceToHost, st_);
+      cudaStreamSynchronize(st_);
+      if (*h_nactive_ == 0) break;
+    }
+  }
+  stats.decode_steps += steps;
+  pev_used_ = profile_ ? steps : 0;
+  nl += launch_finalize(d_, B, lens_, bb_, out_tok_, out_len_, out_lp_, out_avg_, st_);
+}
+
+std::string Engine::run() {
+  if (!staged_) return "pgen_stage_run before pgen_stage_upload";
+  CK(cudaSetDevice(device_));
+  CK(cudaEventRecord(ev_[2], st_));
+  if (nB_ > 0) encoder();
+  CK(cudaEventRecord(ev_[3], st_));
+  if (nB_ > 0) decoder();
+  CK(cudaEventRecord(ev_[4], st_));
+  std::string err = check("decode launch");
+  if (!err.empty()) return err;
+  ran_ = true; synced_ = false;
+  ++stats.batches;
+  return "";
+}
+
+std::string Engine::sync() {
+  CK(cudaSetDevice(device_));
+  CK(cudaStreamSynchronize(st_));
+  if (ran_ && !synced_) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ev_[0], ev_[1]) == cudaSuccess) stats.ms_h2d = ms;
+    if (cudaEventElapsedTime(&ms, ev_[2], ev_[3]) == cudaSuccess) stats.ms_encoder = ms;
+    if (cudaEventElapsedTime(&ms, ev_[3], ev_[4]) == cudaSuccess) stats.ms_decoder = ms;
+    if (pev_used_ > 0) {
+      stats.ms_attention = stats.ms_vocab = 0;
+      for (int s = 0; s < pev_used_; ++s) {
+        if (cudaEventElapsedTime(&ms, pev_[4 * s], pev_[4 * s + 1]) == cudaSuccess) stats.ms_attention += ms;
+        if (cudaEventElapsedTime(&ms, pev_[4 * s + 2], pev_[4 * s + 3]) == cudaSuccess) stats.ms_vocab += ms;
+      }
+      stats.prof_steps = pev_used_;
+    }
+    synced_ = true;
+  }
+  return check("decode");
+}
+
+std::string Engine::download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg) {
+  if (!ran_) return "pgen_stage_download before pgen_stage_run";
+  CK(cudaSetDevice(device_));
+  const size_t n = nB_, S = d_.S;
+  CK(cudaEventRecord(ev_[5], st_));
+  if (n > 0) {
+    CK(cudaMemcpyAsync(h_out_tok_, out_tok_, n * S * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_out_len_, out_len_, n * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_out_lp_, out_lp_, n * S * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_out_avg_, out_avg_, n * 8, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_steps_, bb_.steps_done, n * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_rescnt_, bb_.res_count, n * 4, cudaMemcpyDeviceToHost, st_));
+  }
+  CK(cudaEventRecord(ev_[6], st_));
+  CK(cudaStreamSynchronize(st_));
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, ev_[5], ev_[6]) == cudaSuccess) stats.ms_d2h = ms;
+  std::string err = check("download");
+  if (!err.empty()) return err;
+  for (size_t b = 0; b < n; ++b) {
+    stats.article_steps += h_steps_[b];
+    if (h_rescnt_[b] >= d_.K) ++stats.early_stops;
+  }
+  if (out_tokens) memcpy(out_tokens, h_out_tok_, n * S * 4);
+  if (out_lens) memcpy(out_lens, h_out_len_, n * 4);
+  if (out_logp) memcpy(out_logp, h_out_lp_, n * S * 4);
+  if (out_avg) memcpy(out_avg, h_out_avg_, n * 8);
+  return "";
+}
+
+std::string Engine::fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n) {
+  if (!ran_) return "pgen_debug_fetch before pgen_stage_run";
+  CK(cudaSetDevice(device_));
+  CK(cudaStreamSynchronize(st_));
+  const size_t B = nB_, T = d_.T, A = d_.A, H = d_.H, S = d_.S, K = d_.K;
+  const void* src = nullptr;
+  size_t cnt = 0, esz = 4;
+  if (name == "enc_states") { src = enc_states_; cnt = B * T * A; }
+  else if (name == "enc_feat") { src = enc_feat_; cnt = B * T * A; }
+  else if (name == "trace_tokens") { src = bb_.hist_tok; cnt = B * S * K; }
+  else if (name == "trace_parents") { src = bb_.hist_par; cnt = B * S * K; }
+  else if (name == "trace_logp") { src = bb_.hist_logp; cnt = B * S * K; }
+  else if (name == "steps_done") { src = bb_.steps_done; cnt = B; }
+  else if (name == "dec_c0" || name == "dec_h0") {
+    // the initial state is overwritten by step 1 (double buffering): only valid with max_dec_steps == 1
+    cnt = B * H;
+    if (cap_bytes < cnt * 4) return "buffer too small";
+    const float* base = state_[0] + A + (name == "dec_h0" ? H : 0);
+    CK(cudaMemcpy2D(out, H * 4, base, (size_t)K * d_.SW * 4, H * 4, B, cudaMemcpyDeviceToHost));
+    *n = cnt;
+    return "";
+  } else return "unknown debug buffer '" + name + "'";
+  if (cap_bytes < cnt * esz) return "buffer too small";
+  if (cnt) CK(cudaMemcpy(out, src, cnt * esz, cudaMemcpyDeviceToHost));
+  *n = cnt;
+  return "";
+}
+
+}  // namespace pgn

@@ -1,0 +1,82 @@
+// Device-side decode engine: weights in HBM, one batch slot, encoder + beam-search step loop.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "text.h"
+
+namespace pgn {
+
+struct DeviceWeights {
+  float *emb, *enc_kxT[2], *enc_kh[2], *enc_b[2];
+  float *red_wcT, *red_whT, *red_bc, *red_bh;
+  float *WhT, *v, *w_c, *att_MT, *att_b, *x_MT, *x_b, *dec_kT, *dec_b, *pg_w, *pg_b, *out_MT, *out_b;
+  float *proj_wT, *proj_v;
+};
+
+struct EngineStats {
+  uint64_t batches = 0, decode_steps = 0, article_steps = 0, early_stops = 0, kernel_launches = 0;
+  double ms_h2d = 0, ms_encoder = 0, ms_decoder = 0, ms_d2h = 0;
+  double ms_attention = 0, ms_vocab = 0, ms_beam = 0;   // summed over the steps of the last profiled batch
+  uint64_t prof_steps = 0;
+};
+
+class Engine {
+ public:
+  ~Engine();
+  // Returns "" or an error message; *code receives the PGEN_ERR_* class.
+  std::string init(const HyperParams& hp, int vocab_size, int device, int* code);
+  std::string upload(int n, const int32_t* enc_ids, const int32_t* ext_ids, int ld, const int32_t* lens,
+                     const int32_t* n_oovs);
+  std::string run();
+  std::string sync();
+  std::string download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg);
+  std::string fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n);
+  std::string set_option(const std::string& kv);
+  cudaStream_t stream() const { return st_; }
+  int capacity() const { return Bcap_; }
+  const Dims& dims() const { return d_; }
+  EngineStats stats;
+
+ private:
+  std::string load_weights(const std::string& path);
+  void encoder();
+  void decoder();
+  template <class T> T* dalloc(size_t n);
+  std::string check(const char* what);
+
+  Dims d_{};
+  int device_ = 0, Bcap_ = 0, R_ = 0, nB_ = 0, max_len_ = 0;
+  bool staged_ = false, ran_ = false, synced_ = false;
+  int check_every_ = 8;
+  bool profile_ = false;
+  std::vector<cudaEvent_t> pev_;   // 4 events per step when profiling: attn begin, attn end/vocab begin... 
+  int pev_used_ = 0;
+  cudaStream_t st_ = nullptr;
+  cudaEvent_t ev_[7] = {};
+  DeviceWeights w_{};
+  std::vector<void*> allocs_;
+  // host staging (pinned)
+  int32_t *h_ids_ = nullptr, *h_ext_ = nullptr, *h_lens_ = nullptr, *h_noov_ = nullptr, *h_uniq_ = nullptr,
+          *h_ucnt_ = nullptr, *h_pstart_ = nullptr, *h_plist_ = nullptr, *h_nactive_ = nullptr;
+  int32_t *h_out_tok_ = nullptr, *h_out_len_ = nullptr, *h_steps_ = nullptr, *h_rescnt_ = nullptr;
+  float* h_out_lp_ = nullptr;
+  double* h_out_avg_ = nullptr;
+  // device batch slot
+  int *ids_, *ext_, *lens_, *noov_, *uniq_, *ucnt_, *pstart_, *plist_;
+  float *zx_, *enc_states_, *enc_feat_, *h_enc_[2], *c_enc_;
+  float *state_[2], *attn_[2], *cov_[2], *xin_, *hprev_, *cprev_, *z_, *dfeat_, *e_, *out_, *pgen_, *logits_,
+      *rowmax_, *rowsum_, *topk_logp_;
+  int* topk_ids_;
+  BeamBufs bb_{};
+  int *out_tok_, *out_len_;
+  float* out_lp_;
+  double* out_avg_;
+};
+
+}  // namespace pgn

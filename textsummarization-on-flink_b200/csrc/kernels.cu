@@ -1,0 +1,783 @@
+// sm_100a kernels of the pointer-generator decode path (first, all-fp32 SIMT generation).
+// File:line citations are relative to /root/reference/src/main/python/pointer-generator/.
+//
+// Row convention: decoder row r = b*K + k (article b, beam slot k).  Every per-element reduction
+// runs in an order that depends only on that element's own row/article, so an article's result
+// does not depend on what else shares the device batch.
+#include "kernels.h"
+
+#include <cfloat>
+#include <cmath>
+
+namespace pgn {
+
+// ======================================================================================
+// Generic fp32 GEMM  C = act([A0|A1] . B^T + bias)
+// ======================================================================================
+constexpr int GBK = 16;
+
+template <int BM, int BN, int TM, int TN>
+__global__ void __launch_bounds__((BM / TM) * (BN / TN))
+gemm_nt_kernel(GemmArgs g) {
+  constexpr int NT = (BM / TM) * (BN / TN);
+  __shared__ __align__(16) float As[GBK][BM + 4];
+  __shared__ __align__(16) float Bs[GBK][BN + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid % (BN / TN), ty = tid / (BN / TN);
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int Ktot = g.k0 + g.k1;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  for (int kt = 0; kt < Ktot; kt += GBK) {
+    const bool seg0 = kt < g.k0;
+    // A tile: BM rows x 16 k  (BM*4 float4)
+    for (int idx = tid; idx < BM * 4; idx += NT) {
+      const int row = idx >> 2, k4 = (idx & 3) * 4;
+      const int m = m0 + row;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < g.M) {
+        const float* src;
+        if (seg0) {
+          const long long rr = g.gather0 ? (long long)g.gather0[m] : (long long)m;
+          src = g.A0 + rr * g.lda0 + kt + k4;
+        } else {
+          src = g.A1 + (long long)m * g.lda1 + (kt - g.k0) + k4;
+        }
+        v = *reinterpret_cast<const float4*>(src);
+      }
+      As[k4 + 0][row] = v.x; As[k4 + 1][row] = v.y; As[k4 + 2][row] = v.z; As[k4 + 3][row] = v.w;
+    }
+    for (int idx = tid; idx < BN * 4; idx += NT) {
+      const int row = idx >> 2, k4 = (idx & 3) * 4;
+      const int n = n0 + row;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (n < g.N) v = *reinterpret_cast<const float4*>(g.B + (long long)n * g.ldb + kt + k4);
+      Bs[k4 + 0][row] = v.x; Bs[k4 + 1][row] = v.y; Bs[k4 + 2][row] = v.z; Bs[k4 + 3][row] = v.w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < GBK; ++k) {
+      float a[TM], b[TN];
+#pragma unroll
+      for (int i = 0; i < TM; i += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(&As[k][ty * TM + i]);
+        a[i] = t.x; a[i + 1] = t.y; a[i + 2] = t.z; a[i + 3] = t.w;
+      }
+#pragma unroll
+      for (int j = 0; j < TN; j += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(&Bs[k][tx * TN + j]);
+        b[j] = t.x; b[j + 1] = t.y; b[j + 2] = t.z; b[j + 3] = t.w;
+      }
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + ty * TM + i;
+    if (m >= g.M) continue;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + tx * TN + j;
+      if (n >= g.N) continue;
+      float v = acc[i][j] + (g.bias ? g.bias[n] : 0.f);
+      if (g.act == 1) v = fmaxf(v, 0.f);
+      g.C[(long long)m * g.ldc + n] = v;
+    }
+  }
+}
+
+int launch_gemm_nt(const GemmArgs& a, cudaStream_t st) {
+  if (a.M <= 0 || a.N <= 0) return 0;
+  const long long work = (long long)a.M * a.N;
+  if (work >= 128LL * 128 * 296) {
+    dim3 grid((a.N + 127) / 128, (a.M + 127) / 128);
+    gemm_nt_kernel<128, 128, 8, 8><<<grid, 256, 0, st>>>(a);
+  } else if (work >= 64LL * 64 * 148) {
+    dim3 grid((a.N + 63) / 64, (a.M + 63) / 64);
+    gemm_nt_kernel<64, 64, 4, 4><<<grid, 256, 0, st>>>(a);
+  } else {
+    dim3 grid((a.N + 31) / 32, (a.M + 31) / 32);
+    gemm_nt_kernel<32, 32, 4, 4><<<grid, 64, 0, st>>>(a);
+  }
+  return 1;
+}
+
+// ======================================================================================
+// Encoder LSTM time step (both directions)
+// ======================================================================================
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+
+constexpr int ENC_AG = 8;   // articles per block
+
+__global__ void __launch_bounds__(128)
+enc_lstm_step_kernel(int H, int T, int B, int s, const int* __restrict__ lens, const float* __restrict__ zx,
+                     const float* __restrict__ kh, const float* __restrict__ h_prev, float* __restrict__ h_next,
+                     float* __restrict__ c_state, float* __restrict__ enc_states) {
+  extern __shared__ float sm[];
+  float* hs = sm;                       // [ENC_AG][H]
+  float* zs = sm + ENC_AG * H;          // [ENC_AG][4][32]
+  const int tid = threadIdx.x;
+  const int chunk = blockIdx.x, dir = blockIdx.y, b0 = blockIdx.z * ENC_AG;
+  const int gate = tid >> 5, ul = tid & 31, u = chunk * 32 + ul;
+  const int n = gate * H + u;
+  const int H4 = 4 * H;
+  const float* hp = h_prev + (size_t)dir * B * H;
+  for (int i = tid; i < ENC_AG * H; i += 128) {
+    const int a = i / H, k = i - a * H;
+    hs[i] = (b0 + a < B) ? hp[(size_t)(b0 + a) * H + k] : 0.f;
+  }
+  float acc[ENC_AG];
+#pragma unroll
+  for (int a = 0; a < ENC_AG; ++a) {
+    const int b = b0 + a;
+    int t = -1;
+    if (b < B) {
+      const int len = lens[b];
+      if (s < len) t = dir == 0 ? s : len - 1 - s;      // bw: reverse over the article's own length
+    }
+    acc[a] = t >= 0 ? zx[((size_t)dir * B * T + (size_t)b * T + t) * H4 + n] : 0.f;
+  }
+  __syncthreads();
+  const float* w = kh + (size_t)dir * H * H4 + n;
+  for (int k = 0; k < H; ++k) {
+    const float wk = w[(size_t)k * H4];
+#pragma unroll
+    for (int a = 0; a < ENC_AG; ++a) acc[a] = fmaf(hs[a * H + k], wk, acc[a]);
+  }
+#pragma unroll
+  for (int a = 0; a < ENC_AG; ++a) zs[(a * 4 + gate) * 32 + ul] = acc[a];
+  __syncthreads();
+  for (int i = tid; i < ENC_AG * 32; i += 128) {
+    const int a = i >> 5, l = i & 31, b = b0 + a, uu = chunk * 32 + l;
+    if (b >= B) continue;
+    const size_t si = (size_t)dir * B * H + (size_t)b * H + uu;
+    // recompute t for article a (tpos[] is indexed by a compile-time-unrolled a only)
+    const int len = lens[b];
+    if (s < len) {
+      const int t = dir == 0 ? s : len - 1 - s;
+      const float zi = zs[(a * 4 + 0) * 32 + l], zj = zs[(a * 4 + 1) * 32 + l];
+      const float zf = zs[(a * 4 + 2) * 32 + l], zo = zs[(a * 4 + 3) * 32 + l];
+      const float c = sigmoidf_(zf + 1.0f) * c_state[si] + sigmoidf_(zi) * tanhf(zj);   // LSTMCell, forget_bias 1
+      const float h = sigmoidf_(zo) * tanhf(c);
+      c_state[si] = c;
+      h_next[si] = h;
+      enc_states[((size_t)b * T + t) * (2 * H) + dir * H + uu] = h;                       // model.py:93
+    } else {
+      h_next[si] = hs[a * H + uu];                      // past the end: state frozen (dynamic_rnn)
+    }
+  }
+}
+
+int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const float* zx, const float* kh,
+                         const float* h_prev, float* h_next, float* c_state, float* enc_states,
+                         cudaStream_t st) {
+  dim3 grid(d.H / 32, 2, (B + ENC_AG - 1) / ENC_AG);
+  const size_t smem = (size_t)(ENC_AG * d.H + ENC_AG * 4 * 32) * sizeof(float);
+  enc_lstm_step_kernel<<<grid, 128, smem, st>>>(d.H, d.T, B, s, lens, zx, kh, h_prev, h_next, c_state, enc_states);
+  return 1;
+}
+
+// ======================================================================================
+// Decoder step: gather by parent, LSTM pointwise
+// ======================================================================================
+__global__ void __launch_bounds__(128)
+gather_step_kernel(Dims d, StepBufs b) {
+  const int r = blockIdx.x;
+  const int art = r / d.K;
+  if (!b.active[art]) return;
+  const int p = b.sel_parent[r];
+  int tok = b.sel_token[r];
+  if (tok >= d.V) tok = 0;                                           // beam_search.py:112-113  OOV -> [UNK]
+  const int rp = art * d.K + p;
+  const float* so = b.state_old + (size_t)rp * d.SW;
+  float* xin = b.xin + (size_t)r * (d.E + d.A);
+  const float* er = b.emb + (size_t)tok * d.E;
+  for (int i = threadIdx.x; i < d.E; i += 128) xin[i] = er[i];       // model.py:214
+  for (int i = threadIdx.x; i < d.A; i += 128) xin[d.E + i] = so[i]; // previous context
+  for (int i = threadIdx.x; i < d.H; i += 128) {
+    b.cprev[(size_t)r * d.H + i] = so[d.A + i];
+    b.hprev[(size_t)r * d.H + i] = so[d.A + d.H + i];
+  }
+  if (d.use_cov) {                                                   // attention_decoder.py:114
+    const int len = b.lens[art];
+    const float* co = b.cov_old + (size_t)rp * d.T;
+    const float* ao = b.attn_old + (size_t)rp * d.T;
+    float* cn = b.cov_new + (size_t)r * d.T;
+    for (int t = threadIdx.x; t < len; t += 128) cn[t] = co[t] + ao[t];
+  }
+}
+
+int launch_gather_step(const Dims& d, int B, const StepBufs& b, cudaStream_t st) {
+  gather_step_kernel<<<B * d.K, 128, 0, st>>>(d, b);
+  return 1;
+}
+
+__global__ void lstm_pointwise_kernel(int H, int A, int SW, int K, int R, const float* __restrict__ z,
+                                      const float* __restrict__ cprev, float* __restrict__ state_new,
+                                      const int* __restrict__ active) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R * H) return;
+  const int r = i / H, u = i - r * H;
+  if (!active[r / K]) return;
+  const float* zr = z + (size_t)r * 4 * H;
+  const float zi = zr[u], zj = zr[H + u], zf = zr[2 * H + u], zo = zr[3 * H + u];
+  const float c = sigmoidf_(zf + 1.0f) * cprev[i] + sigmoidf_(zi) * tanhf(zj);
+  const float h = sigmoidf_(zo) * tanhf(c);
+  state_new[(size_t)r * SW + A + u] = c;
+  state_new[(size_t)r * SW + A + H + u] = h;
+}
+
+int launch_lstm_pointwise(const Dims& d, int R, const float* z, const float* cprev, float* state_new,
+                          const int* active, cudaStream_t st) {
+  const int n = R * d.H;
+  lstm_pointwise_kernel<<<(n + 255) / 256, 256, 0, st>>>(d.H, d.A, d.SW, d.K, R, z, cprev, state_new, active);
+  return 1;
+}
+
+// ======================================================================================
+// Attention: energies, then softmax + context
+// ======================================================================================
+constexpr int ATT_TCH = 16;     // encoder positions per block (2 per warp)
+
+template <int KMAX>
+__global__ void __launch_bounds__(256)
+attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __restrict__ active,
+                   const float* __restrict__ enc_feat, const float* __restrict__ dfeat,
+                   const float* __restrict__ cov, const float* __restrict__ v, const float* __restrict__ w_c,
+                   float* __restrict__ e) {
+  extern __shared__ __align__(16) float sm[];
+  const int art = blockIdx.y;
+  if (!active[art]) return;
+  const int len = lens[art];
+  const int t0 = blockIdx.x * ATT_TCH;
+  if (t0 >= len) return;
+  const int A = d.A;
+  float* ds = sm;                 // [rpa][A]
+  float* vs = ds + KMAX * A;      // [A]
+  float* ws = vs + A;             // [A]
+  for (int i = threadIdx.x; i < rpa * A; i += 256) {
+    const int k = i / A, a = i - k * A;
+    ds[i] = dfeat[(size_t)(art * d.K + k) * A + a];
+  }
+  for (int i = threadIdx.x; i < A; i += 256) { vs[i] = v[i]; ws[i] = d.use_cov ? w_c[i] : 0.f; }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int tt = warp; tt < ATT_TCH; tt += 8) {
+    const int t = t0 + tt;
+    if (t >= len) break;
+    float cv[KMAX], acc[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      acc[k] = 0.f;
+      cv[k] = (d.use_cov && k < rpa) ? cov[(size_t)(art * d.K + k) * d.T + t] : 0.f;
+    }
+    const float4* f4 = reinterpret_cast<const float4*>(enc_feat + ((size_t)art * d.T + t) * A);
+    for (int a4 = lane; a4 < A / 4; a4 += 32) {
+      const float4 f = __ldg(f4 + a4);
+      const float4 vv = *reinterpret_cast<const float4*>(vs + a4 * 4);
+      const float4 ww = *reinterpret_cast<const float4*>(ws + a4 * 4);
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        if (k < rpa) {
+          const float4 dd = *reinterpret_cast<const float4*>(ds + k * A + a4 * 4);
+          float x;
+          x = f.x + dd.x + cv[k] * ww.x; acc[k] = fmaf(vv.x, tanhf(x), acc[k]);
+          x = f.y + dd.y + cv[k] * ww.y; acc[k] = fmaf(vv.y, tanhf(x), acc[k]);
+          x = f.z + dd.z + cv[k] * ww.z; acc[k] = fmaf(vv.z, tanhf(x), acc[k]);
+          x = f.w + dd.w + cv[k] * ww.w; acc[k] = fmaf(vv.w, tanhf(x), acc[k]);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      if (k < rpa) {
+        float s = acc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) e[(size_t)(art * d.K + k) * d.T + t] = s;
+      }
+    }
+  }
+}
+
+int launch_attn_energy(const Dims& d, int B, int rpa, const int* lens, const int* active,
+                       const float* enc_feat, const float* dfeat, const float* cov, const float* v,
+                       const float* w_c, float* e, cudaStream_t st) {
+  dim3 grid((d.T + ATT_TCH - 1) / ATT_TCH, B);
+  if (d.K <= 4) {
+    const size_t smem = (size_t)(4 * d.A + 2 * d.A) * sizeof(float);
+    attn_energy_kernel<4><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+  } else if (d.K <= 8) {
+    const size_t smem = (size_t)(8 * d.A + 2 * d.A) * sizeof(float);
+    attn_energy_kernel<8><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+  } else {
+    const size_t smem = (size_t)(16 * d.A + 2 * d.A) * sizeof(float);
+    static bool set = false;
+    if (!set) { cudaFuncSetAttribute(attn_energy_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); set = true; }
+    attn_energy_kernel<16><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+  }
+  return 1;
+}
+
+constexpr int CTX_COLS = 64;    // context columns per block
+
+template <int KMAX>
+__global__ void __launch_bounds__(256)
+attn_context_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __restrict__ active,
+                    const float* __restrict__ enc_states, const float* __restrict__ e,
+                    float* __restrict__ attn, float* __restrict__ state) {
+  extern __shared__ __align__(16) float sm[];
+  const int art = blockIdx.y;
+  if (!active[art]) return;
+  const int len = lens[art];
+  const int T = d.T, A = d.A;
+  float* as = sm;                         // [KMAX][T]
+  float* red = sm + KMAX * T;             // [8][KMAX][CTX_COLS]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // masked softmax per row (attention_decoder.py:96-101); mask == (t < len)
+  for (int k = warp; k < rpa; k += 8) {
+    const float* er = e + (size_t)(art * d.K + k) * T;
+    float m = -FLT_MAX;
+    for (int t = lane; t < len; t += 32) m = fmaxf(m, er[t]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float s = 0.f;
+    for (int t = lane; t < len; t += 32) { const float x = expf(er[t] - m); as[k * T + t] = x; s += x; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    float s2 = 0.f;
+    for (int t = lane; t < len; t += 32) { const float x = as[k * T + t] / s; as[k * T + t] = x; s2 += x; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    for (int t = lane; t < len; t += 32) {
+      const float x = as[k * T + t] / s2;                             // re-normalise (:100-101)
+      as[k * T + t] = x;
+      if (blockIdx.x == 0) attn[(size_t)(art * d.K + k) * T + t] = x;
+    }
+  }
+  __syncthreads();
+  // context = sum_t attn[t] * h_t   (:126-127)
+  const int c4 = threadIdx.x & 15, tl = threadIdx.x >> 4;             // 16 float4 columns x 16 t-lanes
+  const int col = blockIdx.x * CTX_COLS + c4 * 4;
+  float4 acc[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* hb = enc_states + (size_t)art * T * A + col;
+  for (int t = tl; t < len; t += 16) {
+    const float4 h = __ldg(reinterpret_cast<const float4*>(hb + (size_t)t * A));
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      if (k < rpa) {
+        const float a = as[k * T + t];
+        acc[k].x = fmaf(a, h.x, acc[k].x); acc[k].y = fmaf(a, h.y, acc[k].y);
+        acc[k].z = fmaf(a, h.z, acc[k].z); acc[k].w = fmaf(a, h.w, acc[k].w);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    acc[k].x += __shfl_xor_sync(0xffffffffu, acc[k].x, 16);
+    acc[k].y += __shfl_xor_sync(0xffffffffu, acc[k].y, 16);
+    acc[k].z += __shfl_xor_sync(0xffffffffu, acc[k].z, 16);
+    acc[k].w += __shfl_xor_sync(0xffffffffu, acc[k].w, 16);
+    if (lane < 16 && k < rpa)
+      *reinterpret_cast<float4*>(red + ((size_t)warp * KMAX + k) * CTX_COLS + c4 * 4) = acc[k];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < rpa * CTX_COLS; i += 256) {
+    const int k = i / CTX_COLS, c = i - k * CTX_COLS;
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[((size_t)w * KMAX + k) * CTX_COLS + c];
+    state[(size_t)(art * d.K + k) * d.SW + blockIdx.x * CTX_COLS + c] = s;
+  }
+}
+
+template <int KMAX>
+static void launch_ctx_t(const Dims& d, int B, int rpa, const int* lens, const int* active,
+                         const float* enc_states, const float* e, float* attn, float* state, cudaStream_t st) {
+  const size_t smem = (size_t)(KMAX * d.T + 8 * KMAX * CTX_COLS) * sizeof(float);
+  static bool set = false;
+  if (!set && smem > 48 * 1024) {
+    cudaFuncSetAttribute(attn_context_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    set = true;
+  }
+  dim3 grid(d.A / CTX_COLS, B);
+  attn_context_kernel<KMAX><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_states, e, attn, state);
+}
+
+int launch_attn_context(const Dims& d, int B, int rpa, const int* lens, const int* active,
+                        const float* enc_states, const float* e, float* attn, float* state, cudaStream_t st) {
+  if (d.K <= 4) launch_ctx_t<4>(d, B, rpa, lens, active, enc_states, e, attn, state, st);
+  else if (d.K <= 8) launch_ctx_t<8>(d, B, rpa, lens, active, enc_states, e, attn, state, st);
+  else launch_ctx_t<16>(d, B, rpa, lens, active, enc_states, e, attn, state, st);
+  return 1;
+}
+
+// ======================================================================================
+// p_gen, softmax statistics
+// ======================================================================================
+__global__ void __launch_bounds__(256)
+pgen_kernel(int SW, int K, int R, const float* __restrict__ state, const float* __restrict__ w,
+            const float* __restrict__ bias, float* __restrict__ pgen, const int* __restrict__ active) {
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (r >= R || !active[r / K]) return;
+  const float* s = state + (size_t)r * SW;
+  float acc = 0.f;
+  for (int i = lane; i < SW; i += 32) acc = fmaf(s[i], w[i], acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) pgen[r] = sigmoidf_(acc + bias[0]);
+}
+
+int launch_pgen(const Dims& d, int R, const float* state, const float* pg_w, const float* pg_b, float* pgen,
+                const int* active, cudaStream_t st) {
+  pgen_kernel<<<(R + 7) / 8, 256, 0, st>>>(d.SW, d.K, R, state, pg_w, pg_b, pgen, active);
+  return 1;
+}
+
+__device__ __forceinline__ float block_reduce_max(float v, float* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  float r = sh[0];
+  for (int i = 1; i < nw; ++i) r = fmaxf(r, sh[i]);
+  return r;
+}
+__device__ __forceinline__ float block_reduce_sum(float v, float* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+  for (int i = 0; i < nw; ++i) r += sh[i];
+  return r;
+}
+
+__global__ void __launch_bounds__(256)
+softmax_stats_kernel(int V, int K, const float* __restrict__ logits, float* __restrict__ rowmax,
+                     float* __restrict__ rowsum, const int* __restrict__ active) {
+  __shared__ float sh[8];
+  const int r = blockIdx.x;
+  if (!active[r / K]) return;
+  const float* l = logits + (size_t)r * V;
+  float m = -FLT_MAX;
+  for (int i = threadIdx.x; i < V; i += 256) m = fmaxf(m, l[i]);
+  m = block_reduce_max(m, sh);
+  float s = 0.f;
+  for (int i = threadIdx.x; i < V; i += 256) s += expf(l[i] - m);
+  s = block_reduce_sum(s, sh);
+  if (threadIdx.x == 0) { rowmax[r] = m; rowsum[r] = s; }
+}
+
+int launch_softmax_stats(const Dims& d, int R, const float* logits, float* rowmax, float* rowsum,
+                         const int* active, cudaStream_t st) {
+  softmax_stats_kernel<<<R, 256, 0, st>>>(d.V, d.K, logits, rowmax, rowsum, active);
+  return 1;
+}
+
+// ======================================================================================
+// Final distribution + top-2K
+// ======================================================================================
+__device__ __forceinline__ bool better(float v1, int i1, float v2, int i2) {
+  return v1 > v2 || (v1 == v2 && i1 < i2);          // tf.nn.top_k: descending, ties -> lower index
+}
+
+template <int K2MAX>
+__device__ __forceinline__ void topk_insert(float (&tv)[K2MAX], int (&ti)[K2MAX], int k2, float v, int i) {
+  if (!better(v, i, tv[K2MAX - 1], ti[K2MAX - 1])) return;
+  tv[K2MAX - 1] = v; ti[K2MAX - 1] = i;
+#pragma unroll
+  for (int j = K2MAX - 1; j > 0; --j) {
+    if (better(tv[j], ti[j], tv[j - 1], ti[j - 1])) {
+      const float fv = tv[j]; tv[j] = tv[j - 1]; tv[j - 1] = fv;
+      const int fi = ti[j]; ti[j] = ti[j - 1]; ti[j - 1] = fi;
+    }
+  }
+  (void)k2;
+}
+
+template <int K2MAX>
+__global__ void __launch_bounds__(256)
+final_topk_kernel(Dims d, FinalArgs a) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  const int r = blockIdx.x, art = r / d.K;
+  if (!a.active[art]) return;
+  const int V = d.V, T = d.T, K2 = d.K2;
+  const int nbm = (V + 31) / 32;
+  unsigned* bitmap = reinterpret_cast<unsigned*>(smraw);                  // [nbm]
+  float* cv = reinterpret_cast<float*>(bitmap + nbm);                     // [256*K2MAX]
+  int* ci = reinterpret_cast<int*>(cv + 256 * K2MAX);                     // [256*K2MAX]
+  float* redv = reinterpret_cast<float*>(ci + 256 * K2MAX);               // [8]
+  int* redi = reinterpret_cast<int*>(redv + 8);                           // [8]
+  int* redw = redi + 8;                                                   // [8] owner thread
+  const float* l = a.logits + (size_t)r * V;
+  const float m = a.rowmax[r], s = a.rowsum[r];
+  const float pg = d.pointer_gen ? a.pgen[r] : 1.f;
+  const int nu = d.pointer_gen ? a.uniq_cnt[art] : 0;
+  const int* uid = a.uniq_ids + (size_t)art * T;
+  for (int i = threadIdx.x; i < nbm; i += 256) bitmap[i] = 0u;
+  __syncthreads();
+  for (int u = threadIdx.x; u < nu; u += 256) {
+    const int id = uid[u];
+    if (id < V) atomicOr(&bitmap[id >> 5], 1u << (id & 31));
+  }
+  __syncthreads();
+  float tv[K2MAX];
+  int ti[K2MAX];
+#pragma unroll
+  for (int j = 0; j < K2MAX; ++j) { tv[j] = -FLT_MAX; ti[j] = 0x7fffffff; }
+  // vocabulary words that do not occur in the article: p_gen * softmax        (model.py:158)
+  for (int w = threadIdx.x; w < V; w += 256) {
+    if ((bitmap[w >> 5] >> (w & 31)) & 1u) continue;
+    const float val = d.pointer_gen ? pg * (expf(l[w] - m) / s) : expf(l[w] - m) / s;
+    topk_insert<K2MAX>(tv, ti, K2, val, w);
+  }
+  // extended-vocabulary ids that occur in the article: add the copy mass       (model.py:159-181)
+  if (nu > 0) {
+    const int* ps = a.pos_start + (size_t)art * (T + 1);
+    const int* pl = a.pos_list + (size_t)art * T;
+    const float* at = a.attn + (size_t)r * T;
+    const float omp = 1.0f - pg;
+    for (int u = threadIdx.x; u < nu; u += 256) {
+      const int id = uid[u];
+      float copy = 0.f;
+      for (int q = ps[u]; q < ps[u + 1]; ++q) copy += omp * at[pl[q]];     // scatter_nd: duplicates accumulate
+      const float vocab = id < V ? pg * (expf(l[id] - m) / s) : 0.f;       // zeros for in-article OOVs (:162-164)
+      topk_insert<K2MAX>(tv, ti, K2, vocab + copy, id);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < K2MAX; ++j) { cv[threadIdx.x * K2MAX + j] = tv[j]; ci[threadIdx.x * K2MAX + j] = ti[j]; }
+  __syncthreads();
+  // K2 rounds of block arg-best over the heads of the 256 sorted lists
+  int head = 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int round = 0; round < K2; ++round) {
+    float bv = head < K2MAX ? cv[threadIdx.x * K2MAX + head] : -FLT_MAX;
+    int bi = head < K2MAX ? ci[threadIdx.x * K2MAX + head] : 0x7fffffff;
+    int bw = threadIdx.x;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      const int ow = __shfl_xor_sync(0xffffffffu, bw, o);
+      if (better(ov, oi, bv, bi)) { bv = ov; bi = oi; bw = ow; }
+    }
+    if (lane == 0) { redv[warp] = bv; redi[warp] = bi; redw[warp] = bw; }
+    __syncthreads();
+    float fv = redv[0]; int fi = redi[0], fw = redw[0];
+#pragma unroll
+    for (int w8 = 1; w8 < 8; ++w8)
+      if (better(redv[w8], redi[w8], fv, fi)) { fv = redv[w8]; fi = redi[w8]; fw = redw[w8]; }
+    if (threadIdx.x == fw) ++head;
+    if (threadIdx.x == 0) {
+      const bool valid = fi != 0x7fffffff;
+      a.topk_ids[(size_t)r * K2 + round] = valid ? fi : 0;
+      a.topk_logp[(size_t)r * K2 + round] = valid ? logf(fv) : -INFINITY;    // model.py:285
+    }
+    __syncthreads();
+  }
+}
+
+template <int K2MAX>
+static void launch_final_t(const Dims& d, int B, const FinalArgs& a, cudaStream_t st) {
+  const size_t smem = (size_t)((d.V + 31) / 32) * 4 + (size_t)256 * K2MAX * 8 + 8 * 12 + 16;
+  static size_t set = 0;
+  if (smem > 48 * 1024 && smem > set) {
+    cudaFuncSetAttribute(final_topk_kernel<K2MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    set = smem;
+  }
+  final_topk_kernel<K2MAX><<<B * d.K, 256, smem, st>>>(d, a);
+}
+
+int launch_final_topk(const Dims& d, int B, const FinalArgs& a, cudaStream_t st) {
+  if (d.K2 <= 8) launch_final_t<8>(d, B, a, st);
+  else if (d.K2 <= 16) launch_final_t<16>(d, B, a, st);
+  else launch_final_t<32>(d, B, a, st);
+  return 1;
+}
+
+// ======================================================================================
+// Beam bookkeeping (beam_search.py:100-168)
+// ======================================================================================
+constexpr int kStop = 3, kStart = 2;
+constexpr int BEAM_MAXC = 512;      // K * 2K candidates, K <= 16
+
+__global__ void __launch_bounds__(128)
+beam_step_kernel(Dims d, int step, const int* __restrict__ topk_ids, const float* __restrict__ topk_logp, BeamBufs b) {
+  __shared__ double keys[BEAM_MAXC];
+  __shared__ double sums[BEAM_MAXC];
+  __shared__ int order[BEAM_MAXC];
+  __shared__ int n_new_s;
+  const int art = blockIdx.x;
+  if (!b.active[art]) return;
+  const int K = d.K, K2 = d.K2;
+  const int num_orig = step == 0 ? 1 : K;                               // :127-129
+  const int nc = num_orig * K2;
+  for (int c = threadIdx.x; c < nc; c += 128) {
+    const int i = c / K2;
+    const float lp = topk_logp[(size_t)(art * K + i) * K2 + (c - i * K2)];
+    const double s = b.beam_sum[art * K + i] + (double)lp;              // Hypothesis.log_prob (:72-74), float64
+    sums[c] = s;
+    keys[c] = s / (double)(step + 2);                                   // avg_log_prob (:77-79), [START] counted
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < nc; c += 128) {                         // stable descending sort == rank count
+    const double kc = keys[c];
+    int rank = 0;
+    for (int o = 0; o < nc; ++o) rank += (keys[o] > kc || (keys[o] == kc && o < c)) ? 1 : 0;
+    order[rank] = c;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int n_new = 0, n_res = b.res_count[art];
+    for (int rk = 0; rk < nc; ++rk) {                                   // :145-154
+      const int c = order[rk];
+      const int i = c / K2;
+      const int tok = topk_ids[(size_t)(art * K + i) * K2 + (c - i * K2)];
+      const float lp = topk_logp[(size_t)(art * K + i) * K2 + (c - i * K2)];
+      if (tok == kStop) {
+        if (step >= d.min_dec_steps) {
+          const int q = art * K + n_res;
+          b.res_sum[q] = sums[c]; b.res_len[q] = step + 2; b.res_step[q] = step; b.res_parent[q] = i;
+          b.res_lp[q] = lp;
+          ++n_res;
+        }
+      } else {
+        const size_t hq = ((size_t)art * d.S + step) * K + n_new;
+        b.hist_tok[hq] = tok; b.hist_par[hq] = i; b.hist_logp[hq] = lp;
+        b.sel_parent[art * K + n_new] = i;
+        b.sel_token[art * K + n_new] = tok;
+        order[n_new] = c;                                               // reuse: slot -> candidate (n_new <= rk)
+        ++n_new;
+      }
+      if (n_new == K || n_res == K) break;
+    }
+    n_new_s = n_new;
+    b.res_count[art] = n_res;
+    b.steps_done[art] = step + 1;
+    const bool go = (step + 1 < d.S) && (n_res < K);                    // :110
+    if (!go) {
+      b.active[art] = 0;
+      atomicSub(b.n_active, 1);
+      if (n_res == 0) { b.best_kind[art] = 1; b.best_idx[art] = 0; }    // :160-162 results = hyps; hyps[0] is best
+      else {
+        int best = 0;
+        double bk = b.res_sum[art * K] / (double)b.res_len[art * K];
+        for (int q = 1; q < n_res; ++q) {                               // :165-168 stable: first maximum wins
+          const double k2 = b.res_sum[art * K + q] / (double)b.res_len[art * K + q];
+          if (k2 > bk) { bk = k2; best = q; }
+        }
+        b.best_kind[art] = 0; b.best_idx[art] = best;
+      }
+    }
+  }
+  __syncthreads();
+  for (int sidx = threadIdx.x; sidx < n_new_s; sidx += 128) b.beam_sum[art * K + sidx] = sums[order[sidx]];
+}
+
+int launch_beam_step(const Dims& d, int B, int step, const int* topk_ids, const float* topk_logp,
+                     const BeamBufs& b, cudaStream_t st) {
+  beam_step_kernel<<<B, 128, 0, st>>>(d, step, topk_ids, topk_logp, b);
+  return 1;
+}
+
+__global__ void init_beam_kernel(Dims d, int B, const int* __restrict__ lens, BeamBufs b) {
+  const int art = blockIdx.x * blockDim.x + threadIdx.x;
+  if (art == 0) *b.n_active = 0;
+  __threadfence();
+  if (art >= B) return;
+  const int act = lens[art] > 0 ? 1 : 0;
+  b.active[art] = act;
+  b.res_count[art] = 0;
+  b.steps_done[art] = 0;
+  b.best_kind[art] = 2;
+  b.best_idx[art] = 0;
+  for (int k = 0; k < d.K; ++k) {
+    b.sel_parent[art * d.K + k] = 0;
+    b.sel_token[art * d.K + k] = kStart;                                // :100
+    b.beam_sum[art * d.K + k] = 0.0;                                    // log_probs=[0.0] (:101)
+  }
+}
+__global__ void count_active_kernel(int B, const int* __restrict__ active, int* n_active) {
+  int n = 0;
+  for (int i = 0; i < B; ++i) n += active[i];
+  *n_active = n;
+}
+
+int launch_init_beam(const Dims& d, int B, const int* lens, const BeamBufs& b, cudaStream_t st) {
+  init_beam_kernel<<<(B + 127) / 128, 128, 0, st>>>(d, B, lens, b);
+  count_active_kernel<<<1, 1, 0, st>>>(B, b.active, b.n_active);
+  return 2;
+}
+
+__global__ void finalize_kernel(Dims d, int B, const int* __restrict__ lens, BeamBufs b, int* __restrict__ out_tokens,
+                                int* __restrict__ out_len, float* __restrict__ out_logp, double* __restrict__ out_avg) {
+  const int art = blockIdx.x * blockDim.x + threadIdx.x;
+  if (art >= B) return;
+  const int K = d.K, S = d.S;
+  int kind = b.best_kind[art];
+  if (lens[art] <= 0) kind = 2;
+  int* ot = out_tokens + (size_t)art * S;
+  float* ol = out_logp + (size_t)art * S;
+  if (kind == 2) {
+    out_len[art] = 0; out_avg[art] = 0.0;
+    for (int i = 0; i < S; ++i) { ot[i] = 0; ol[i] = 0.f; }
+    return;
+  }
+  int step, slot, n;
+  if (kind == 0) {
+    const int q = art * K + b.best_idx[art];
+    const int rs = b.res_step[q];
+    n = rs + 1;
+    ot[rs] = kStop;
+    ol[rs] = b.res_lp[q];
+    step = rs - 1; slot = b.res_parent[q];
+    out_avg[art] = b.res_sum[q] / (double)b.res_len[q];
+  } else {
+    const int sd = b.steps_done[art];
+    n = sd; step = sd - 1; slot = 0;
+    out_avg[art] = b.beam_sum[art * K] / (double)(sd + 1);
+  }
+  out_len[art] = n;
+  for (int i = n; i < S; ++i) { ot[i] = 0; ol[i] = 0.f; }      // entries past out_len are zero
+  while (step >= 0) {
+    const size_t hq = ((size_t)art * S + step) * K + slot;
+    ot[step] = b.hist_tok[hq];
+    ol[step] = b.hist_logp[hq];
+    slot = b.hist_par[hq];
+    --step;
+  }
+}
+
+int launch_finalize(const Dims& d, int B, const int* lens, const BeamBufs& b, int* out_tokens, int* out_len,
+                    float* out_logp, double* out_avg, cudaStream_t st) {
+  finalize_kernel<<<(B + 63) / 64, 64, 0, st>>>(d, B, lens, b, out_tokens, out_len, out_logp, out_avg);
+  return 1;
+}
+
+__global__ void fill_kernel(float* p, float v, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+int launch_fill(float* p, float v, size_t n, cudaStream_t st) {
+  if (n == 0) return 0;
+  fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, v, n);
+  return 1;
+}
+
+}  // namespace pgn

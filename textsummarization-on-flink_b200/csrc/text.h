@@ -1,0 +1,68 @@
+// Host-side text path of the decode operator: flag parsing, vocabulary, article -> ids,
+// ids -> summary string.  Integer / byte work only; mirrors data.py, batcher.py, decode.py and the
+// flag table of run_summarization.py (paths relative to
+// /root/reference/src/main/python/pointer-generator/).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <string_view>
+#include <unordered_map>
+#include <vector>
+#include <deque>
+
+namespace pgn {
+
+constexpr int kUnkId = 0, kPadId = 1, kStartId = 2, kStopId = 3;   // data.py:50-54
+
+struct HyperParams {                       // run_summarization.py:48-88 (names and defaults)
+  std::string data_path, vocab_path, mode = "train", log_root, exp_name;
+  int64_t num_steps = 0, hidden_dim = 256, emb_dim = 128, batch_size = 16, max_enc_steps = 400,
+          max_dec_steps = 100, beam_size = 4, min_dec_steps = 35, vocab_size = 50000;
+  bool single_pass = false, inference = false, pointer_gen = true, coverage = false,
+       convert_to_coverage_model = false, restore_best_model = false, debug = false;
+  // Flags that only this library knows; the reference's parser ignores them (known_only=True).
+  int64_t articles_per_batch = 64;         // device-level article batching
+  int64_t flush_ms = 50;                   // deadline after which poll() decodes a partial batch
+  std::string weights_path;                // overrides <log_root>/<exp_name>/train/model.pgenw
+};
+
+// Returns "" on success, else the error message.  Token 0 is a dummy program name
+// (TensorFlowTest.java:41); unknown flags are ignored; mode=decode forces batch_size := beam_size
+// (run_summarization.py:312-313).
+std::string parse_hyperparams(const std::string& s, HyperParams* hp);
+// -1 when the name is not an integer/boolean flag.
+int64_t flag_int(const HyperParams& hp, const std::string& name);
+
+class Vocab {                              // data.py:37-91
+ public:
+  // Returns "" on success.  max_size == 0 reads the whole file.
+  std::string load(const std::string& path, int64_t max_size);
+  int word2id(std::string_view w) const {  // data.py:77-81
+    auto it = map_.find(w);
+    return it == map_.end() ? kUnkId : it->second;
+  }
+  const std::string& id2word(int id) const { return words_[id]; }
+  int size() const { return (int)words_.size(); }
+  int warnings() const { return warnings_; }
+
+ private:
+  struct SvHash { size_t operator()(std::string_view s) const { return std::hash<std::string_view>()(s); } };
+  std::deque<std::string> words_;   // stable addresses: map_ keys view into these
+  std::unordered_map<std::string_view, int, SvHash> map_;
+  int warnings_ = 0;
+};
+
+struct EncodedArticle {                    // Example.__init__ (batcher.py:36-81), encoder side
+  std::vector<int32_t> enc_ids;            // OOV -> [UNK]              (batcher.py:56)
+  std::vector<int32_t> ext_ids;            // j-th distinct OOV -> V+j  (data.py:156-168)
+  std::vector<std::string> oovs;           // first-appearance order
+};
+
+void encode_article(const Vocab& v, std::string_view article, int max_enc_steps, EncodedArticle* out);
+
+// tokens after [START] -> summary (data.py:196-219, decode.py:109-118, 167-182).  Returns false
+// when a token id is outside the extended vocabulary of this article.
+bool summary_from_ids(const Vocab& v, const std::vector<std::string>& oovs, const int32_t* tokens,
+                      int n_tokens, std::string* out);
+
+}  // namespace pgn

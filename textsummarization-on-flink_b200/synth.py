@@ -82,7 +82,7 @@ def make_weights(kind: str = "W1", vsize: int = 50000, hidden: int = 256, emb: i
         lstm_mag, tn_std, glorot_gain, stop_bias, bias_std = 0.02, 1e-4, 1.0, 0.0, 0.0
         emb_std = proj_std = red_std = tn_std
     elif kind == "W1":
-        lstm_mag, emb_std, proj_std, red_std = 0.32, 0.5, 0.7, 0.05
+        lstm_mag, emb_std, proj_std, red_std = 0.16, 0.5, 0.7, 0.05   # 0.32 makes the 256-unit LSTMs chaotic
         glorot_gain, stop_bias, bias_std = 1.5, 13.0, 0.05
     else:
         raise ValueError("unknown weight set %r" % kind)
