@@ -133,6 +133,18 @@ PGEN_API int pgen_stage_download(pgen_t* h, int32_t* out_tokens, int32_t* out_le
 /* The handle's cudaStream_t (as void*), so that a harness can record CUDA events on it. */
 PGEN_API void* pgen_stream(pgen_t* h);
 
+/* Kernel-level entry: one attention pass (attention_decoder.py:79-129 -- energies with coverage,
+ * masked softmax, re-normalisation, context vector) over n_articles x beam_size decoder rows, using the
+ * handle's attention weights v / w_c.  ALL pointers are DEVICE memory on the handle's device:
+ *   enc_feat, enc_states [n_articles, max_enc_steps, 2H]   W_h.h_i and h_i
+ *   lens [n_articles] (int32)   dfeat [n_articles*beam_size, 2H] = W_s s_t + b_attn
+ *   cov [n_articles*beam_size, max_enc_steps] (ignored when coverage=0)
+ *   attn [n_articles*beam_size, max_enc_steps]   ctx [n_articles*beam_size, 2H]      (outputs)
+ * The energies scratch (one float per row and encoder position) is cudaMalloc'ed for the call.
+ * Synchronous: returns after the kernels have finished. */
+PGEN_API int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float* enc_states,
+                   const int32_t* lens, const float* dfeat, const float* cov, float* attn, float* ctx);
+
 /* Test hooks: copy a named device buffer of the last staged batch to the host.  Names:
  * "enc_states" [B,T,2H], "enc_feat" [B,T,2H], "dec_c0" / "dec_h0" [B,H], "trace_tokens" /
  * "trace_parents" [B,S,K] (int32), "trace_logp" [B,S,K].  Returns the element count in *n. */

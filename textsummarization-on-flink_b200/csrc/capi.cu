@@ -243,6 +243,16 @@ int pgen_decode_ids(pgen_t* h, int n_articles, const int32_t* enc_ids, const int
   return PGEN_OK;
 }
 
+int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float* enc_states, const int32_t* lens,
+                   const float* dfeat, const float* cov, float* attn, float* ctx) {
+  if (!h) return PGEN_ERR_ARG;
+  if (n_articles < 0 || (n_articles && (!enc_feat || !enc_states || !lens || !dfeat || !attn || !ctx)))
+    return fail(h, PGEN_ERR_ARG, "pgen_attention: NULL device pointer");
+  if (n_articles && h->hp.coverage && !cov) return fail(h, PGEN_ERR_ARG, "pgen_attention: coverage=1 needs cov");
+  std::string err = h->eng.attention_op(n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx);
+  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
+}
+
 int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n) {
   if (!h || !name || !out || !n) return PGEN_ERR_ARG;
   std::string err = h->eng.fetch(name, out, cap_bytes, n);

@@ -482,6 +482,28 @@ std::string Engine::download(int32_t* out_tokens, int32_t* out_lens, float* out_
   return "";
 }
 
+std::string Engine::attention_op(int n, const float* enc_feat, const float* enc_states, const int32_t* lens,
+                                 const float* dfeat, const float* cov, float* attn, float* ctx) {
+  if (n <= 0) return "";
+  CK(cudaSetDevice(device_));
+  const size_t rows = (size_t)n * d_.K;
+  float* e = nullptr;
+  int* act = nullptr;
+  CK(cudaMalloc((void**)&e, rows * d_.T * sizeof(float)));
+  if (cudaMalloc((void**)&act, (size_t)n * sizeof(int)) != cudaSuccess) { cudaFree(e); return "cudaMalloc failed"; }
+  std::vector<int> ones((size_t)n, 1);
+  cudaMemcpyAsync(act, ones.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, st_);
+  Dims d = d_;
+  d.SW = d.A;                      // ctx rows are dense [rows, A] here
+  stats.kernel_launches += launch_attn_energy(d, n, d.K, lens, act, enc_feat, dfeat, cov, w_.v, w_.w_c, e, st_);
+  stats.kernel_launches += launch_attn_context(d, n, d.K, lens, act, enc_states, e, attn, ctx, st_);
+  cudaError_t err = cudaStreamSynchronize(st_);
+  cudaFree(e);
+  cudaFree(act);
+  if (err != cudaSuccess) return std::string("pgen_attention: ") + cudaGetErrorString(err);
+  return check("pgen_attention");
+}
+
 std::string Engine::fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n) {
   if (!ran_) return "pgen_debug_fetch before pgen_stage_run";
   CK(cudaSetDevice(device_));

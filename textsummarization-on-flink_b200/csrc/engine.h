@@ -38,6 +38,10 @@ class Engine {
   std::string download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg);
   std::string fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n);
   std::string set_option(const std::string& kv);
+  std::string attention_op(int n, const float* enc_feat, const float* enc_states, const int32_t* lens,
+                           const float* dfeat, const float* cov, float* attn, float* ctx);
+  const DeviceWeights& weights() const { return w_; }
+  int device() const { return device_; }
   cudaStream_t stream() const { return st_; }
   int capacity() const { return Bcap_; }
   const Dims& dims() const { return d_; }

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libpgen_cuda.so")
 EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_stats", "pgen_last_error",
            "pgen_destroy", "pgen_flag_int", "pgen_text_encode", "pgen_text_summary", "pgen_decode_ids",
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
-           "pgen_debug_fetch", "pgen_set_option"]
+           "pgen_debug_fetch", "pgen_set_option", "pgen_attention"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -76,6 +76,7 @@ def lib() -> C.CDLL:
         L.pgen_stream.restype = C.c_void_p
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
+        L.pgen_attention.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
         _lib = L
     return _lib
 
@@ -211,6 +212,10 @@ class Decoder:
         self._ck(self._L.pgen_stage_download(self._h, _p(tok, C.c_int32), _p(ln, C.c_int32), _p(lp, C.c_float),
                                               _p(avg, C.c_double)))
         return tok, ln, lp, avg
+
+    def attention(self, n_articles: int, enc_feat, enc_states, lens, dfeat, cov, attn, ctx, fn: str = "pgen_attention"):
+        """Kernel-level attention pass on DEVICE pointers (ints, e.g. torch.Tensor.data_ptr())."""
+        self._ck(getattr(self._L, fn)(self._h, n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx))
 
     def stream_ptr(self) -> int:
         return int(self._L.pgen_stream(self._h) or 0)
