@@ -145,6 +145,23 @@ PGEN_API void* pgen_stream(pgen_t* h);
 PGEN_API int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float* enc_states,
                    const int32_t* lens, const float* dfeat, const float* cov, float* attn, float* ctx);
 
+/* No counterpart in the reference (it never touches device memory).  Same computation, arguments and
+ * results as pgen_attention, for callers that are not allowed to allocate device memory: an operator
+ * embedded in a process whose GPU memory belongs entirely to another allocator or to a fixed budget, or a
+ * service loop that cannot afford the device-wide stall and driver lock of cudaMalloc/cudaFree.  The
+ * energies scratch (plus one flag per article) lives in a fixed device array inside the library,
+ * PGEN_ATTENTION_STATIC_SCRATCH_BYTES large, which every GPU that loads the library holds until the
+ * process exits.  The call makes no cudaMalloc/cudaFree and calls no allocating library routine.
+ *   Limit: round_up(4*n_articles, 256) + 4*n_articles*beam_size*max_enc_steps bytes must fit in the array
+ *   (e.g. 163 articles at beam 4 x 400 positions); larger requests fail with PGEN_ERR_ARG.
+ *   Set-up: the first call on a device looks up the array's device address (once per device); make that
+ *   first call before starting any stream capture.
+ *   Sharing: all calls on a device use the same array, which keeps the previous call's contents (the
+ *   call rewrites what it needs); two calls whose GPU work overlaps in time race on it -- serialise them. */
+#define PGEN_ATTENTION_STATIC_SCRATCH_BYTES (1u << 20)
+PGEN_API int pgen_attention_static(pgen_t* h, int n_articles, const float* enc_feat, const float* enc_states,
+                          const int32_t* lens, const float* dfeat, const float* cov, float* attn, float* ctx);
+
 /* Test hooks: copy a named device buffer of the last staged batch to the host.  Names:
  * "enc_states" [B,T,2H], "enc_feat" [B,T,2H], "dec_c0" / "dec_h0" [B,H], "trace_tokens" /
  * "trace_parents" [B,S,K] (int32), "trace_logp" [B,S,K].  Returns the element count in *n. */

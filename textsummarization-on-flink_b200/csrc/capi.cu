@@ -9,6 +9,7 @@
 #include "../../include/pgen.h"
 #include "engine.h"
 #include "text.h"
+#include "handle_access.h"
 
 using namespace pgn;
 
@@ -79,6 +80,10 @@ static int run_pending(pgen_t* h, size_t n) {
   h->ms_host_text += ms_since(t0);
   return PGEN_OK;
 }
+
+pgn::Engine* pgen_internal_engine(pgen_t* h) { return &h->eng; }
+bool pgen_internal_coverage(pgen_t* h) { return h->hp.coverage; }
+int pgen_internal_fail(pgen_t* h, int code, const std::string& msg) { return fail(h, code, msg); }
 
 extern "C" {
 

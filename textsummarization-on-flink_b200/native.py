@@ -14,7 +14,8 @@ LIB_PATH = os.path.join(_HERE, "libpgen_cuda.so")
 EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_stats", "pgen_last_error",
            "pgen_destroy", "pgen_flag_int", "pgen_text_encode", "pgen_text_summary", "pgen_decode_ids",
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
-           "pgen_debug_fetch", "pgen_set_option", "pgen_attention"]
+           "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
+           "pgen_attention_static"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -77,6 +78,7 @@ def lib() -> C.CDLL:
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
         L.pgen_attention.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
+        L.pgen_attention_static.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
         _lib = L
     return _lib
 
