@@ -166,6 +166,10 @@ PGEN_API int pgen_attention_static(pgen_t* h, int n_articles, const float* enc_f
  * "enc_states" [B,T,2H], "enc_feat" [B,T,2H], "dec_c0" / "dec_h0" [B,H], "trace_tokens" /
  * "trace_parents" [B,S,K] (int32), "trace_logp" [B,S,K].  Returns the element count in *n. */
 PGEN_API int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n);
+/* Test hook: the vocabulary scores out . w + v (model.py:236) for `rows` decoder outputs, DEVICE pointers
+ * out_dev [rows, H] -> logits_dev [rows, V]; use_tc != 0 runs the tcgen05 tf32 kernel (scores carry tf32
+ * rounding), 0 the fp32 SIMT kernel. */
+PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* logits_dev, int use_tc);
 /* Test hook: choose kernel variants at run time (e.g. "vocab=simt", "vocab=tc", "profile=1"). */
 PGEN_API int pgen_set_option(pgen_t* h, const char* key_value);
 

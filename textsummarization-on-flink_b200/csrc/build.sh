@@ -6,7 +6,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden"
 OUT=../libpgen_cuda.so
 mkdir -p build
-for f in kernels.cu engine.cu capi.cu noalloc.cu; do
+for f in kernels.cu engine.cu capi.cu noalloc.cu vocab_tc.cu; do
   if [ ! -f build/${f%.cu}.o ] || [ $f -nt build/${f%.cu}.o ] || [ -n "$(find . ../../include -maxdepth 1 -name '*.h' -newer build/${f%.cu}.o)" ]; then
     $NVCC $FLAGS -c $f -o build/${f%.cu}.o &
   fi
@@ -15,5 +15,5 @@ if [ ! -f build/text.o ] || [ text.cc -nt build/text.o ] || [ text.h -nt build/t
   g++ -std=c++17 -O2 -fPIC -fvisibility=hidden -c text.cc -o build/text.o &
 fi
 wait
-$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $OUT build/kernels.o build/engine.o build/capi.o build/noalloc.o build/text.o -cudart static
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $OUT build/kernels.o build/engine.o build/capi.o build/noalloc.o build/vocab_tc.o build/text.o -cudart static
 echo built $OUT

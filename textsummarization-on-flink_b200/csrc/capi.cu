@@ -258,6 +258,12 @@ int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
 }
 
+int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* logits_dev, int use_tc) {
+  if (!h || !out_dev || !logits_dev) return PGEN_ERR_ARG;
+  std::string err = h->eng.vocab_logits_op(rows, out_dev, logits_dev, use_tc);
+  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
+}
+
 int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n) {
   if (!h || !name || !out || !n) return PGEN_ERR_ARG;
   std::string err = h->eng.fetch(name, out, cap_bytes, n);

@@ -225,6 +225,18 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   DALLOC(bb_.hist_tok, int, B * S * K); DALLOC(bb_.hist_par, int, B * S * K); DALLOC(bb_.hist_logp, float, B * S * K);
   DALLOC(bb_.steps_done, int, B); DALLOC(bb_.n_active, int, 1); DALLOC(bb_.best_kind, int, B); DALLOC(bb_.best_idx, int, B);
   DALLOC(out_tok_, int, B * S); DALLOC(out_len_, int, B); DALLOC(out_lp_, float, B * S); DALLOC(out_avg_, double, B);
+  {
+    cudaDeviceGetAttribute(&n_sms_, cudaDevAttrMultiProcessorCount, device_);
+    const size_t Rpad = (R + 127) / 128 * 128;
+    DALLOC(proj_wT_tf32_, float, V * H); DALLOC(out_tf32_, float, Rpad * H);
+    DALLOC(part_m_, float, (size_t)2 * n_sms_ * R); DALLOC(part_s_, float, (size_t)2 * n_sms_ * R);
+    DALLOC(cand_v_, float, (size_t)2 * n_sms_ * R * 16); DALLOC(cand_i_, int, (size_t)2 * n_sms_ * R * 16);
+    DALLOC(artl_, float, R * T);
+    launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
+    if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
+    else vtc_why_ = "vocabulary smaller than one 128-word tile";
+    vocab_tc_ = vtc_.ready;
+  }
 #undef DALLOC
   CK(cudaDeviceSynchronize());
   *code = PGEN_OK;
@@ -236,6 +248,15 @@ std::string Engine::set_option(const std::string& kv) {
   if (eq == std::string::npos) return "option must be key=value";
   const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
   if (k == "check_every") { check_every_ = std::max(1, atoi(v.c_str())); return ""; }
+  if (k == "vocab") {
+    if (v == "simt") { vocab_tc_ = false; return ""; }
+    if (v == "tc") {
+      if (!vtc_.ready) return "tensor-core vocabulary path unavailable: " + vtc_why_;
+      vocab_tc_ = true;
+      return "";
+    }
+    return "vocab must be simt or tc";
+  }
   if (k == "profile") {
     profile_ = atoi(v.c_str()) != 0;
     if (profile_ && pev_.empty()) {
@@ -371,16 +392,16 @@ void Engine::decoder() {
     GemmArgs g;
     // x = [emb(y); ctx] . Linear/Matrix + Bias                                  (attention_decoder.py:150)
     g = GemmArgs(); g.A0 = xin_; g.lda0 = E + A; g.k0 = E + A; g.B = w_.x_MT; g.ldb = E + A; g.bias = w_.x_b;
-    g.C = state_[n] + A + 2 * H; g.ldc = SW; g.M = R; g.N = E;
+    g.C = state_[n] + A + 2 * H; g.ldc = SW; g.M = R; g.N = E; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
     // LSTM cell                                                                   (:153)
     g = GemmArgs(); g.A0 = state_[n] + A + 2 * H; g.lda0 = SW; g.k0 = E; g.A1 = hprev_; g.lda1 = H; g.k1 = H;
-    g.B = w_.dec_kT; g.ldb = E + H; g.bias = w_.dec_b; g.C = z_; g.ldc = 4 * H; g.M = R; g.N = 4 * H;
+    g.B = w_.dec_kT; g.ldb = E + H; g.bias = w_.dec_b; g.C = z_; g.ldc = 4 * H; g.M = R; g.N = 4 * H; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
     nl += launch_lstm_pointwise(d_, R, z_, cprev_, state_[n], bb_.active, st_);
     // attention on the new state, coverage not updated                            (:156-158)
     g = GemmArgs(); g.A0 = state_[n] + A; g.lda0 = SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
-    g.C = dfeat_; g.ldc = A; g.M = R; g.N = A;
+    g.C = dfeat_; g.ldc = A; g.M = R; g.N = A; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
     if (profile_) cudaEventRecord(pev_[4 * s + 0], st_);
     nl += launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[n], w_.v, w_.w_c, e_, st_);
@@ -389,8 +410,25 @@ void Engine::decoder() {
     if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, st_);   // :166-167
     // output = [h; ctx] . AttnOutputProjection + b                                (:173)
     g = GemmArgs(); g.A0 = state_[n] + A + H; g.lda0 = SW; g.k0 = H; g.A1 = state_[n]; g.lda1 = SW; g.k1 = A;
-    g.B = w_.out_MT; g.ldb = H + A; g.bias = w_.out_b; g.C = out_; g.ldc = H; g.M = R; g.N = H;
+    g.B = w_.out_MT; g.ldb = H + A; g.bias = w_.out_b; g.C = out_; g.ldc = H; g.M = R; g.N = H; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
+    if (vocab_tc_) {
+      // vocabulary scores on the tensor cores, candidates + softmax statistics in the epilogue   (model.py:236-238)
+      int nmb, nr;
+      vtc_.plan(R, &nmb, &nr);
+      MergeArgs ma;
+      ma.out = out_; ma.wT = w_.proj_wT; ma.bias = w_.proj_v; ma.part_m = part_m_; ma.part_s = part_s_;
+      ma.cand_v = cand_v_; ma.cand_i = cand_i_; ma.artl = artl_; ma.pgen = pgen_; ma.attn = attn_[n]; ma.uniq_ids = uniq_;
+      ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active;
+      ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.K2MAX = vtc_.K2MAX; ma.H = H;
+      ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
+      if (profile_) cudaEventRecord(pev_[4 * s + 2], st_);
+      nl += launch_round_tf32(out_, out_tf32_, (size_t)R * H, st_);
+      nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, cand_v_, cand_i_, nullptr, st_);
+      if (profile_) cudaEventRecord(pev_[4 * s + 3], st_);
+      nl += vtc_.launch_rescore(ma, B, st_);                 // exact fp32 logits of the article's words
+      nl += vtc_.launch_merge(ma, B, st_);                   // exact re-scoring, copy mass, top-2K   (model.py:146-183, 284-285)
+    } else {
     // vocabulary scores                                                           (model.py:236)
     g = GemmArgs(); g.A0 = out_; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;
     g.C = logits_; g.ldc = d_.V; g.M = R; g.N = d_.V;
@@ -403,6 +441,7 @@ void Engine::decoder() {
     fa.uniq_ids = uniq_; fa.uniq_cnt = ucnt_; fa.pos_start = pstart_; fa.pos_list = plist_; fa.n_oov = noov_;
     fa.active = bb_.active; fa.topk_ids = topk_ids_; fa.topk_logp = topk_logp_;
     nl += launch_final_topk(d_, B, fa, st_);
+    }
     nl += launch_beam_step(d_, B, s, topk_ids_, topk_logp_, bb_, st_);
     ++steps;
     if (s + 1 < d_.S && s + 1 > d_.min_dec_steps && (s + 1) % check_every_ == 0) {
@@ -480,6 +519,24 @@ std::string Engine::download(int32_t* out_tokens, int32_t* out_lens, float* out_
   if (out_logp) memcpy(out_logp, h_out_lp_, n * S * 4);
   if (out_avg) memcpy(out_avg, h_out_avg_, n * 8);
   return "";
+}
+
+std::string Engine::vocab_logits_op(int rows, const float* out_dev, float* logits_dev, int use_tc) {
+  if (rows <= 0 || rows > R_) return "rows must be in 1..articles_per_batch*beam_size";
+  CK(cudaSetDevice(device_));
+  const int H = d_.H, V = d_.V;
+  if (use_tc) {
+    if (!vtc_.ready) return "tensor-core vocabulary path unavailable: " + vtc_why_;
+    launch_round_tf32(out_dev, out_tf32_, (size_t)rows * H, st_);
+    vtc_.launch(rows, w_.proj_v, part_m_, part_s_, cand_v_, cand_i_, logits_dev, st_);
+  } else {
+    GemmArgs g;
+    g.A0 = out_dev; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;
+    g.C = logits_dev; g.ldc = V; g.M = rows; g.N = V;
+    launch_gemm_nt(g, st_);
+  }
+  CK(cudaStreamSynchronize(st_));
+  return check("pgen_debug_vocab_logits");
 }
 
 std::string Engine::attention_op(int n, const float* enc_feat, const float* enc_states, const int32_t* lens,

@@ -9,6 +9,7 @@
 
 #include "kernels.h"
 #include "text.h"
+#include "vocab_tc.h"
 
 namespace pgn {
 
@@ -38,6 +39,7 @@ class Engine {
   std::string download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg);
   std::string fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n);
   std::string set_option(const std::string& kv);
+  std::string vocab_logits_op(int rows, const float* out_dev, float* logits_dev, int use_tc);
   std::string attention_op(int n, const float* enc_feat, const float* enc_states, const int32_t* lens,
                            const float* dfeat, const float* cov, float* attn, float* ctx);
   const DeviceWeights& weights() const { return w_; }
@@ -59,6 +61,13 @@ class Engine {
   bool staged_ = false, ran_ = false, synced_ = false;
   int check_every_ = 8;
   bool profile_ = false;
+  bool vocab_tc_ = false;          // tensor-core vocabulary path in use (falls back to the SIMT kernels when
+                                   // the dims are outside what vocab_tc.cu covers)
+  VocabTC vtc_;
+  std::string vtc_why_;
+  float *proj_wT_tf32_ = nullptr, *out_tf32_ = nullptr, *part_m_ = nullptr, *part_s_ = nullptr, *cand_v_ = nullptr, *artl_ = nullptr;
+  int* cand_i_ = nullptr;
+  int n_sms_ = 148;
   std::vector<cudaEvent_t> pev_;   // 4 events per step when profiling: attn begin, attn end/vocab begin... 
   int pev_used_ = 0;
   cudaStream_t st_ = nullptr;

@@ -94,8 +94,88 @@ gemm_nt_kernel(GemmArgs g) {
   }
 }
 
+// Skinny variant for the per-step decoder GEMMs (M = articles x beam, a few hundred rows): a 32 x 32 output
+// tile per CTA, the K loop split over KSPLIT groups of 64 threads that each own every KSPLIT-th k-tile, partial
+// sums combined through shared memory in group order (deterministic, independent of the batch).
+template <int KSPLIT>
+__global__ void __launch_bounds__(64 * KSPLIT)
+gemm_skinny_kernel(GemmArgs g) {
+  constexpr int BM = 32, BN = 32, LD = 36;
+  __shared__ __align__(16) float sm[KSPLIT * 2 * GBK * LD];
+  const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
+  float (*As)[LD] = reinterpret_cast<float (*)[LD]>(sm + grp * 2 * GBK * LD);
+  float (*Bs)[LD] = reinterpret_cast<float (*)[LD]>(sm + grp * 2 * GBK * LD + GBK * LD);
+  const int tx = t & 7, ty = t >> 3;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int Ktot = g.k0 + g.k1;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int kt = grp * GBK; kt < Ktot; kt += KSPLIT * GBK) {
+    const bool seg0 = kt < g.k0;
+#pragma unroll
+    for (int rep = 0; rep < 2; ++rep) {
+      const int idx = t + rep * 64, row = idx >> 2, k4 = (idx & 3) * 4;
+      const int m = m0 + row, n = n0 + row;
+      float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
+      if (m < g.M) {
+        const float* src;
+        if (seg0) {
+          const long long rr = g.gather0 ? (long long)g.gather0[m] : (long long)m;
+          src = g.A0 + rr * g.lda0 + kt + k4;
+        } else {
+          src = g.A1 + (long long)m * g.lda1 + (kt - g.k0) + k4;
+        }
+        va = *reinterpret_cast<const float4*>(src);
+      }
+      if (n < g.N) vb = *reinterpret_cast<const float4*>(g.B + (long long)n * g.ldb + kt + k4);
+      As[k4 + 0][row] = va.x; As[k4 + 1][row] = va.y; As[k4 + 2][row] = va.z; As[k4 + 3][row] = va.w;
+      Bs[k4 + 0][row] = vb.x; Bs[k4 + 1][row] = vb.y; Bs[k4 + 2][row] = vb.z; Bs[k4 + 3][row] = vb.w;
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(grp + 1));           // only this group's 64 threads
+#pragma unroll
+    for (int k = 0; k < GBK; ++k) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(grp + 1));
+  }
+  __syncthreads();
+  float* red = sm;                                               // [KSPLIT][32][32], aliases the tiles
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) red[grp * 1024 + (ty * 4 + i) * 32 + tx * 4 + j] = acc[i][j];
+  __syncthreads();
+  for (int o = tid; o < 1024; o += 64 * KSPLIT) {
+    const int m = m0 + (o >> 5), n = n0 + (o & 31);
+    if (m >= g.M || n >= g.N) continue;
+    float v = 0.f;
+#pragma unroll
+    for (int q = 0; q < KSPLIT; ++q) v += red[q * 1024 + o];
+    v += g.bias ? g.bias[n] : 0.f;
+    if (g.act == 1) v = fmaxf(v, 0.f);
+    g.C[(long long)m * g.ldc + n] = v;
+  }
+}
+static_assert(8 * 2 * GBK * 36 >= 8 * 1024, "reduction buffer must fit in the tile storage");
+
 int launch_gemm_nt(const GemmArgs& a, cudaStream_t st) {
   if (a.M <= 0 || a.N <= 0) return 0;
+  const int ktiles = (a.k0 + a.k1) / GBK;
+  if (a.skinny && ktiles >= 8) {
+    dim3 grid((a.N + 31) / 32, (a.M + 31) / 32);
+    if (a.N <= 512 && ktiles >= 16) gemm_skinny_kernel<8><<<grid, 512, 0, st>>>(a);
+    else gemm_skinny_kernel<4><<<grid, 256, 0, st>>>(a);
+    return 1;
+  }
   const long long work = (long long)a.M * a.N;
   if (work >= 128LL * 128 * 296) {
     dim3 grid((a.N + 127) / 128, (a.M + 127) / 128);

@@ -16,6 +16,8 @@ struct GemmArgs {
   float* C = nullptr; int ldc = 0;
   int M = 0, N = 0;
   int act = 0;            // 0 none, 1 relu
+  int skinny = 0;         // per-step decoder GEMM (few hundred rows): split-K tile kernel.  Chosen by the call
+                          // site, never by M, so that an article's rounding does not depend on the batch size
 };
 int launch_gemm_nt(const GemmArgs& a, cudaStream_t st);
 

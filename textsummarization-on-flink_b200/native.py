@@ -15,7 +15,7 @@ EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_st
            "pgen_destroy", "pgen_flag_int", "pgen_text_encode", "pgen_text_summary", "pgen_decode_ids",
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
            "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
-           "pgen_attention_static"]
+           "pgen_attention_static", "pgen_debug_vocab_logits"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -78,6 +78,7 @@ def lib() -> C.CDLL:
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
         L.pgen_attention.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
+        L.pgen_debug_vocab_logits.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.pgen_attention_static.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
         _lib = L
     return _lib
@@ -218,6 +219,9 @@ class Decoder:
     def attention(self, n_articles: int, enc_feat, enc_states, lens, dfeat, cov, attn, ctx, fn: str = "pgen_attention"):
         """Kernel-level attention pass on DEVICE pointers (ints, e.g. torch.Tensor.data_ptr())."""
         self._ck(getattr(self._L, fn)(self._h, n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx))
+
+    def vocab_logits(self, rows: int, out_ptr: int, logits_ptr: int, use_tc: bool):
+        self._ck(self._L.pgen_debug_vocab_logits(self._h, rows, out_ptr, logits_ptr, 1 if use_tc else 0))
 
     def stream_ptr(self) -> int:
         return int(self._L.pgen_stream(self._h) or 0)
