@@ -149,3 +149,36 @@ def test_rows_submit_poll_matches_oracle_rows(small_cfg, small_model_dir):
         ref = O.decode_row(small_cfg["W"], vocab, hps, b"uuid-%d" % i, arts[i], b"reference %d." % i, mode="dedup")
         assert (uuid, article, reference) == (ref[0], ref[1], ref[3])        # echoed unchanged
         assert summary == ref[2], "row %d" % i
+
+
+@pytest.mark.parametrize("encoder", ["persistent", "steps"])
+def test_full_size_encoder_states(model_dir, encoder):
+    """Config 2 of BASELINE.json (encoder only) at full size: the persistent cluster kernel (hidden 256) and the
+    per-time-step kernel against the oracle, ragged lengths included."""
+    from textsummarization_on_flink_b200 import weights_io
+    flags = synth.hyperparams_string(model_dir, max_dec_steps=1, min_dec_steps=0, extra="--articles_per_batch=16")
+    W = weights_io.load_weights(model_dir["weights"])
+    arts = synth.make_article_ids(9, seed=31) + synth.make_article_ids(2, seed=32, max_len=5)
+    arts.append((np.zeros(0, np.int32), np.zeros(0, np.int32), 0))
+    H = 256
+    with native.Decoder(flags) as dec:
+        dec.set_option("encoder=" + encoder)
+        ids, ext, lens, noov = native.pack_articles(arts, dec.max_enc_steps)
+        dec.stage_upload(ids, ext, lens, noov)
+        dec.stage_run()
+        dec.stage_sync()
+        n, T, A = len(arts), dec.max_enc_steps, 2 * H
+        es = dec.debug_fetch("enc_states", n * T * A).reshape(n, T, A)
+        ef = dec.debug_fetch("enc_feat", n * T * A).reshape(n, T, A)
+        c0 = dec.debug_fetch("dec_c0", n * H).reshape(n, H)
+        h0 = dec.debug_fetch("dec_h0", n * H).reshape(n, H)
+    for b, (a, _, _) in enumerate(arts):
+        L = len(a)
+        assert not es[b, L:].any()
+        if L == 0:
+            continue
+        enc, (rc, rh) = O.run_encoder(W, a)
+        np.testing.assert_allclose(es[b, :L], enc, atol=2e-5, rtol=1e-4)
+        np.testing.assert_allclose(ef[b, :L], O.encoder_features(W, enc[None])[0], atol=1e-4, rtol=1e-4)
+        np.testing.assert_allclose(c0[b], rc, atol=2e-5, rtol=1e-4)
+        np.testing.assert_allclose(h0[b], rh, atol=2e-5, rtol=1e-4)

@@ -248,6 +248,7 @@ std::string Engine::set_option(const std::string& kv) {
   if (eq == std::string::npos) return "option must be key=value";
   const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
   if (k == "check_every") { check_every_ = std::max(1, atoi(v.c_str())); return ""; }
+  if (k == "encoder") { enc_persistent_ = (v != "steps"); return ""; }
   if (k == "vocab") {
     if (v == "simt") { vocab_tc_ = false; return ""; }
     if (v == "tc") {
@@ -344,10 +345,16 @@ void Engine::encoder() {
     g.C = zx_ + (size_t)dir * B * T * 4 * H; g.ldc = 4 * H; g.M = B * T; g.N = 4 * H;
     nl += launch_gemm_nt(g, st_);
   }
-  for (int s = 0; s < max_len_; ++s)                   // model.py:90-93
-    nl += launch_enc_lstm_step(d_, B, s, lens_, zx_, w_.enc_kh[0], h_enc_[s & 1], h_enc_[(s + 1) & 1], c_enc_,
-                               enc_states_, st_);
-  const float* hfin = h_enc_[max_len_ & 1];
+  const float* hfin;
+  if (H == 256 && enc_persistent_) {                   // model.py:90-93, one launch
+    nl += launch_enc_lstm_persistent(d_, B, lens_, zx_, w_.enc_kh[0], h_enc_[1], c_enc_, enc_states_, st_);
+    hfin = h_enc_[1];
+  } else {
+    for (int s = 0; s < max_len_; ++s)                 // model.py:90-93, one launch per time step
+      nl += launch_enc_lstm_step(d_, B, s, lens_, zx_, w_.enc_kh[0], h_enc_[s & 1], h_enc_[(s + 1) & 1], c_enc_,
+                                 enc_states_, st_);
+    hfin = h_enc_[max_len_ & 1];
+  }
   {                                                    // model.py:117-120 -> row b*K of the "old" state
     GemmArgs g;
     g.A0 = c_enc_; g.lda0 = H; g.k0 = H; g.A1 = c_enc_ + (size_t)B * H; g.lda1 = H; g.k1 = H;

@@ -61,6 +61,7 @@ class Engine {
   bool staged_ = false, ran_ = false, synced_ = false;
   int check_every_ = 8;
   bool profile_ = false;
+  bool enc_persistent_ = true;
   bool vocab_tc_ = false;          // tensor-core vocabulary path in use (falls back to the SIMT kernels when
                                    // the dims are outside what vocab_tc.cu covers)
   VocabTC vtc_;

@@ -6,6 +6,8 @@
 // does not depend on what else shares the device batch.
 #include "kernels.h"
 
+#include <cooperative_groups.h>
+
 #include <cfloat>
 #include <cmath>
 
@@ -262,6 +264,119 @@ int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const flo
   dim3 grid(d.H / 32, 2, (B + ENC_AG - 1) / ENC_AG);
   const size_t smem = (size_t)(ENC_AG * d.H + ENC_AG * 4 * 32) * sizeof(float);
   enc_lstm_step_kernel<<<grid, 128, smem, st>>>(d.H, d.T, B, s, lens, zx, kh, h_prev, h_next, c_state, enc_states);
+  return 1;
+}
+
+// --------------------------------------------------------------------------------------
+// Persistent encoder recurrence for hidden_dim = 256 (model.py:90-93): one launch for all time steps.
+// A cluster of 8 CTAs owns one (direction, group of 8 articles); CTA c of the cluster holds the recurrent
+// weights of hidden units [32c, 32c+32) (4 gates x 32 = 128 columns, 128 KB fp32) in shared memory for the
+// whole sequence, computes their gates for the 8 articles, and pushes the 32 new h values into every CTA's
+// shared memory through DSMEM; one cluster barrier per time step.  c stays in registers.
+// --------------------------------------------------------------------------------------
+namespace cgx = cooperative_groups;
+constexpr int PE_H = 256, PE_AG = 8, PE_THREADS = 512;
+constexpr size_t PE_SMEM = (size_t)(PE_H * 128 + 2 * PE_H * PE_AG + 8 * PE_AG * 128) * sizeof(float);
+
+__global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(PE_THREADS, 1)
+enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const float* __restrict__ zx,
+                           const float* __restrict__ kh, float* __restrict__ h_fin, float* __restrict__ c_fin,
+                           float* __restrict__ enc_states) {
+  extern __shared__ __align__(16) float sm[];
+  float* Ws = sm;                                  // [256 k][128 local cols]
+  float* hs = Ws + PE_H * 128;                     // [2][256 k][8 articles]
+  float* red = hs + 2 * PE_H * PE_AG;              // [8 kq][8 articles][128 cols]
+  cgx::cluster_group cluster = cgx::this_cluster();
+  const int c = (int)cluster.block_rank();         // which 32 hidden units
+  const int dir = blockIdx.y, b0 = blockIdx.z * PE_AG;
+  const int tid = threadIdx.x;
+  constexpr int H4 = 4 * PE_H;
+
+  // recurrent weights of this CTA's 128 gate columns, and h(0) = 0
+  const float* khd = kh + (size_t)dir * PE_H * H4;
+  for (int i = tid; i < PE_H * 128; i += PE_THREADS) {
+    const int k = i >> 7, lc = i & 127, g = lc >> 5, ul = lc & 31;
+    Ws[i] = khd[(size_t)k * H4 + g * PE_H + 32 * c + ul];
+  }
+  for (int i = tid; i < 2 * PE_H * PE_AG; i += PE_THREADS) hs[i] = 0.f;
+  int grp_max = 0;
+  for (int a = 0; a < PE_AG; ++a) if (b0 + a < B) grp_max = max(grp_max, lens[b0 + a]);
+  // roles
+  const int kq = tid >> 6, cp = tid & 63;          // mat-vec: k range [32kq, 32kq+32), columns cp and cp+64
+  const int ful = tid & 31, fa = (tid >> 5) & 7;   // gate math (threads < 256): unit ful, article fa
+  const int fb = b0 + fa;
+  const int flen = (tid < 256 && fb < B) ? lens[fb] : 0;
+  float c_reg = 0.f, h_reg = 0.f;
+  cluster.sync();
+
+  for (int s = 0; s < grp_max; ++s) {
+    const int cur = s & 1;
+    // prefetch this step's input projection (x.Kx + b) for the gate-math threads
+    float zi = 0.f, zj = 0.f, zf = 0.f, zo = 0.f;
+    int t = -1;
+    if (tid < 256 && s < flen) {
+      t = dir == 0 ? s : flen - 1 - s;             // backward: reversed over the article's own length
+      const float* zp = zx + ((size_t)dir * B * T + (size_t)fb * T + t) * H4 + 32 * c + ful;
+      zi = __ldg(zp); zj = __ldg(zp + PE_H); zf = __ldg(zp + 2 * PE_H); zo = __ldg(zp + 3 * PE_H);
+    }
+    // partial h . Kh over this thread's k range
+    float acc0[PE_AG], acc1[PE_AG];
+#pragma unroll
+    for (int a = 0; a < PE_AG; ++a) { acc0[a] = 0.f; acc1[a] = 0.f; }
+    const float* hcur = hs + cur * PE_H * PE_AG;
+#pragma unroll 8
+    for (int kk = 0; kk < 32; ++kk) {
+      const int k = kq * 32 + kk;
+      const float w0 = Ws[k * 128 + cp], w1 = Ws[k * 128 + cp + 64];
+      const float4 ha = *reinterpret_cast<const float4*>(hcur + k * PE_AG);
+      const float4 hb = *reinterpret_cast<const float4*>(hcur + k * PE_AG + 4);
+      acc0[0] = fmaf(ha.x, w0, acc0[0]); acc0[1] = fmaf(ha.y, w0, acc0[1]); acc0[2] = fmaf(ha.z, w0, acc0[2]); acc0[3] = fmaf(ha.w, w0, acc0[3]);
+      acc0[4] = fmaf(hb.x, w0, acc0[4]); acc0[5] = fmaf(hb.y, w0, acc0[5]); acc0[6] = fmaf(hb.z, w0, acc0[6]); acc0[7] = fmaf(hb.w, w0, acc0[7]);
+      acc1[0] = fmaf(ha.x, w1, acc1[0]); acc1[1] = fmaf(ha.y, w1, acc1[1]); acc1[2] = fmaf(ha.z, w1, acc1[2]); acc1[3] = fmaf(ha.w, w1, acc1[3]);
+      acc1[4] = fmaf(hb.x, w1, acc1[4]); acc1[5] = fmaf(hb.y, w1, acc1[5]); acc1[6] = fmaf(hb.z, w1, acc1[6]); acc1[7] = fmaf(hb.w, w1, acc1[7]);
+    }
+#pragma unroll
+    for (int a = 0; a < PE_AG; ++a) {
+      red[(kq * PE_AG + a) * 128 + cp] = acc0[a];
+      red[(kq * PE_AG + a) * 128 + cp + 64] = acc1[a];
+    }
+    __syncthreads();
+    if (tid < 256) {
+      float hn = h_reg;
+      if (t >= 0) {
+        float gi = zi, gj = zj, gf = zf, go = zo;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {              // fixed order: deterministic
+          const float* r = red + (q * PE_AG + fa) * 128 + ful;
+          gi += r[0]; gj += r[32]; gf += r[64]; go += r[96];
+        }
+        c_reg = sigmoidf_(gf + 1.0f) * c_reg + sigmoidf_(gi) * tanhf(gj);   // LSTMCell, forget_bias 1
+        hn = sigmoidf_(go) * tanhf(c_reg);
+        h_reg = hn;
+        enc_states[((size_t)fb * T + t) * (2 * PE_H) + dir * PE_H + 32 * c + ful] = hn;   // model.py:93
+      }
+      // new h (or the frozen one past the article's end) into every CTA of the cluster
+      float* dst = hs + (cur ^ 1) * PE_H * PE_AG + (32 * c + ful) * PE_AG + fa;
+#pragma unroll
+      for (int rk = 0; rk < 8; ++rk) *cluster.map_shared_rank(dst, rk) = hn;
+    }
+    cluster.sync();                                // h(s+1) visible cluster-wide; also protects `red`
+  }
+  if (tid < 256 && fb < B) {
+    h_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = h_reg;
+    c_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = c_reg;
+  }
+}
+
+int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const float* kh,
+                               float* h_fin, float* c_fin, float* enc_states, cudaStream_t st) {
+  static bool set = false;
+  if (!set) {
+    cudaFuncSetAttribute(enc_lstm_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PE_SMEM);
+    set = true;
+  }
+  dim3 grid(8, 2, (B + PE_AG - 1) / PE_AG);
+  enc_lstm_persistent_kernel<<<grid, PE_THREADS, PE_SMEM, st>>>(d.T, B, lens, zx, kh, h_fin, c_fin, enc_states);
   return 1;
 }
 

@@ -37,6 +37,11 @@ int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const flo
                          const float* h_prev, float* h_next, float* c_state, float* enc_states,
                          cudaStream_t st);
 
+// The whole recurrence in one launch (hidden_dim == 256 only): clusters of 8 CTAs, recurrent weights resident in
+// shared memory, h exchanged through DSMEM.  Writes the final (h, c) of both directions to h_fin / c_fin [2][B][H].
+int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const float* kh,
+                               float* h_fin, float* c_fin, float* enc_states, cudaStream_t st);
+
 // ---- decoder step ----
 struct StepBufs {
   const int* lens; const int* n_oov;
