@@ -426,7 +426,7 @@ void Engine::decoder() {
       MergeArgs ma;
       ma.out = out_; ma.wT = w_.proj_wT; ma.bias = w_.proj_v; ma.part_m = part_m_; ma.part_s = part_s_;
       ma.cand_v = cand_v_; ma.cand_i = cand_i_; ma.artl = artl_; ma.pgen = pgen_; ma.attn = attn_[n]; ma.uniq_ids = uniq_;
-      ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active;
+      ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active; ma.lens = lens_;
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.K2MAX = vtc_.K2MAX; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
       if (profile_) cudaEventRecord(pev_[4 * s + 2], st_);

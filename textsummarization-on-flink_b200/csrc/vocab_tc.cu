@@ -26,7 +26,7 @@ namespace pgn {
 namespace {
 
 constexpr int BM = 128, BN = 128, BK = 32;          // tile: 128 rows x 128 words x 32 tf32 (= 128 bytes of K)
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int TILE_BYTES = 128 * 128;                // one [128 x 128B] operand tile
 constexpr int NTHREADS = 320;                        // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
 constexpr int EPI_THREADS = 256;
@@ -138,6 +138,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* t_empty = t_full + 2;        // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
   float* bias_s = reinterpret_cast<float*>(bars + 16);           // [8 epilogue warps][64], 16-byte aligned
+  float* xstage = bias_s + 8 * 64;                               // [8 epilogue warps][32 words][32 lanes]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mb = blockIdx.x % n_mblocks, range = blockIdx.x / n_mblocks;
@@ -220,23 +221,21 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_wait(&t_full[acc], (tcount >> 1) & 1);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * 64);
-      uint32_t raw0[32], raw1[32];
-      tmem_ld32(tbase, raw0);
-      tmem_ld_wait();
-      tmem_ld32(tbase + 32, raw1);                             // in flight while chunk 0 is processed
-#pragma unroll
+#pragma unroll 1
       for (int c = 0; c < 2; ++c) {
-        if (c == 1) tmem_ld_wait();
+        uint32_t raw[32];
+        tmem_ld32(tbase + c * 32, raw);
+        tmem_ld_wait();
         const int n0 = nb + c * 32;
         float x[32];
         float c0 = -FLT_MAX, c1 = -FLT_MAX, c2 = -FLT_MAX, c3 = -FLT_MAX;
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const float4 b4 = *reinterpret_cast<const float4*>(bsm + c * 32 + j);
-          x[j + 0] = fmaf(__uint_as_float(c == 0 ? raw0[j + 0] : raw1[j + 0]), kLog2e, b4.x);
-          x[j + 1] = fmaf(__uint_as_float(c == 0 ? raw0[j + 1] : raw1[j + 1]), kLog2e, b4.y);
-          x[j + 2] = fmaf(__uint_as_float(c == 0 ? raw0[j + 2] : raw1[j + 2]), kLog2e, b4.z);
-          x[j + 3] = fmaf(__uint_as_float(c == 0 ? raw0[j + 3] : raw1[j + 3]), kLog2e, b4.w);
+          x[j + 0] = fmaf(__uint_as_float(raw[j + 0]), kLog2e, b4.x);
+          x[j + 1] = fmaf(__uint_as_float(raw[j + 1]), kLog2e, b4.y);
+          x[j + 2] = fmaf(__uint_as_float(raw[j + 2]), kLog2e, b4.z);
+          x[j + 3] = fmaf(__uint_as_float(raw[j + 3]), kLog2e, b4.w);
           if (n0 + j + 3 >= V) {                               // only the last tile
             if (n0 + j + 0 >= V) x[j + 0] = -FLT_MAX;
             if (n0 + j + 1 >= V) x[j + 1] = -FLT_MAX;
@@ -261,9 +260,24 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           s0 += exp2f(x[j + 0] - m_run); s1 += exp2f(x[j + 1] - m_run);
           s2 += exp2f(x[j + 2] - m_run); s3 += exp2f(x[j + 3] - m_run);
         }
-        if (cm > cv[K2MAX - 1]) {                              // rare once the list has warmed up
+        // Candidates.  Lanes are different rows, so "does this word enter my list" is divergent; to keep the
+        // warp's trip count at max-over-lanes (not the union of positions) each lane first builds a bit mask of
+        // the words above its threshold, then walks its own set bits.
+        float thr = cv[K2MAX - 1];
+        if (cm > thr) {
+          float* xs = xstage + ew * 1024;
+          unsigned pass = 0u;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) cand_insert<K2MAX>(cv, ci, x[j], n0 + j);
+          for (int j = 0; j < 32; ++j) {
+            xs[j * 32 + lane] = x[j];
+            pass |= (x[j] > thr) ? (1u << j) : 0u;
+          }
+          while (pass) {
+            const int j = __ffs(pass) - 1;
+            pass &= pass - 1;
+            const float v = xs[j * 32 + lane];
+            cand_insert<K2MAX>(cv, ci, v, n0 + j);
+          }
         }
       }
       tc_fence_before();
@@ -350,6 +364,7 @@ vocab_rescore_kernel(MergeArgs a) {
 }
 
 constexpr int MERGE_THREADS = 512;
+constexpr int MERGE_PPL = 10;       // candidate lists ("parts") per lane in the tournament: up to 320 parts
 
 template <int K2MAX>
 __global__ void __launch_bounds__(MERGE_THREADS)
@@ -365,22 +380,43 @@ vocab_merge_kernel(MergeArgs a) {
   float* outs = sm;                                             // [K][H]
   float* Ms = outs + K * H;                                     // [K]   max, log2 domain
   float* Ss = Ms + K;                                           // [K]   sum of exp(l - M)
-  float* apv = Ss + K;                                          // [K][nc] approx logits (log2 domain)
+  float* apv = Ss + K;                                          // [K][nc] approx logits (log2 domain), per part descending
   int* api = reinterpret_cast<int*>(apv + (size_t)K * nc);      // [K][nc]
   int* sel_i = api + (size_t)K * nc;                            // [K][C]
   float* sel_a = reinterpret_cast<float*>(sel_i + K * C);       // [K][C] approx logit (log2 domain)
   float* sel_x = sel_a + K * C;                                 // [K][C] exact logit
   float* finv = sel_x + K * C;                                  // [K][C + T]
   int* fini = reinterpret_cast<int*>(finv + (size_t)K * (C + T));   // [K][C + T]
+  float* att = reinterpret_cast<float*>(fini + (size_t)K * (C + T));   // [K][T]  attention of the K rows
+  float* arl = att + (size_t)K * T;                             // [K][T]  exact logits of the article's words
+  int* pss = reinterpret_cast<int*>(arl + (size_t)K * T);       // [T + 1] pos_start
+  int* pls = pss + (T + 1);                                     // [T]     pos_list
+  int* uids = pls + T;                                          // [T]     uniq_ids
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r0 = art * K;
+  const int len = a.lens[art];
 
+  // ---- A: stage everything this article needs in shared memory
   for (int i = threadIdx.x; i < K * H; i += MERGE_THREADS) outs[i] = a.out[(size_t)r0 * H + i];
+#pragma unroll 4
   for (int i = threadIdx.x; i < K * nc; i += MERGE_THREADS) {
     const int k = i / nc, c = i - k * nc, pt = c / K2MAX, j = c - pt * K2MAX;
     const size_t pi = ((size_t)pt * R + r0 + k) * K2MAX + j;
     apv[i] = a.cand_v[pi];
     api[i] = a.cand_i[pi];
+  }
+  if (nu > 0) {
+    for (int i = threadIdx.x; i < K * len; i += MERGE_THREADS) {
+      const int k = i / len, t = i - k * len;
+      att[k * T + t] = a.attn[(size_t)(r0 + k) * T + t];
+    }
+    for (int i = threadIdx.x; i < K * nu; i += MERGE_THREADS) {
+      const int k = i / nu, u = i - k * nu;
+      arl[k * T + u] = a.artl[(size_t)(r0 + k) * T + u];
+    }
+    for (int i = threadIdx.x; i <= nu; i += MERGE_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
+    for (int i = threadIdx.x; i < len; i += MERGE_THREADS) pls[i] = a.pos_list[(size_t)art * T + i];
+    for (int i = threadIdx.x; i < nu; i += MERGE_THREADS) uids[i] = a.uniq_ids[(size_t)art * T + i];
   }
   for (int k = warp; k < K; k += NW) {                          // combine the per-part (max, sum exp2)
     float M = -FLT_MAX;
@@ -395,31 +431,47 @@ vocab_merge_kernel(MergeArgs a) {
     if (lane == 0) { Ms[k] = M; Ss[k] = S; }
   }
   __syncthreads();
-  // top-C approx candidates per row (warp per row, C rounds of arg-best with removal)
+  // ---- B: top-C approx candidates per row: every part's list is already sorted, so a C-round tournament over
+  // the list heads suffices (warp per row; lane owns parts lane, lane+32, ...)
   for (int k = warp; k < K; k += NW) {
+    float hv[MERGE_PPL]; int hi[MERGE_PPL], hp[MERGE_PPL];
+#pragma unroll
+    for (int q = 0; q < MERGE_PPL; ++q) {
+      const int pt = lane + 32 * q;
+      hp[q] = 0;
+      hi[q] = pt < NP ? api[k * nc + pt * K2MAX] : -1;
+      hv[q] = pt < NP ? apv[k * nc + pt * K2MAX] : -FLT_MAX;
+    }
     for (int round = 0; round < C; ++round) {
-      float bv = -FLT_MAX; int bi = 0x7fffffff, bp = -1;
-      for (int c = lane; c < nc; c += 32) {
-        const int id = api[k * nc + c];
-        if (id >= 0 && better_vi(apv[k * nc + c], id, bv, bi)) { bv = apv[k * nc + c]; bi = id; bp = c; }
-      }
+      float bv = -FLT_MAX; int bi = 0x7fffffff, bq = -1;
+#pragma unroll
+      for (int q = 0; q < MERGE_PPL; ++q)
+        if (hi[q] >= 0 && better_vi(hv[q], hi[q], bv, bi)) { bv = hv[q]; bi = hi[q]; bq = q; }
+      int bl = lane;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
         const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        const int op = __shfl_xor_sync(0xffffffffu, bp, o);
-        if (better_vi(ov, oi, bv, bi)) { bv = ov; bi = oi; bp = op; }
+        const int ol = __shfl_xor_sync(0xffffffffu, bl, o);
+        if (better_vi(ov, oi, bv, bi)) { bv = ov; bi = oi; bl = ol; }
       }
-      if (lane == 0) {
-        sel_i[k * C + round] = bp >= 0 ? bi : -1;
-        sel_a[k * C + round] = bv;
-        if (bp >= 0) api[k * nc + bp] = -1;
+      const bool found = bi != 0x7fffffff;
+      if (lane == 0) { sel_i[k * C + round] = found ? bi : -1; sel_a[k * C + round] = bv; }
+      if (found && lane == bl) {                                // the winning lane advances that list's head
+#pragma unroll
+        for (int q = 0; q < MERGE_PPL; ++q) {
+          if (q == bq) {
+            const int pt = lane + 32 * q;
+            ++hp[q];
+            if (hp[q] < K2MAX) { hi[q] = api[k * nc + pt * K2MAX + hp[q]]; hv[q] = apv[k * nc + pt * K2MAX + hp[q]]; }
+            else hi[q] = -1;
+          }
+        }
       }
-      __syncwarp();
     }
   }
   __syncthreads();
-  // exact fp32 logits of the K*C (row, candidate) pairs
+  // ---- C: exact fp32 logits of the K*C (row, candidate) pairs (warp per pair)
   for (int it = warp; it < K * C; it += NW) {
     const int k = it / C, id = sel_i[it];
     float acc = 0.f;
@@ -436,7 +488,7 @@ vocab_merge_kernel(MergeArgs a) {
     if (lane == 0) sel_x[it] = id >= 0 ? acc + a.bias[id] : -FLT_MAX;
   }
   __syncthreads();
-  // exact values replace the tensor-core ones inside the sum of exponentials; M stays the tf32 maximum
+  // ---- D: exact values replace the tensor-core ones inside the sum of exponentials; M stays the tf32 maximum
   if (threadIdx.x < K) {
     const int k = threadIdx.x;
     float S = Ss[k];
@@ -446,7 +498,7 @@ vocab_merge_kernel(MergeArgs a) {
     Ss[k] = S;
   }
   __syncthreads();
-  // final distribution on the candidate set (model.py:158-181)
+  // ---- E: final distribution on the candidate set (model.py:158-181)
   const int nf = C + nu;
   for (int i = threadIdx.x; i < K * nf; i += MERGE_THREADS) {
     const int k = i / nf, c = i - k * nf;
@@ -457,28 +509,25 @@ vocab_merge_kernel(MergeArgs a) {
     if (c < C) {
       id = sel_i[k * C + c];
       if (id >= 0) {
-        int lo = 0, hi = nu;                                    // article words are handled below with their copy mass
-        const int* uid = a.uniq_ids + (size_t)art * T;
-        while (lo < hi) { const int mid = (lo + hi) >> 1; if (uid[mid] < id) lo = mid + 1; else hi = mid; }
-        if (lo < nu && uid[lo] == id) id = -1;
+        int lo = 0, hi2 = nu;                                   // article words are handled below with their copy mass
+        while (lo < hi2) { const int mid = (lo + hi2) >> 1; if (uids[mid] < id) lo = mid + 1; else hi2 = mid; }
+        if (lo < nu && uids[lo] == id) id = -1;
         else val = a.pointer_gen ? pg * (expf(sel_x[k * C + c] - M) / S) : expf(sel_x[k * C + c] - M) / S;
       }
     } else {
       const int u = c - C;
-      id = a.uniq_ids[(size_t)art * T + u];
-      const int* ps = a.pos_start + (size_t)art * (T + 1);
-      const int* pl = a.pos_list + (size_t)art * T;
-      const float* at = a.attn + (size_t)r * T;
+      id = uids[u];
       const float omp = 1.0f - pg;
       float copy = 0.f;
-      for (int qq = ps[u]; qq < ps[u + 1]; ++qq) copy += omp * at[pl[qq]];   // scatter_nd: duplicates accumulate in t order
-      const float vocab = id < V ? pg * (expf(a.artl[(size_t)r * T + u] - M) / S) : 0.f;
+      for (int qq = pss[u]; qq < pss[u + 1]; ++qq) copy += omp * att[k * T + pls[qq]];   // scatter_nd: duplicates accumulate in t order
+      const float vocab = id < V ? pg * (expf(arl[k * T + u] - M) / S) : 0.f;
       val = vocab + copy;
     }
     finv[i] = val; fini[i] = id;
   }
   __syncthreads();
-  for (int k = warp; k < K; k += NW) {                          // top-2K with the tf.nn.top_k tie rule
+  // ---- F: top-2K with the tf.nn.top_k tie rule (warp per row)
+  for (int k = warp; k < K; k += NW) {
     const int r = r0 + k;
     for (int round = 0; round < K2; ++round) {
       float bv = -FLT_MAX; int bi = 0x7fffffff, bp = -1;
@@ -521,7 +570,7 @@ std::string make_map(EncodeTiledFn fn, CUtensorMap* map, const float* base, int 
 
 }  // namespace
 
-size_t VocabTC::smem_bytes() const { return (size_t)(KB + STAGES) * TILE_BYTES + 1024 + 256 + 8 * 64 * 4; }
+size_t VocabTC::smem_bytes() const { return (size_t)(KB + STAGES) * TILE_BYTES + 1024 + 256 + 8 * 64 * 4 + 8 * 1024 * 4; }
 
 std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out_tf32, int Rcap, int K2_, int n_sms) {
   V = V_; H = H_; K2 = K2_;
@@ -573,7 +622,8 @@ size_t VocabTC::merge_smem(int K, int T, int n_parts) const {
   const int nc = n_parts * K2MAX;
   int C = K2 + MERGE_EXTRA;
   if (C > nc) C = nc;
-  size_t fl = (size_t)K * H + 2 * K + 2 * (size_t)K * nc + 3 * (size_t)K * C + 2 * (size_t)K * (C + T);
+  size_t fl = (size_t)K * H + 2 * K + 2 * (size_t)K * nc + 3 * (size_t)K * C + 2 * (size_t)K * (C + T) +
+              2 * (size_t)K * T + 3 * (size_t)T + 1;
   return fl * 4 + 64;
 }
 

@@ -17,7 +17,7 @@ struct MergeArgs {
   float* artl;                                   // [R, T] exact logits of the article's distinct words
   const float* pgen; const float* attn;          // [R], [R, T]
   const int* uniq_ids; const int* uniq_cnt; const int* pos_start; const int* pos_list;
-  const int* active;
+  const int* active; const int* lens;
   int* topk_ids; float* topk_logp;               // [R, 2K]
   int K, K2, K2MAX, H, V, T, R, n_parts, pointer_gen;
 };
