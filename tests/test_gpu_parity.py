@@ -140,7 +140,8 @@ def test_rows_submit_poll_matches_oracle_rows(small_cfg, small_model_dir):
         for i, a in enumerate(arts):
             dec.submit(b"uuid-%d" % i, a, b"reference %d." % i)
             got += dec.poll()
-        assert len(got) == (len(arts) // 4) * 4                              # only full batches so far
+        # decoding is asynchronous: poll() hands back only batches that have finished, never a partial one
+        assert len(got) % 4 == 0 and len(got) <= (len(arts) // 4) * 4
         got += dec.poll(flush=True)
         st = dec.stats()
     assert st["rows_in"] == st["rows_out"] == len(arts)

@@ -29,10 +29,17 @@ double ms_since(std::chrono::steady_clock::time_point t0) {
 }
 }  // namespace
 
+struct InFlight { int slot; std::vector<PendingRow> rows; };
+
 struct pgen {
   HyperParams hp;
   Vocab vocab;
-  Engine eng;
+  // One engine (weights replica + batch slot + stream) per slot: batch i+1 is tokenised, uploaded and
+  // launched while batch i is still decoding, and their kernels overlap on the GPU.
+  std::vector<std::unique_ptr<Engine>> engs;
+  std::deque<InFlight> inflight;     // launched batches, oldest first (= submission order)
+  int next_slot = 0, stage_slot = 0;
+  Engine& eng() { return *engs[stage_slot]; }
   std::string err;
   std::deque<PendingRow> pending;
   std::deque<DoneRow> done;
@@ -49,39 +56,64 @@ static int fail(pgen_t* h, int code, const std::string& msg) {
   return code;
 }
 
-// decode the first n pending rows as one device batch and move them to `done`
-static int run_pending(pgen_t* h, size_t n) {
-  const int T = (int)h->hp.max_enc_steps, S = (int)h->hp.max_dec_steps;
-  h->b_ids.assign(n * T, 0); h->b_ext.assign(n * T, 0); h->b_lens.assign(n, 0); h->b_noov.assign(n, 0);
-  for (size_t b = 0; b < n; ++b) {
-    const EncodedArticle& e = h->pending[b].enc;
-    h->b_lens[b] = (int)e.enc_ids.size();
-    h->b_noov[b] = (int)e.oovs.size();
-    memcpy(&h->b_ids[b * T], e.enc_ids.data(), e.enc_ids.size() * 4);
-    memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
-  }
+// finish the oldest in-flight batch: wait for it, detokenise, move its rows to `done`
+static int collect_oldest(pgen_t* h) {
+  InFlight f = std::move(h->inflight.front());
+  h->inflight.pop_front();
+  Engine& e = *h->engs[f.slot];
+  const size_t n = f.rows.size();
+  const int S = (int)h->hp.max_dec_steps;
   h->b_tok.resize(n * S); h->b_len.resize(n); h->b_lp.resize(n * S); h->b_avg.resize(n);
-  std::string err = h->eng.upload((int)n, h->b_ids.data(), h->b_ext.data(), T, h->b_lens.data(), h->b_noov.data());
-  if (err.empty()) err = h->eng.run();
-  if (err.empty()) err = h->eng.sync();
-  if (err.empty()) err = h->eng.download(h->b_tok.data(), h->b_len.data(), h->b_lp.data(), h->b_avg.data());
+  std::string err = e.download(h->b_tok.data(), h->b_len.data(), h->b_lp.data(), h->b_avg.data());
   if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);
   auto t0 = std::chrono::steady_clock::now();
   for (size_t b = 0; b < n; ++b) {
-    PendingRow& p = h->pending.front();
+    PendingRow& p = f.rows[b];
     DoneRow d;
     if (!summary_from_ids(h->vocab, p.enc.oovs, &h->b_tok[b * S], h->b_len[b], &d.summary))
       return fail(h, PGEN_ERR_STATE, "decoder produced a token id outside the article's extended vocabulary");
     h->tokens_out += h->b_len[b];
     d.uuid = std::move(p.uuid); d.article = std::move(p.article); d.reference = std::move(p.reference);
     h->done.push_back(std::move(d));
-    h->pending.pop_front();
   }
   h->ms_host_text += ms_since(t0);
   return PGEN_OK;
 }
 
-pgn::Engine* pgen_internal_engine(pgen_t* h) { return &h->eng; }
+// launch the first n pending rows as one device batch on the next slot (asynchronous)
+static int launch_pending(pgen_t* h, size_t n) {
+  const int slot = h->next_slot;
+  while (!h->inflight.empty()) {                   // the slot must be free; batches complete in FIFO order
+    bool busy = false;
+    for (auto& f : h->inflight) busy |= (f.slot == slot);
+    if (!busy) break;
+    int rc = collect_oldest(h);
+    if (rc != PGEN_OK) return rc;
+  }
+  const int T = (int)h->hp.max_enc_steps;
+  h->b_ids.assign(n * T, 0); h->b_ext.assign(n * T, 0); h->b_lens.assign(n, 0); h->b_noov.assign(n, 0);
+  InFlight f;
+  f.slot = slot;
+  f.rows.reserve(n);
+  for (size_t b = 0; b < n; ++b) {
+    const EncodedArticle& e = h->pending.front().enc;
+    h->b_lens[b] = (int)e.enc_ids.size();
+    h->b_noov[b] = (int)e.oovs.size();
+    memcpy(&h->b_ids[b * T], e.enc_ids.data(), e.enc_ids.size() * 4);
+    memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
+    f.rows.push_back(std::move(h->pending.front()));
+    h->pending.pop_front();
+  }
+  Engine& e = *h->engs[slot];
+  std::string err = e.upload((int)n, h->b_ids.data(), h->b_ext.data(), T, h->b_lens.data(), h->b_noov.data());
+  if (err.empty()) err = e.run();
+  if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);
+  h->inflight.push_back(std::move(f));
+  h->next_slot = (slot + 1) % (int)h->engs.size();
+  return PGEN_OK;
+}
+
+pgn::Engine* pgen_internal_engine(pgen_t* h) { return &h->eng(); }
 bool pgen_internal_coverage(pgen_t* h) { return h->hp.coverage; }
 int pgen_internal_fail(pgen_t* h, int code, const std::string& msg) { return fail(h, code, msg); }
 
@@ -102,9 +134,13 @@ int pgen_create(const char* hyperparams, int device_ordinal, pgen_t** out) {
   }
   err = h->vocab.load(hp.vocab_path, hp.vocab_size);                                          // :307
   if (!err.empty()) return fail(nullptr, PGEN_ERR_IO, err);
-  int code = PGEN_OK;
-  err = h->eng.init(hp, h->vocab.size(), device_ordinal, &code);
-  if (!err.empty()) return fail(nullptr, code, err);
+  if (hp.slots < 1 || hp.slots > 8) return fail(nullptr, PGEN_ERR_ARG, "slots must be in 1..8");
+  for (int64_t i = 0; i < hp.slots; ++i) {
+    int code = PGEN_OK;
+    h->engs.emplace_back(new Engine());
+    err = h->engs.back()->init(hp, h->vocab.size(), device_ordinal, &code);
+    if (!err.empty()) return fail(nullptr, code, err);
+  }
   *out = h.release();
   return PGEN_OK;
 }
@@ -131,7 +167,7 @@ int pgen_submit(pgen_t* h, const char* uuid, size_t uuid_len, const char* articl
   ++h->rows_in;
   h->pending.push_back(std::move(p));
   h->ms_host_text += ms_since(t0);
-  if ((int64_t)h->pending.size() >= h->hp.articles_per_batch) return run_pending(h, (size_t)h->hp.articles_per_batch);
+  if ((int64_t)h->pending.size() >= h->hp.articles_per_batch) return launch_pending(h, (size_t)h->hp.articles_per_batch);
   return PGEN_OK;
 }
 
@@ -143,10 +179,15 @@ int pgen_poll(pgen_t* h, int flush, pgen_rows_t* out) {
     if (flush || late) {
       while (!h->pending.empty()) {
         const size_t n = std::min<size_t>(h->pending.size(), (size_t)h->hp.articles_per_batch);
-        int rc = run_pending(h, n);
+        int rc = launch_pending(h, n);
         if (rc != PGEN_OK) return rc;
       }
     }
+  }
+  // finished batches, oldest first; with flush wait for everything in flight
+  while (!h->inflight.empty() && (flush || h->engs[h->inflight.front().slot]->done())) {
+    int rc = collect_oldest(h);
+    if (rc != PGEN_OK) return rc;
   }
   if (h->done.empty()) return PGEN_OK;
   auto* own = new RowsOwner();
@@ -172,13 +213,19 @@ void pgen_rows_free(pgen_rows_t* rows) {
 int pgen_stats(pgen_t* h, pgen_stats_t* out) {
   if (!h || !out) return PGEN_ERR_ARG;
   memset(out, 0, sizeof *out);
-  const EngineStats& s = h->eng.stats;
+  EngineStats s;
+  for (auto& e : h->engs) {
+    const EngineStats& x = e->stats;
+    s.batches += x.batches; s.decode_steps += x.decode_steps; s.article_steps += x.article_steps;
+    s.early_stops += x.early_stops; s.kernel_launches += x.kernel_launches;
+  }
+  const EngineStats& last = h->eng().stats;          // timings: the slot the stage API addresses
   out->rows_in = h->rows_in; out->rows_out = h->rows_out; out->batches = s.batches;
   out->tokens_in = h->tokens_in; out->tokens_out = h->tokens_out; out->decode_steps = s.decode_steps;
   out->article_steps = s.article_steps; out->early_stops = s.early_stops; out->kernel_launches = s.kernel_launches;
-  out->ms_host_text = h->ms_host_text; out->ms_h2d = s.ms_h2d; out->ms_encoder = s.ms_encoder;
-  out->ms_decoder = s.ms_decoder; out->ms_d2h = s.ms_d2h;
-  out->ms_attention = s.ms_attention; out->ms_vocab = s.ms_vocab; out->prof_steps = (double)s.prof_steps;
+  out->ms_host_text = h->ms_host_text; out->ms_h2d = last.ms_h2d; out->ms_encoder = last.ms_encoder;
+  out->ms_decoder = last.ms_decoder; out->ms_d2h = last.ms_d2h;
+  out->ms_attention = last.ms_attention; out->ms_vocab = last.ms_vocab; out->prof_steps = (double)last.prof_steps;
   return PGEN_OK;
 }
 
@@ -208,32 +255,39 @@ int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out,
 int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
                       const int32_t* enc_lens, const int32_t* n_oovs) {
   if (!h || n_articles < 0 || (n_articles && (!enc_ids || !enc_ext_ids || !enc_lens))) return h ? fail(h, PGEN_ERR_ARG, "bad arguments") : PGEN_ERR_ARG;
-  std::string err = h->eng.upload(n_articles, enc_ids, enc_ext_ids, ld, enc_lens, n_oovs);
+  std::string err = h->eng().upload(n_articles, enc_ids, enc_ext_ids, ld, enc_lens, n_oovs);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
 }
 int pgen_stage_run(pgen_t* h) {
   if (!h) return PGEN_ERR_ARG;
-  std::string err = h->eng.run();
+  std::string err = h->eng().run();
   return err.empty() ? PGEN_OK : fail(h, err.find("before") != std::string::npos ? PGEN_ERR_STATE : PGEN_ERR_CUDA, err);
 }
 int pgen_stage_sync(pgen_t* h) {
   if (!h) return PGEN_ERR_ARG;
-  std::string err = h->eng.sync();
+  std::string err = h->eng().sync();
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
 }
 int pgen_stage_download(pgen_t* h, int32_t* out_tokens, int32_t* out_lens, float* out_logprobs, double* out_avg) {
   if (!h) return PGEN_ERR_ARG;
-  std::string err = h->eng.download(out_tokens, out_lens, out_logprobs, out_avg);
+  std::string err = h->eng().download(out_tokens, out_lens, out_logprobs, out_avg);
   return err.empty() ? PGEN_OK : fail(h, err.find("before") != std::string::npos ? PGEN_ERR_STATE : PGEN_ERR_CUDA, err);
 }
-void* pgen_stream(pgen_t* h) { return h ? (void*)h->eng.stream() : nullptr; }
+void* pgen_stream(pgen_t* h) { return h ? (void*)h->eng().stream() : nullptr; }
+
+int pgen_stage_slot(pgen_t* h, int slot) {
+  if (!h) return PGEN_ERR_ARG;
+  if (slot < 0 || slot >= (int)h->engs.size()) return fail(h, PGEN_ERR_ARG, "slot out of range");
+  h->stage_slot = slot;
+  return PGEN_OK;
+}
 
 int pgen_decode_ids(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
                     const int32_t* enc_lens, const int32_t* n_oovs, int32_t* out_tokens, int32_t* out_lens,
                     float* out_logprobs, double* out_avg) {
   if (!h) return PGEN_ERR_ARG;
   if (n_articles < 0 || (n_articles && (!enc_ids || !enc_ext_ids || !enc_lens))) return fail(h, PGEN_ERR_ARG, "bad arguments");
-  const int cap = h->eng.capacity(), S = (int)h->hp.max_dec_steps;
+  const int cap = h->eng().capacity(), S = (int)h->hp.max_dec_steps;
   for (int b0 = 0; b0 < n_articles; b0 += cap) {
     const int n = std::min(cap, n_articles - b0);
     int rc = pgen_stage_upload(h, n, enc_ids + (size_t)b0 * ld, enc_ext_ids + (size_t)b0 * ld, ld, enc_lens + b0,
@@ -254,26 +308,29 @@ int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float
   if (n_articles < 0 || (n_articles && (!enc_feat || !enc_states || !lens || !dfeat || !attn || !ctx)))
     return fail(h, PGEN_ERR_ARG, "pgen_attention: NULL device pointer");
   if (n_articles && h->hp.coverage && !cov) return fail(h, PGEN_ERR_ARG, "pgen_attention: coverage=1 needs cov");
-  std::string err = h->eng.attention_op(n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx);
+  std::string err = h->eng().attention_op(n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
 }
 
 int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* logits_dev, int use_tc) {
   if (!h || !out_dev || !logits_dev) return PGEN_ERR_ARG;
-  std::string err = h->eng.vocab_logits_op(rows, out_dev, logits_dev, use_tc);
+  std::string err = h->eng().vocab_logits_op(rows, out_dev, logits_dev, use_tc);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
 }
 
 int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n) {
   if (!h || !name || !out || !n) return PGEN_ERR_ARG;
-  std::string err = h->eng.fetch(name, out, cap_bytes, n);
+  std::string err = h->eng().fetch(name, out, cap_bytes, n);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
 }
 
 int pgen_set_option(pgen_t* h, const char* key_value) {
   if (!h || !key_value) return PGEN_ERR_ARG;
-  std::string err = h->eng.set_option(key_value);
-  return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
+  for (auto& e : h->engs) {
+    std::string err = e->set_option(key_value);
+    if (!err.empty()) return fail(h, PGEN_ERR_ARG, err);
+  }
+  return PGEN_OK;
 }
 
 }  // extern "C"

@@ -247,7 +247,7 @@ std::string Engine::set_option(const std::string& kv) {
   const size_t eq = kv.find('=');
   if (eq == std::string::npos) return "option must be key=value";
   const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
-  if (k == "check_every") { check_every_ = std::max(1, atoi(v.c_str())); return ""; }
+  if (k == "check_every") { check_every_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "encoder") { enc_persistent_ = (v != "steps"); return ""; }
   if (k == "vocab") {
     if (v == "simt") { vocab_tc_ = false; return ""; }
@@ -451,7 +451,7 @@ void Engine::decoder() {
     }
     nl += launch_beam_step(d_, B, s, topk_ids_, topk_logp_, bb_, st_);
     ++steps;
-    if (s + 1 < d_.S && s + 1 > d_.min_dec_steps && (s + 1) % check_every_ == 0) {
+    if (check_every_ > 0 && s + 1 < d_.S && s + 1 > d_.min_dec_steps && (s + 1) % check_every_ == 0) {
       cudaMemcpyAsync(h_nactive_, bb_.n_active, sizeof(int), cudaMemcpyDeviceToHost, st_);
       cudaStreamSynchronize(st_);
       if (*h_nactive_ == 0) break;
@@ -470,11 +470,29 @@ std::string Engine::run() {
   CK(cudaEventRecord(ev_[3], st_));
   if (nB_ > 0) decoder();
   CK(cudaEventRecord(ev_[4], st_));
+  // results to pinned host memory on the same stream: the batch is complete when ev_[6] has fired
+  const size_t n = nB_, S = d_.S;
+  CK(cudaEventRecord(ev_[5], st_));
+  if (n > 0) {
+    CK(cudaMemcpyAsync(h_out_tok_, out_tok_, n * S * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_out_len_, out_len_, n * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_out_lp_, out_lp_, n * S * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_out_avg_, out_avg_, n * 8, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_steps_, bb_.steps_done, n * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_rescnt_, bb_.res_count, n * 4, cudaMemcpyDeviceToHost, st_));
+  }
+  CK(cudaEventRecord(ev_[6], st_));
   std::string err = check("decode launch");
   if (!err.empty()) return err;
-  ran_ = true; synced_ = false;
+  ran_ = true; synced_ = false; counted_ = false;
   ++stats.batches;
   return "";
+}
+
+bool Engine::done() {
+  if (!ran_) return true;
+  cudaSetDevice(device_);
+  return cudaEventQuery(ev_[6]) == cudaSuccess;
 }
 
 std::string Engine::sync() {
@@ -485,6 +503,7 @@ std::string Engine::sync() {
     if (cudaEventElapsedTime(&ms, ev_[0], ev_[1]) == cudaSuccess) stats.ms_h2d = ms;
     if (cudaEventElapsedTime(&ms, ev_[2], ev_[3]) == cudaSuccess) stats.ms_encoder = ms;
     if (cudaEventElapsedTime(&ms, ev_[3], ev_[4]) == cudaSuccess) stats.ms_decoder = ms;
+    if (cudaEventElapsedTime(&ms, ev_[5], ev_[6]) == cudaSuccess) stats.ms_d2h = ms;
     if (pev_used_ > 0) {
       stats.ms_attention = stats.ms_vocab = 0;
       for (int s = 0; s < pev_used_; ++s) {
@@ -500,26 +519,15 @@ std::string Engine::sync() {
 
 std::string Engine::download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg) {
   if (!ran_) return "pgen_stage_download before pgen_stage_run";
-  CK(cudaSetDevice(device_));
-  const size_t n = nB_, S = d_.S;
-  CK(cudaEventRecord(ev_[5], st_));
-  if (n > 0) {
-    CK(cudaMemcpyAsync(h_out_tok_, out_tok_, n * S * 4, cudaMemcpyDeviceToHost, st_));
-    CK(cudaMemcpyAsync(h_out_len_, out_len_, n * 4, cudaMemcpyDeviceToHost, st_));
-    CK(cudaMemcpyAsync(h_out_lp_, out_lp_, n * S * 4, cudaMemcpyDeviceToHost, st_));
-    CK(cudaMemcpyAsync(h_out_avg_, out_avg_, n * 8, cudaMemcpyDeviceToHost, st_));
-    CK(cudaMemcpyAsync(h_steps_, bb_.steps_done, n * 4, cudaMemcpyDeviceToHost, st_));
-    CK(cudaMemcpyAsync(h_rescnt_, bb_.res_count, n * 4, cudaMemcpyDeviceToHost, st_));
-  }
-  CK(cudaEventRecord(ev_[6], st_));
-  CK(cudaStreamSynchronize(st_));
-  float ms = 0;
-  if (cudaEventElapsedTime(&ms, ev_[5], ev_[6]) == cudaSuccess) stats.ms_d2h = ms;
-  std::string err = check("download");
+  std::string err = sync();
   if (!err.empty()) return err;
-  for (size_t b = 0; b < n; ++b) {
-    stats.article_steps += h_steps_[b];
-    if (h_rescnt_[b] >= d_.K) ++stats.early_stops;
+  const size_t n = nB_, S = d_.S;
+  if (!counted_) {
+    for (size_t b = 0; b < n; ++b) {
+      stats.article_steps += h_steps_[b];
+      if (h_rescnt_[b] >= d_.K) ++stats.early_stops;
+    }
+    counted_ = true;
   }
   if (out_tokens) memcpy(out_tokens, h_out_tok_, n * S * 4);
   if (out_lens) memcpy(out_lens, h_out_len_, n * 4);

@@ -36,6 +36,7 @@ class Engine {
                      const int32_t* n_oovs);
   std::string run();
   std::string sync();
+  bool done();                       // the last run() (including its D2H copies) has finished
   std::string download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg);
   std::string fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n);
   std::string set_option(const std::string& kv);
@@ -58,8 +59,9 @@ class Engine {
 
   Dims d_{};
   int device_ = 0, Bcap_ = 0, R_ = 0, nB_ = 0, max_len_ = 0;
-  bool staged_ = false, ran_ = false, synced_ = false;
-  int check_every_ = 8;
+  bool staged_ = false, ran_ = false, synced_ = false, counted_ = false;
+  int check_every_ = 0;              // > 0: poll the device every N steps (after min_dec_steps) to stop early;
+                                     // 0: never block the host -- run() is fully asynchronous
   bool profile_ = false;
   bool enc_persistent_ = true;
   bool vocab_tc_ = false;          // tensor-core vocabulary path in use (falls back to the SIMT kernels when

@@ -115,13 +115,16 @@ gemm_skinny_kernel(GemmArgs g) {
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  for (int kt = grp * GBK; kt < Ktot; kt += KSPLIT * GBK) {
+  // register-staged software pipeline: the global loads of k-tile i+1 are in flight while tile i is multiplied
+  float4 pa[2], pb[2];
+  auto fetch = [&](int kt) {
     const bool seg0 = kt < g.k0;
 #pragma unroll
     for (int rep = 0; rep < 2; ++rep) {
       const int idx = t + rep * 64, row = idx >> 2, k4 = (idx & 3) * 4;
       const int m = m0 + row, n = n0 + row;
-      float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
+      pa[rep] = make_float4(0.f, 0.f, 0.f, 0.f);
+      pb[rep] = pa[rep];
       if (m < g.M) {
         const float* src;
         if (seg0) {
@@ -130,13 +133,22 @@ gemm_skinny_kernel(GemmArgs g) {
         } else {
           src = g.A1 + (long long)m * g.lda1 + (kt - g.k0) + k4;
         }
-        va = *reinterpret_cast<const float4*>(src);
+        pa[rep] = *reinterpret_cast<const float4*>(src);
       }
-      if (n < g.N) vb = *reinterpret_cast<const float4*>(g.B + (long long)n * g.ldb + kt + k4);
-      As[k4 + 0][row] = va.x; As[k4 + 1][row] = va.y; As[k4 + 2][row] = va.z; As[k4 + 3][row] = va.w;
-      Bs[k4 + 0][row] = vb.x; Bs[k4 + 1][row] = vb.y; Bs[k4 + 2][row] = vb.z; Bs[k4 + 3][row] = vb.w;
+      if (n < g.N) pb[rep] = *reinterpret_cast<const float4*>(g.B + (long long)n * g.ldb + kt + k4);
+    }
+  };
+  int kt = grp * GBK;
+  if (kt < Ktot) fetch(kt);
+  for (; kt < Ktot; kt += KSPLIT * GBK) {
+#pragma unroll
+    for (int rep = 0; rep < 2; ++rep) {
+      const int idx = t + rep * 64, row = idx >> 2, k4 = (idx & 3) * 4;
+      As[k4 + 0][row] = pa[rep].x; As[k4 + 1][row] = pa[rep].y; As[k4 + 2][row] = pa[rep].z; As[k4 + 3][row] = pa[rep].w;
+      Bs[k4 + 0][row] = pb[rep].x; Bs[k4 + 1][row] = pb[rep].y; Bs[k4 + 2][row] = pb[rep].z; Bs[k4 + 3][row] = pb[rep].w;
     }
     asm volatile("bar.sync %0, 64;" ::"r"(grp + 1));           // only this group's 64 threads
+    if (kt + KSPLIT * GBK < Ktot) fetch(kt + KSPLIT * GBK);
 #pragma unroll
     for (int k = 0; k < GBK; ++k) {
       const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
@@ -442,6 +454,15 @@ int launch_lstm_pointwise(const Dims& d, int R, const float* z, const float* cpr
 // ======================================================================================
 constexpr int ATT_TCH = 16;     // encoder positions per block (2 per warp)
 
+// tanh(x) = 1 - 2 / (1 + e^{2x}) on the special-function unit (ex2.approx + rcp.approx): absolute error ~2e-7,
+// saturates to +-1 for large |x|.  tanhf() costs ~4x the instructions and made the energy kernel issue-bound.
+__device__ __forceinline__ float tanh_mufu(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.885390081777927f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return fmaf(-2.0f, r, 1.0f);
+}
+
 template <int KMAX>
 __global__ void __launch_bounds__(256)
 attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __restrict__ active,
@@ -484,10 +505,10 @@ attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __r
         if (k < rpa) {
           const float4 dd = *reinterpret_cast<const float4*>(ds + k * A + a4 * 4);
           float x;
-          x = f.x + dd.x + cv[k] * ww.x; acc[k] = fmaf(vv.x, tanhf(x), acc[k]);
-          x = f.y + dd.y + cv[k] * ww.y; acc[k] = fmaf(vv.y, tanhf(x), acc[k]);
-          x = f.z + dd.z + cv[k] * ww.z; acc[k] = fmaf(vv.z, tanhf(x), acc[k]);
-          x = f.w + dd.w + cv[k] * ww.w; acc[k] = fmaf(vv.w, tanhf(x), acc[k]);
+          x = f.x + dd.x + cv[k] * ww.x; acc[k] = fmaf(vv.x, tanh_mufu(x), acc[k]);
+          x = f.y + dd.y + cv[k] * ww.y; acc[k] = fmaf(vv.y, tanh_mufu(x), acc[k]);
+          x = f.z + dd.z + cv[k] * ww.z; acc[k] = fmaf(vv.z, tanh_mufu(x), acc[k]);
+          x = f.w + dd.w + cv[k] * ww.w; acc[k] = fmaf(vv.w, tanh_mufu(x), acc[k]);
         }
       }
     }
@@ -566,7 +587,24 @@ attn_context_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
   const float* hb = enc_states + (size_t)art * T * A + col;
-  for (int t = tl; t < len; t += 16) {
+  int t = tl;
+  for (; t + 48 < len; t += 64) {                                     // 4 independent 16-byte loads in flight
+    float4 h[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) h[u] = __ldg(reinterpret_cast<const float4*>(hb + (size_t)(t + 16 * u) * A));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        if (k < rpa) {
+          const float a = as[k * T + t + 16 * u];
+          acc[k].x = fmaf(a, h[u].x, acc[k].x); acc[k].y = fmaf(a, h[u].y, acc[k].y);
+          acc[k].z = fmaf(a, h[u].z, acc[k].z); acc[k].w = fmaf(a, h[u].w, acc[k].w);
+        }
+      }
+    }
+  }
+  for (; t < len; t += 16) {
     const float4 h = __ldg(reinterpret_cast<const float4*>(hb + (size_t)t * A));
 #pragma unroll
     for (int k = 0; k < KMAX; ++k) {

@@ -15,7 +15,7 @@ EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_st
            "pgen_destroy", "pgen_flag_int", "pgen_text_encode", "pgen_text_summary", "pgen_decode_ids",
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
            "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
-           "pgen_attention_static", "pgen_debug_vocab_logits"]
+           "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -74,6 +74,7 @@ def lib() -> C.CDLL:
         L.pgen_stage_sync.argtypes = [C.c_void_p]
         L.pgen_stage_download.argtypes = [C.c_void_p, i32p, i32p, f32p, f64p]
         L.pgen_stream.argtypes = [C.c_void_p]
+        L.pgen_stage_slot.argtypes = [C.c_void_p, C.c_int]
         L.pgen_stream.restype = C.c_void_p
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
@@ -203,6 +204,9 @@ class Decoder:
         self._n_staged = n
         self._ck(self._L.pgen_stage_upload(self._h, n, _p(ids, C.c_int32), _p(ext, C.c_int32), ld,
                                             _p(lens, C.c_int32), _p(noov, C.c_int32)))
+
+    def stage_slot(self, slot: int):
+        self._ck(self._L.pgen_stage_slot(self._h, slot))
 
     def stage_run(self):
         self._ck(self._L.pgen_stage_run(self._h))
