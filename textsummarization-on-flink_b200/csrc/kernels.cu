@@ -288,7 +288,29 @@ int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const flo
 // --------------------------------------------------------------------------------------
 namespace cgx = cooperative_groups;
 constexpr int PE_H = 256, PE_AG = 8, PE_THREADS = 512;
-constexpr size_t PE_SMEM = (size_t)(PE_H * 128 + 2 * PE_H * PE_AG + 8 * PE_AG * 128) * sizeof(float);
+constexpr size_t PE_SMEM = (size_t)(PE_H * 128 + 2 * PE_H * PE_AG + 2 * 8 * PE_AG * 128) * sizeof(float) + 64;
+constexpr uint32_t PE_H_BYTES = PE_H * PE_AG * sizeof(float);   // one full h(s) for the group: 8 KB
+
+__device__ __forceinline__ uint32_t pe_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t pe_mapa(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// DSMEM store that signals the destination CTA's mbarrier with the bytes written (no cluster-wide fence)
+__device__ __forceinline__ void pe_st_async(uint32_t raddr, float v, uint32_t rbar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
+               ::"r"(raddr), "r"(__float_as_uint(v)), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void pe_bar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok = 0, spins = 0;
+  const uint32_t a = pe_smem_u32(bar);
+  while (!ok) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    if (!ok && ++spins > (1u << 26)) __trap();
+  }
+}
 
 __global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(PE_THREADS, 1)
 enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const float* __restrict__ zx,
@@ -297,20 +319,28 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
   extern __shared__ __align__(16) float sm[];
   float* Ws = sm;                                  // [256 k][128 local cols]
   float* hs = Ws + PE_H * 128;                     // [2][256 k][8 articles]
-  float* red = hs + 2 * PE_H * PE_AG;              // [8 kq][8 articles][128 cols]
+  float* red = hs + 2 * PE_H * PE_AG;              // [2][8 kq][8 articles][128 cols]
+  uint64_t* hbar = reinterpret_cast<uint64_t*>(red + 2 * 8 * PE_AG * 128);   // [2] "h buffer b is complete"
   cgx::cluster_group cluster = cgx::this_cluster();
   const int c = (int)cluster.block_rank();         // which 32 hidden units
   const int dir = blockIdx.y, b0 = blockIdx.z * PE_AG;
   const int tid = threadIdx.x;
   constexpr int H4 = 4 * PE_H;
 
-  // recurrent weights of this CTA's 128 gate columns, and h(0) = 0
+  // recurrent weights of this CTA's 128 gate columns, and h(-1) = 0
   const float* khd = kh + (size_t)dir * PE_H * H4;
   for (int i = tid; i < PE_H * 128; i += PE_THREADS) {
     const int k = i >> 7, lc = i & 127, g = lc >> 5, ul = lc & 31;
     Ws[i] = khd[(size_t)k * H4 + g * PE_H + 32 * c + ul];
   }
   for (int i = tid; i < 2 * PE_H * PE_AG; i += PE_THREADS) hs[i] = 0.f;
+  if (tid == 0) {
+    for (int b = 0; b < 2; ++b) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(pe_smem_u32(&hbar[b])));
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[b])), "r"(PE_H_BYTES) : "memory");
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   int grp_max = 0;
   for (int a = 0; a < PE_AG; ++a) if (b0 + a < B) grp_max = max(grp_max, lens[b0 + a]);
   // roles
@@ -319,6 +349,13 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
   const int fb = b0 + fa;
   const int flen = (tid < 256 && fb < B) ? lens[fb] : 0;
   float c_reg = 0.f, h_reg = 0.f;
+  // remote addresses of "my" h element and of the two barriers in each CTA of the cluster
+  uint32_t r_h[8], r_bar[8];
+#pragma unroll
+  for (int rk = 0; rk < 8; ++rk) {
+    r_h[rk] = pe_mapa(pe_smem_u32(hs + (32 * c + ful) * PE_AG + fa), rk);
+    r_bar[rk] = pe_mapa(pe_smem_u32(&hbar[0]), rk);
+  }
   cluster.sync();
 
   for (int s = 0; s < grp_max; ++s) {
@@ -330,6 +367,11 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
       t = dir == 0 ? s : flen - 1 - s;             // backward: reversed over the article's own length
       const float* zp = zx + ((size_t)dir * B * T + (size_t)fb * T + t) * H4 + 32 * c + ful;
       zi = __ldg(zp); zj = __ldg(zp + PE_H); zf = __ldg(zp + 2 * PE_H); zo = __ldg(zp + 3 * PE_H);
+    }
+    if (s > 0) {                                   // h(s-1) from all 8 CTAs has landed in hs[cur]
+      pe_bar_wait(&hbar[cur], ((s - 1) >> 1) & 1);
+      if (tid == 0 && s + 1 < grp_max)             // arm the same barrier for h(s+1), which reuses this buffer
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[cur])), "r"(PE_H_BYTES) : "memory");
     }
     // partial h . Kh over this thread's k range
     float acc0[PE_AG], acc1[PE_AG];
@@ -347,10 +389,11 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
       acc1[0] = fmaf(ha.x, w1, acc1[0]); acc1[1] = fmaf(ha.y, w1, acc1[1]); acc1[2] = fmaf(ha.z, w1, acc1[2]); acc1[3] = fmaf(ha.w, w1, acc1[3]);
       acc1[4] = fmaf(hb.x, w1, acc1[4]); acc1[5] = fmaf(hb.y, w1, acc1[5]); acc1[6] = fmaf(hb.z, w1, acc1[6]); acc1[7] = fmaf(hb.w, w1, acc1[7]);
     }
+    float* redc = red + cur * (8 * PE_AG * 128);   // double-buffered: step s+1 may write while step s is still read
 #pragma unroll
     for (int a = 0; a < PE_AG; ++a) {
-      red[(kq * PE_AG + a) * 128 + cp] = acc0[a];
-      red[(kq * PE_AG + a) * 128 + cp + 64] = acc1[a];
+      redc[(kq * PE_AG + a) * 128 + cp] = acc0[a];
+      redc[(kq * PE_AG + a) * 128 + cp + 64] = acc1[a];
     }
     __syncthreads();
     if (tid < 256) {
@@ -359,7 +402,7 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
         float gi = zi, gj = zj, gf = zf, go = zo;
 #pragma unroll
         for (int q = 0; q < 8; ++q) {              // fixed order: deterministic
-          const float* r = red + (q * PE_AG + fa) * 128 + ful;
+          const float* r = redc + (q * PE_AG + fa) * 128 + ful;
           gi += r[0]; gj += r[32]; gf += r[64]; go += r[96];
         }
         c_reg = sigmoidf_(gf + 1.0f) * c_reg + sigmoidf_(gi) * tanhf(gj);   // LSTMCell, forget_bias 1
@@ -367,13 +410,16 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
         h_reg = hn;
         enc_states[((size_t)fb * T + t) * (2 * PE_H) + dir * PE_H + 32 * c + ful] = hn;   // model.py:93
       }
-      // new h (or the frozen one past the article's end) into every CTA of the cluster
-      float* dst = hs + (cur ^ 1) * PE_H * PE_AG + (32 * c + ful) * PE_AG + fa;
+      // new h (or the frozen one past the article's end) into buffer cur^1 of every CTA of the cluster; each
+      // store adds its 4 bytes to that CTA's barrier for the buffer
+      if (s + 1 < grp_max) {
+        const uint32_t boff = (uint32_t)(cur ^ 1) * PE_H_BYTES, bar_off = (uint32_t)(cur ^ 1) * 8u;
 #pragma unroll
-      for (int rk = 0; rk < 8; ++rk) *cluster.map_shared_rank(dst, rk) = hn;
+        for (int rk = 0; rk < 8; ++rk) pe_st_async(r_h[rk] + boff, hn, r_bar[rk] + bar_off);
+      }
     }
-    cluster.sync();                                // h(s+1) visible cluster-wide; also protects `red`
   }
+  cluster.sync();                                  // nobody leaves while remote stores may still target it
   if (tid < 256 && fb < B) {
     h_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = h_reg;
     c_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = c_reg;
