@@ -119,6 +119,17 @@ def ensure_model(rank: int, barrier) -> dict:
     return paths
 
 
+def use_all_host_threads() -> int:
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core."""
+    n = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=n)
+    except Exception:
+        pass
+    return n
+
+
 def cpu_reference_sample(paths: dict, n_articles: int, seed: int) -> tuple:
     """The oracle in reference-faithful mode (K replicated rows, W_h.h_i recomputed every step, two
     attention passes, host-side beam search).  bench.py is one of the few places allowed to import it."""
@@ -128,6 +139,7 @@ def cpu_reference_sample(paths: dict, n_articles: int, seed: int) -> tuple:
     W = weights_io.load_weights(paths["weights"])
     hps = O.parse_hyperparams(synth.hyperparams_string(paths))
     arts = synth.make_article_ids(n_articles, vsize=V, seed=seed, full_len_only=False)
+    use_all_host_threads()
     t0 = time.perf_counter()
     for ids, ext, n_oov in arts:
         O.decode_ids(W, hps, ids, ext, n_oov, mode="literal")
@@ -145,6 +157,7 @@ def run_reference(args, rank: int, world: int):
     W = weights_io.load_weights(paths["weights"])
     hps = O.parse_hyperparams(synth.hyperparams_string(paths))
     arts = synth.make_article_ids(per_step * (args.steps + args.warmup), vsize=V, seed=4321)
+    use_all_host_threads()
     times = []
     for s in range(args.steps + args.warmup):
         t0 = time.perf_counter()
