@@ -138,7 +138,7 @@ int pgen_create(const char* hyperparams, int device_ordinal, pgen_t** out) {
   for (int64_t i = 0; i < hp.slots; ++i) {
     int code = PGEN_OK;
     h->engs.emplace_back(new Engine());
-    err = h->engs.back()->init(hp, h->vocab.size(), device_ordinal, &code);
+    err = h->engs.back()->init(hp, h->vocab.size(), device_ordinal, &code, i == 0 ? nullptr : h->engs[0].get());
     if (!err.empty()) return fail(nullptr, code, err);
   }
   *out = h.release();

@@ -163,7 +163,7 @@ std::string Engine::load_weights(const std::string& path) {
   return "";
 }
 
-std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int* code) {
+std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int* code, const Engine* share) {
   *code = PGEN_ERR_CUDA;
   device_ = device;
   int ndev = 0;
@@ -196,7 +196,9 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   *code = PGEN_ERR_IO;
   std::string wpath = hp.weights_path;
   if (wpath.empty()) wpath = hp.log_root + "/" + hp.exp_name + "/train/model.pgenw";   // util.py:34
-  std::string err = load_weights(wpath);
+  std::string err;
+  if (share) w_ = share->w_;                       // borrowed device pointers; the owner frees them
+  else err = load_weights(wpath);
   if (!err.empty()) return err;
 
   *code = PGEN_ERR_CUDA;
@@ -228,11 +230,13 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   {
     cudaDeviceGetAttribute(&n_sms_, cudaDevAttrMultiProcessorCount, device_);
     const size_t Rpad = (R + 127) / 128 * 128;
-    DALLOC(proj_wT_tf32_, float, V * H); DALLOC(out_tf32_, float, Rpad * H);
+    if (share) proj_wT_tf32_ = share->proj_wT_tf32_;
+    else DALLOC(proj_wT_tf32_, float, V * H);
+    DALLOC(out_tf32_, float, Rpad * H);
     DALLOC(part_m_, float, (size_t)2 * n_sms_ * R); DALLOC(part_s_, float, (size_t)2 * n_sms_ * R);
     DALLOC(cand_v_, float, (size_t)2 * n_sms_ * R * 16); DALLOC(cand_i_, int, (size_t)2 * n_sms_ * R * 16);
     DALLOC(artl_, float, R * T);
-    launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
+    if (!share) launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
     else vtc_why_ = "vocabulary smaller than one 128-word tile";
     vocab_tc_ = vtc_.ready;

@@ -31,7 +31,9 @@ class Engine {
  public:
   ~Engine();
   // Returns "" or an error message; *code receives the PGEN_ERR_* class.
-  std::string init(const HyperParams& hp, int vocab_size, int device, int* code);
+  // `share` (optional): another engine of the same handle whose weight replica (fp32 + tf32 copy) is reused, so
+  // that all slots of a handle read ONE copy of the weights.
+  std::string init(const HyperParams& hp, int vocab_size, int device, int* code, const Engine* share = nullptr);
   std::string upload(int n, const int32_t* enc_ids, const int32_t* ext_ids, int ld, const int32_t* lens,
                      const int32_t* n_oovs);
   std::string run();
