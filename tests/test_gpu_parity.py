@@ -183,3 +183,27 @@ def test_full_size_encoder_states(model_dir, encoder):
         np.testing.assert_allclose(ef[b, :L], O.encoder_features(W, enc[None])[0], atol=1e-4, rtol=1e-4)
         np.testing.assert_allclose(c0[b], rc, atol=2e-5, rtol=1e-4)
         np.testing.assert_allclose(h0[b], rh, atol=2e-5, rtol=1e-4)
+
+
+def test_config4_beam8_200_oovs(model_dir):
+    """Config 4 of BASELINE.json: beam 8, max_dec_steps 120, exactly 200 distinct OOV words per article
+    (extended vocabulary 50 200, top-16)."""
+    from textsummarization_on_flink_b200 import weights_io
+    flags = synth.hyperparams_string(model_dir, beam_size=8, max_dec_steps=120, extra="--articles_per_batch=4")
+    hps = O.parse_hyperparams(flags)
+    W = weights_io.load_weights(model_dir["weights"])
+    arts = synth.make_article_ids(3, seed=404, fixed_oovs=200, full_len_only=True)
+    assert all(k == 200 for _, _, k in arts)
+    with native.Decoder(flags) as dec:
+        check_against_oracle(dec, W, hps, arts, max_near_tie_frac=0.34)
+    # the same articles inside a full device batch of 64 (4 row blocks of 128 in the tensor-core kernel)
+    flags64 = synth.hyperparams_string(model_dir, beam_size=8, max_dec_steps=120, extra="--articles_per_batch=64 --slots=1")
+    more = synth.make_article_ids(61, seed=405, fixed_oovs=200)
+    with native.Decoder(flags64) as dec:
+        ids, ext, lens, noov = native.pack_articles(arts + more, dec.max_enc_steps)
+        tok, ln, lp, avg = dec.decode_ids(ids, ext, lens, noov)
+        with native.Decoder(flags) as small:
+            t2, l2, p2, a2 = small.decode_ids(ids[:3], ext[:3], lens[:3], noov[:3])
+        for b in range(3):
+            assert ln[b] == l2[b] and np.array_equal(tok[b], t2[b])
+            np.testing.assert_allclose(lp[b, :ln[b]], p2[b, :l2[b]], rtol=1e-4, atol=1e-5)

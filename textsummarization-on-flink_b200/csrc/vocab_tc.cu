@@ -599,6 +599,11 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
 void VocabTC::plan(int R, int* n_mblocks, int* n_ranges) const {
   *n_mblocks = (R + BM - 1) / BM;
   int nr = sms / *n_mblocks;
+  // the merge kernel stages every candidate list of an article in shared memory: K rows x 2 parts per range x K2MAX
+  // entries x 8 bytes.  Keep that below ~96 KB (only binds for wide beams on small batches).
+  const int K = K2 / 2 > 0 ? K2 / 2 : 1;
+  const int cap = (96 * 1024) / (16 * K * K2MAX);
+  if (nr > cap) nr = cap;
   if (nr < 1) nr = 1;
   if (nr > n_tiles) nr = n_tiles;
   *n_ranges = nr;
