@@ -604,6 +604,17 @@ attn_context_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __
   float* as = sm;                         // [KMAX][T]
   float* red = sm + KMAX * T;             // [8][KMAX][CTX_COLS]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // The encoder-state loads do not depend on the softmax: put the first four per thread in flight now, so that the
+  // HBM latency is paid while the softmax below is computed.
+  const int c4 = threadIdx.x & 15, tl = threadIdx.x >> 4;             // 16 float4 columns x 16 t-lanes
+  const int col = blockIdx.x * CTX_COLS + c4 * 4;
+  const float* hb = enc_states + (size_t)art * T * A + col;
+  float4 pre[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int t = tl + 16 * u;
+    pre[u] = t < len ? __ldg(reinterpret_cast<const float4*>(hb + (size_t)t * A)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   // masked softmax per row (attention_decoder.py:96-101); mask == (t < len)
   for (int k = warp; k < rpa; k += 8) {
     const float* er = e + (size_t)(art * d.K + k) * T;
@@ -627,13 +638,25 @@ attn_context_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __
   }
   __syncthreads();
   // context = sum_t attn[t] * h_t   (:126-127)
-  const int c4 = threadIdx.x & 15, tl = threadIdx.x >> 4;             // 16 float4 columns x 16 t-lanes
-  const int col = blockIdx.x * CTX_COLS + c4 * 4;
   float4 acc[KMAX];
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-  const float* hb = enc_states + (size_t)art * T * A + col;
   int t = tl;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {                                       // the prefetched positions t = tl + 16u
+    const int tu = tl + 16 * u;
+    if (tu < len) {
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        if (k < rpa) {
+          const float a = as[k * T + tu];
+          acc[k].x = fmaf(a, pre[u].x, acc[k].x); acc[k].y = fmaf(a, pre[u].y, acc[k].y);
+          acc[k].z = fmaf(a, pre[u].z, acc[k].z); acc[k].w = fmaf(a, pre[u].w, acc[k].w);
+        }
+      }
+    }
+  }
+  t = tl + 64;
   for (; t + 48 < len; t += 64) {                                     // 4 independent 16-byte loads in flight
     float4 h[4];
 #pragma unroll
