@@ -322,13 +322,19 @@ def main():
     attn_bytes_total = float(np.sum(steps_done * (2 * lens * A * 4 + 3 * BEAM * lens * 4)))
     roof_attn = {"bound": "hbm", "kernel": "attn_energy + attn_context (per step)",
                  "achieved": attn_bytes_total / (ps["ms_attention"] * 1e-3) / 1e9 if ps["ms_attention"] > 0 else None,
-                 "peak": pk["hbm_gbs"], "unit": "GB/s", "traffic": None, "ms_per_launch": ms_attn}
+                 "peak": pk["hbm_gbs"], "unit": "GB/s", "ms_per_launch": ms_attn,
+                 # dram__bytes_read.sum + dram__bytes_write.sum of one attn_energy + attn_context launch pair from the
+                 # ncu --set full capture summarised in profiles/r1_final_summary.md (batch with mean length 372:
+                 # 96.9 MB algorithmic): bytes per launch pair
+                 "traffic": 96.63e6, "algorithmic_bytes_per_launch": attn_bytes_total / max(1.0, n_prof)}
     if roof_attn["achieved"]:
         roof_attn["frac"] = roof_attn["achieved"] / pk["hbm_gbs"]
     flops = 2.0 * R * H * V
     roof_vocab = {"bound": "tensor", "kernel": "vocab projection GEMM (per step)",
                   "achieved": flops / (ms_vocab * 1e-3) / 1e12 if ms_vocab > 0 else None,
-                  "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "traffic": None, "ms_per_launch": ms_vocab}
+                  "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "ms_per_launch": ms_vocab,
+                  "traffic": 51.80e6, "note": "tf32 operands (kind::tf32); peak is the measured bf16 figure, the tf32 "
+                                               "tensor peak is half of it; traffic = dram bytes of one vocab_tc_kernel launch"}
     if roof_vocab["achieved"]:
         roof_vocab["frac"] = roof_vocab["achieved"] / pk["bf16_tflops_sustained"]
     dominant = roof_vocab if ms_vocab >= ms_attn else roof_attn
