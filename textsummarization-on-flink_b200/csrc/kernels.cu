@@ -525,9 +525,9 @@ attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __r
   float* ds = sm;                 // [rpa][A]
   float* vs = ds + KMAX * A;      // [A]
   float* ws = vs + A;             // [A]
-  for (int i = threadIdx.x; i < rpa * A; i += 256) {
-    const int k = i / A, a = i - k * A;
-    ds[i] = dfeat[(size_t)(art * d.K + k) * A + a];
+  for (int k = 0; k < rpa; ++k) {                       // no i / A here: a runtime integer division per element
+    const float* src = dfeat + (size_t)(art * d.K + k) * A;           // costs more than the loads it indexes
+    for (int a = threadIdx.x; a < A; a += 256) ds[k * A + a] = src[a];
   }
   for (int i = threadIdx.x; i < A; i += 256) { vs[i] = v[i]; ws[i] = d.use_cov ? w_c[i] : 0.f; }
   __syncthreads();
