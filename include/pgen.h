@@ -136,6 +136,17 @@ PGEN_API int pgen_stage_slot(pgen_t* h, int slot);
 /* The handle's cudaStream_t (as void*), so that a harness can record CUDA events on it. */
 PGEN_API void* pgen_stream(pgen_t* h);
 
+/* tf.Example wire format of the rows: what the reference moves through its Java<->Python queues.
+ * pgen_example_parse replaces tf.parse_single_example with the three FixedLenFeature([], tf.string) features of
+ * FlinkInferenceBatcher (batcher.py:554-557): it fills uuid / article / reference (and summary when present) of *out
+ * with views INTO `example`; a missing feature, or one that is not a single bytes value, is PGEN_ERR_ARG (message via
+ * pgen_last_error(NULL)).  pgen_example_write replaces FlinkWriter.write_result's serialisation
+ * (flink_writer.py:26-34): features uuid, article, summary, reference; *len receives the size, call with out == NULL
+ * to query it.  Both are stateless and need no GPU.  pgen_submit_example = parse + pgen_submit. */
+PGEN_API int pgen_example_parse(const void* example, size_t len, pgen_row_t* out);
+PGEN_API int pgen_example_write(const pgen_row_t* row, void* out, size_t cap, size_t* len);
+PGEN_API int pgen_submit_example(pgen_t* h, const void* example, size_t len);
+
 /* Kernel-level entry: one attention pass (attention_decoder.py:79-129 -- energies with coverage,
  * masked softmax, re-normalisation, context vector) over n_articles x beam_size decoder rows, using the
  * handle's attention weights v / w_c.  ALL pointers are DEVICE memory on the handle's device:

@@ -11,9 +11,11 @@ for f in kernels.cu engine.cu capi.cu noalloc.cu vocab_tc.cu; do
     $NVCC $FLAGS -c $f -o build/${f%.cu}.o &
   fi
 done
-if [ ! -f build/text.o ] || [ text.cc -nt build/text.o ] || [ text.h -nt build/text.o ]; then
-  g++ -std=c++17 -O2 -fPIC -fvisibility=hidden -c text.cc -o build/text.o &
-fi
+for f in text tfexample; do
+  if [ ! -f build/$f.o ] || [ $f.cc -nt build/$f.o ] || [ $f.h -nt build/$f.o ]; then
+    g++ -std=c++17 -O2 -fPIC -fvisibility=hidden -c $f.cc -o build/$f.o &
+  fi
+done
 wait
-$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $OUT build/kernels.o build/engine.o build/capi.o build/noalloc.o build/vocab_tc.o build/text.o -cudart static
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $OUT build/kernels.o build/engine.o build/capi.o build/noalloc.o build/vocab_tc.o build/text.o build/tfexample.o -cudart static
 echo built $OUT

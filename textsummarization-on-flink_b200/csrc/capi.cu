@@ -9,6 +9,7 @@
 #include "../../include/pgen.h"
 #include "engine.h"
 #include "text.h"
+#include "tfexample.h"
 #include "handle_access.h"
 
 using namespace pgn;
@@ -310,6 +311,53 @@ int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float
   if (n_articles && h->hp.coverage && !cov) return fail(h, PGEN_ERR_ARG, "pgen_attention: coverage=1 needs cov");
   std::string err = h->eng().attention_op(n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
+}
+
+// ---- tf.Example wire format of the rows (stateless; no GPU involved) ----
+static const pgn::BytesFeature* find_feature(const std::vector<pgn::BytesFeature>& fs, const char* name) {
+  for (auto& f : fs) if (f.name == name) return &f;
+  return nullptr;
+}
+
+int pgen_example_parse(const void* example, size_t len, pgen_row_t* out) {
+  if ((!example && len) || !out) return PGEN_ERR_ARG;
+  std::vector<pgn::BytesFeature> fs;
+  std::string err = pgn::parse_example(static_cast<const uint8_t*>(example), len, &fs);
+  if (!err.empty()) { g_create_error = err; return PGEN_ERR_ARG; }
+  memset(out, 0, sizeof *out);
+  const char* need[3] = {"uuid", "article", "reference"};                 // batcher.py:554-557, FixedLenFeature([], string)
+  const pgn::BytesFeature* got[3];
+  for (int i = 0; i < 3; ++i) {
+    got[i] = find_feature(fs, need[i]);
+    if (!got[i]) { g_create_error = std::string("tf.Example lacks the bytes feature '") + need[i] + "'"; return PGEN_ERR_ARG; }
+  }
+  out->uuid = got[0]->value.data(); out->uuid_len = got[0]->value.size();
+  out->article = got[1]->value.data(); out->article_len = got[1]->value.size();
+  out->reference = got[2]->value.data(); out->reference_len = got[2]->value.size();
+  if (const pgn::BytesFeature* s = find_feature(fs, "summary")) { out->summary = s->value.data(); out->summary_len = s->value.size(); }
+  return PGEN_OK;
+}
+
+int pgen_example_write(const pgen_row_t* row, void* out, size_t cap, size_t* len) {
+  if (!row || !len) return PGEN_ERR_ARG;
+  auto sv = [](const char* p, size_t n) { return std::string_view(p ? p : "", n); };
+  std::vector<pgn::BytesFeature> fs = {{"uuid", sv(row->uuid, row->uuid_len)}, {"article", sv(row->article, row->article_len)},
+                                       {"summary", sv(row->summary, row->summary_len)},
+                                       {"reference", sv(row->reference, row->reference_len)}};   // flink_writer.py:26-33
+  std::string s;
+  pgn::write_example(fs, &s);
+  *len = s.size();
+  if (out && cap >= s.size()) memcpy(out, s.data(), s.size());
+  else if (out) { g_create_error = "pgen_example_write: buffer too small"; return PGEN_ERR_ARG; }
+  return PGEN_OK;
+}
+
+int pgen_submit_example(pgen_t* h, const void* example, size_t len) {
+  if (!h) return PGEN_ERR_ARG;
+  pgen_row_t r;
+  int rc = pgen_example_parse(example, len, &r);
+  if (rc != PGEN_OK) return fail(h, rc, g_create_error);
+  return pgen_submit(h, r.uuid, r.uuid_len, r.article, r.article_len, r.reference, r.reference_len);
 }
 
 int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* logits_dev, int use_tc) {

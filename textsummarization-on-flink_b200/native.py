@@ -15,7 +15,8 @@ EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_st
            "pgen_destroy", "pgen_flag_int", "pgen_text_encode", "pgen_text_summary", "pgen_decode_ids",
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
            "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
-           "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot"]
+           "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot",
+           "pgen_example_parse", "pgen_example_write", "pgen_submit_example"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -75,6 +76,9 @@ def lib() -> C.CDLL:
         L.pgen_stage_download.argtypes = [C.c_void_p, i32p, i32p, f32p, f64p]
         L.pgen_stream.argtypes = [C.c_void_p]
         L.pgen_stage_slot.argtypes = [C.c_void_p, C.c_int]
+        L.pgen_example_parse.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(Row)]
+        L.pgen_example_write.argtypes = [C.POINTER(Row), C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.pgen_submit_example.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
         L.pgen_stream.restype = C.c_void_p
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
@@ -102,6 +106,29 @@ def pack_articles(arts: Sequence[Tuple[np.ndarray, np.ndarray, int]], ld: int):
         ids[i, :len(a)] = a
         ext[i, :len(a)] = e
     return ids, ext, lens, noov
+
+
+def example_parse(buf: bytes):
+    """tf.Example bytes -> (uuid, article, summary, reference) via the library's codec (no GPU needed)."""
+    r = Row()
+    rc = lib().pgen_example_parse(buf, len(buf), C.byref(r))
+    if rc != 0:
+        raise PgenError(rc, (lib().pgen_last_error(None) or b"").decode(errors="replace"))
+    return tuple(C.string_at(getattr(r, f), getattr(r, f + "_len")) if getattr(r, f) else b""
+                 for f in ("uuid", "article", "summary", "reference"))
+
+
+def example_write(uuid: bytes, article: bytes, summary: bytes, reference: bytes) -> bytes:
+    keep = [C.create_string_buffer(x, len(x)) for x in (uuid, article, summary, reference)]
+    r = Row(C.cast(keep[0], C.c_void_p), len(uuid), C.cast(keep[1], C.c_void_p), len(article),
+            C.cast(keep[2], C.c_void_p), len(summary), C.cast(keep[3], C.c_void_p), len(reference))
+    n = C.c_size_t()
+    lib().pgen_example_write(C.byref(r), None, 0, C.byref(n))
+    out = C.create_string_buffer(max(1, n.value))
+    rc = lib().pgen_example_write(C.byref(r), out, n.value, C.byref(n))
+    if rc != 0:
+        raise PgenError(rc, (lib().pgen_last_error(None) or b"").decode(errors="replace"))
+    return out.raw[:n.value]
 
 
 class Decoder:
@@ -148,6 +175,9 @@ class Decoder:
     # ---- row level (the operator's open / flatMap / close pattern) ----
     def submit(self, uuid: bytes, article: bytes, reference: bytes):
         self._ck(self._L.pgen_submit(self._h, uuid, len(uuid), article, len(article), reference, len(reference)))
+
+    def submit_example(self, example: bytes):
+        self._ck(self._L.pgen_submit_example(self._h, example, len(example)))
 
     def poll(self, flush: bool = False) -> List[Tuple[bytes, bytes, bytes, bytes]]:
         rows = Rows()
