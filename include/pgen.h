@@ -65,6 +65,7 @@ typedef struct {
   double ms_host_text;         /* tokenise + id maps + detokenise                            */
   double ms_h2d, ms_encoder, ms_decoder, ms_d2h;   /* CUDA-event times of the last batch    */
   double ms_attention, ms_vocab;   /* summed over the steps of the last batch run with option profile=1 */
+  double ms_select;                /* ... same for what follows the vocabulary GEMM: re-scoring, merge, top-2K */
   double prof_steps;               /* number of steps those two sums cover */
 } pgen_stats_t;
 

@@ -226,7 +226,8 @@ int pgen_stats(pgen_t* h, pgen_stats_t* out) {
   out->article_steps = s.article_steps; out->early_stops = s.early_stops; out->kernel_launches = s.kernel_launches;
   out->ms_host_text = h->ms_host_text; out->ms_h2d = last.ms_h2d; out->ms_encoder = last.ms_encoder;
   out->ms_decoder = last.ms_decoder; out->ms_d2h = last.ms_d2h;
-  out->ms_attention = last.ms_attention; out->ms_vocab = last.ms_vocab; out->prof_steps = (double)last.prof_steps;
+  out->ms_attention = last.ms_attention; out->ms_vocab = last.ms_vocab; out->ms_select = last.ms_beam;
+  out->prof_steps = (double)last.prof_steps;
   return PGEN_OK;
 }
 

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <fstream>
 
 #include "../../include/pgen.h"
@@ -234,7 +235,8 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     else DALLOC(proj_wT_tf32_, float, V * H);
     DALLOC(out_tf32_, float, Rpad * H);
     DALLOC(part_m_, float, (size_t)2 * n_sms_ * R); DALLOC(part_s_, float, (size_t)2 * n_sms_ * R);
-    DALLOC(cand_v_, float, (size_t)2 * n_sms_ * R * 16); DALLOC(cand_i_, int, (size_t)2 * n_sms_ * R * 16);
+    gstride_ = (int)Rpad;
+    DALLOC(gmax_, float4, ((V + 31) / 32) * Rpad);
     DALLOC(artl_, float, R * T);
     if (!share) launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
@@ -265,7 +267,7 @@ std::string Engine::set_option(const std::string& kv) {
   if (k == "profile") {
     profile_ = atoi(v.c_str()) != 0;
     if (profile_ && pev_.empty()) {
-      pev_.resize((size_t)4 * d_.S);
+      pev_.resize((size_t)5 * d_.S);
       for (auto& e : pev_) CK(cudaEventCreate(&e));
     }
     return "";
@@ -414,10 +416,10 @@ void Engine::decoder() {
     g = GemmArgs(); g.A0 = state_[n] + A; g.lda0 = SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
     g.C = dfeat_; g.ldc = A; g.M = R; g.N = A; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
-    if (profile_) cudaEventRecord(pev_[4 * s + 0], st_);
+    if (profile_) cudaEventRecord(pev_[5 * s + 0], st_);
     nl += launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[n], w_.v, w_.w_c, e_, st_);
     nl += launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[n], state_[n], st_);
-    if (profile_) cudaEventRecord(pev_[4 * s + 1], st_);
+    if (profile_) cudaEventRecord(pev_[5 * s + 1], st_);
     if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, st_);   // :166-167
     // output = [h; ctx] . AttnOutputProjection + b                                (:173)
     g = GemmArgs(); g.A0 = state_[n] + A + H; g.lda0 = SW; g.k0 = H; g.A1 = state_[n]; g.lda1 = SW; g.k1 = A;
@@ -429,29 +431,32 @@ void Engine::decoder() {
       vtc_.plan(R, &nmb, &nr);
       MergeArgs ma;
       ma.out = out_; ma.wT = w_.proj_wT; ma.bias = w_.proj_v; ma.part_m = part_m_; ma.part_s = part_s_;
-      ma.cand_v = cand_v_; ma.cand_i = cand_i_; ma.artl = artl_; ma.pgen = pgen_; ma.attn = attn_[n]; ma.uniq_ids = uniq_;
+      ma.gmax = gmax_; ma.gstride = gstride_;
+      ma.artl = artl_; ma.pgen = pgen_; ma.attn = attn_[n]; ma.uniq_ids = uniq_;
       ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active; ma.lens = lens_;
-      ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.K2MAX = vtc_.K2MAX; ma.H = H;
+      ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
-      if (profile_) cudaEventRecord(pev_[4 * s + 2], st_);
+      if (profile_) cudaEventRecord(pev_[5 * s + 2], st_);
       nl += launch_round_tf32(out_, out_tf32_, (size_t)R * H, st_);
-      nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, cand_v_, cand_i_, nullptr, st_);
-      if (profile_) cudaEventRecord(pev_[4 * s + 3], st_);
+      nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, nullptr, st_);
+      if (profile_) cudaEventRecord(pev_[5 * s + 3], st_);
       nl += vtc_.launch_rescore(ma, B, st_);                 // exact fp32 logits of the article's words
-      nl += vtc_.launch_merge(ma, B, st_);                   // exact re-scoring, copy mass, top-2K   (model.py:146-183, 284-285)
+      nl += vtc_.launch_final(ma, st_);                      // candidates re-scored in fp32, copy mass, top-2K   (model.py:146-183, 284-285)
+      if (profile_) cudaEventRecord(pev_[5 * s + 4], st_);
     } else {
     // vocabulary scores                                                           (model.py:236)
     g = GemmArgs(); g.A0 = out_; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;
     g.C = logits_; g.ldc = d_.V; g.M = R; g.N = d_.V;
-    if (profile_) cudaEventRecord(pev_[4 * s + 2], st_);
+    if (profile_) cudaEventRecord(pev_[5 * s + 2], st_);
     nl += launch_gemm_nt(g, st_);
-    if (profile_) cudaEventRecord(pev_[4 * s + 3], st_);
+    if (profile_) cudaEventRecord(pev_[5 * s + 3], st_);
     nl += launch_softmax_stats(d_, R, logits_, rowmax_, rowsum_, bb_.active, st_);
     FinalArgs fa;
     fa.logits = logits_; fa.rowmax = rowmax_; fa.rowsum = rowsum_; fa.pgen = pgen_; fa.attn = attn_[n];
     fa.uniq_ids = uniq_; fa.uniq_cnt = ucnt_; fa.pos_start = pstart_; fa.pos_list = plist_; fa.n_oov = noov_;
     fa.active = bb_.active; fa.topk_ids = topk_ids_; fa.topk_logp = topk_logp_;
     nl += launch_final_topk(d_, B, fa, st_);
+    if (profile_) cudaEventRecord(pev_[5 * s + 4], st_);
     }
     nl += launch_beam_step(d_, B, s, topk_ids_, topk_logp_, bb_, st_);
     ++steps;
@@ -509,10 +514,11 @@ std::string Engine::sync() {
     if (cudaEventElapsedTime(&ms, ev_[3], ev_[4]) == cudaSuccess) stats.ms_decoder = ms;
     if (cudaEventElapsedTime(&ms, ev_[5], ev_[6]) == cudaSuccess) stats.ms_d2h = ms;
     if (pev_used_ > 0) {
-      stats.ms_attention = stats.ms_vocab = 0;
+      stats.ms_attention = stats.ms_vocab = stats.ms_beam = 0;
       for (int s = 0; s < pev_used_; ++s) {
-        if (cudaEventElapsedTime(&ms, pev_[4 * s], pev_[4 * s + 1]) == cudaSuccess) stats.ms_attention += ms;
-        if (cudaEventElapsedTime(&ms, pev_[4 * s + 2], pev_[4 * s + 3]) == cudaSuccess) stats.ms_vocab += ms;
+        if (cudaEventElapsedTime(&ms, pev_[5 * s], pev_[5 * s + 1]) == cudaSuccess) stats.ms_attention += ms;
+        if (cudaEventElapsedTime(&ms, pev_[5 * s + 2], pev_[5 * s + 3]) == cudaSuccess) stats.ms_vocab += ms;
+        if (cudaEventElapsedTime(&ms, pev_[5 * s + 3], pev_[5 * s + 4]) == cudaSuccess) stats.ms_beam += ms;
       }
       stats.prof_steps = pev_used_;
     }
@@ -547,7 +553,7 @@ std::string Engine::vocab_logits_op(int rows, const float* out_dev, float* logit
   if (use_tc) {
     if (!vtc_.ready) return "tensor-core vocabulary path unavailable: " + vtc_why_;
     launch_round_tf32(out_dev, out_tf32_, (size_t)rows * H, st_);
-    vtc_.launch(rows, w_.proj_v, part_m_, part_s_, cand_v_, cand_i_, logits_dev, st_);
+    vtc_.launch(rows, w_.proj_v, part_m_, part_s_, gmax_, gstride_, logits_dev, st_);
   } else {
     GemmArgs g;
     g.A0 = out_dev; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;

@@ -1,21 +1,25 @@
 // Vocabulary projection on the 5th-generation tensor cores (tcgen05, kind::tf32) fused with the
-// softmax statistics and the candidate selection, plus the merge kernel that re-scores the candidates in
+// softmax statistics and the candidate selection, plus the final kernel that re-scores the candidates in
 // exact fp32, adds the copy distribution and emits the top-2K (model.py:228-238, 146-183, 280-285).
 //
 //   scores[r, w] = out[r, :] . w[:, w] + v[w]        r < R = articles x beam,  w < V
 //
 // The [R, V] logits are never written to HBM.  Per CTA: one 128-row block of `out` stays resident in
 // shared memory (TMA, 128B swizzle), vocabulary tiles of 128 words stream through a 4-stage TMA ring,
-// one elected thread issues tcgen05.mma into a double-buffered TMEM accumulator, and four epilogue warps
-// (thread == row) read it back with tcgen05.ld, add the bias and keep a running (max, sum exp) and a
-// sorted top-2K list per row.  Operands are tf32-rounded copies (round to nearest), so the tensor-core
-// logits carry ~1e-3 absolute noise: they are used ONLY to pick candidates and for the tail of the
-// log-sum-exp.  vocab_merge_kernel recomputes the logits of the candidates and of every word that occurs
-// in the article in fp32 from the unrounded operands, and corrects the sum for them.
+// one elected thread issues tcgen05.mma into a double-buffered TMEM accumulator, and eight epilogue warps
+// (thread == row) read it back with tcgen05.ld, add the bias, keep a running (max, sum exp) per row and
+// write the maximum of every group of 8 consecutive words.  Operands are tf32-rounded copies (round to
+// nearest), so the tensor-core logits carry ~1e-3 absolute noise: they are used ONLY to pick candidate
+// groups and for the tail of the log-sum-exp.  The top 2K elements of a row lie inside its top 2K groups (by
+// group maximum), so vocab_final_kernel takes the 2K+8 best groups per row and recomputes all their words
+// in fp32 from the unrounded operands (plus the tf32-emulated value the tensor core summed, to swap it out of
+// the sum of exponentials), adds the copy distribution and emits the top 2K; vocab_rescore_kernel supplies the
+// exact logits of every word that occurs in the article.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cfloat>
+#include <algorithm>
 #include <cstdint>
 #include <string>
 
@@ -26,11 +30,12 @@ namespace pgn {
 namespace {
 
 constexpr int BM = 128, BN = 128, BK = 32;          // tile: 128 rows x 128 words x 32 tf32 (= 128 bytes of K)
-constexpr int STAGES = 3;
+constexpr int STAGES = 4;
 constexpr int TILE_BYTES = 128 * 128;                // one [128 x 128B] operand tile
 constexpr int NTHREADS = 320;                        // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
 constexpr int EPI_THREADS = 256;
 constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+constexpr int GW = 8;                                // words per candidate group
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -102,30 +107,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-template <int K2MAX>
-__device__ __forceinline__ void cand_insert(float (&cv)[K2MAX], int (&ci)[K2MAX], float v, int i) {
-  // strictly greater: within a thread ids arrive in increasing order, so ties keep the lower id
-  if (!(v > cv[K2MAX - 1])) return;
-  cv[K2MAX - 1] = v; ci[K2MAX - 1] = i;
-#pragma unroll
-  for (int j = K2MAX - 1; j > 0; --j) {
-    if (cv[j] > cv[j - 1]) {
-      const float fv = cv[j]; cv[j] = cv[j - 1]; cv[j - 1] = fv;
-      const int fi = ci[j]; ci[j] = ci[j - 1]; ci[j - 1] = fi;
-    }
-  }
-}
-
 // ---------------------------------------------------------------------------------------------
-// GEMM + statistics + candidates.  grid = n_mblocks * n_ranges;  CTA (mb, range) handles the vocabulary
+// GEMM + softmax statistics + group maxima.  grid = n_mblocks * n_ranges;  CTA (mb, range) handles the vocabulary
 // tiles range, range + n_ranges, ...
 // ---------------------------------------------------------------------------------------------
-template <int K2MAX, bool STORE>
+template <bool STORE>
 __global__ void __launch_bounds__(NTHREADS, 1)
 vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const float* __restrict__ bias, int R, int V, int KB, int n_tiles, int n_mblocks, int n_ranges,
-                float* __restrict__ part_m, float* __restrict__ part_s, float* __restrict__ cand_v,
-                int* __restrict__ cand_i, float* __restrict__ logits_out) {
+                float* __restrict__ part_m, float* __restrict__ part_s, float4* __restrict__ gmax, int gstride,
+                float* __restrict__ logits_out) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   unsigned char* smA = smem;                                   // KB tiles
@@ -138,7 +129,6 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* t_empty = t_full + 2;        // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
   float* bias_s = reinterpret_cast<float*>(bars + 16);           // [8 epilogue warps][64], 16-byte aligned
-  float* xstage = bias_s + 8 * 64;                               // [8 epilogue warps][32 words][32 lanes]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mb = blockIdx.x % n_mblocks, range = blockIdx.x / n_mblocks;
@@ -206,10 +196,6 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int row = mb * BM + q * 32 + lane;
     float* bsm = bias_s + ew * 64;                             // warp-private bias staging
     float m_run = -FLT_MAX, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    float cv[K2MAX];
-    int ci[K2MAX];
-#pragma unroll
-    for (int j = 0; j < K2MAX; ++j) { cv[j] = -FLT_MAX; ci[j] = -1; }
     uint32_t tcount = 0;
     for (int tile = range; tile < n_tiles; tile += n_ranges, ++tcount) {
       const int acc = tcount & 1;
@@ -221,35 +207,40 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_wait(&t_full[acc], (tcount >> 1) & 1);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * 64);
-#pragma unroll 1
+      uint32_t raw0[32], raw1[32];
+      tmem_ld32(tbase, raw0);
+      tmem_ld_wait();
+      tmem_ld32(tbase + 32, raw1);                             // in flight while chunk 0 is processed
+#pragma unroll
       for (int c = 0; c < 2; ++c) {
-        uint32_t raw[32];
-        tmem_ld32(tbase + c * 32, raw);
-        tmem_ld_wait();
+        if (c == 1) tmem_ld_wait();
         const int n0 = nb + c * 32;
         float x[32];
-        float c0 = -FLT_MAX, c1 = -FLT_MAX, c2 = -FLT_MAX, c3 = -FLT_MAX;
+        float g[4];                                            // maxima of the 4 groups of 8 words of this chunk
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const float4 b4 = *reinterpret_cast<const float4*>(bsm + c * 32 + j);
-          x[j + 0] = fmaf(__uint_as_float(raw[j + 0]), kLog2e, b4.x);
-          x[j + 1] = fmaf(__uint_as_float(raw[j + 1]), kLog2e, b4.y);
-          x[j + 2] = fmaf(__uint_as_float(raw[j + 2]), kLog2e, b4.z);
-          x[j + 3] = fmaf(__uint_as_float(raw[j + 3]), kLog2e, b4.w);
+          x[j + 0] = fmaf(__uint_as_float(c == 0 ? raw0[j + 0] : raw1[j + 0]), kLog2e, b4.x);
+          x[j + 1] = fmaf(__uint_as_float(c == 0 ? raw0[j + 1] : raw1[j + 1]), kLog2e, b4.y);
+          x[j + 2] = fmaf(__uint_as_float(c == 0 ? raw0[j + 2] : raw1[j + 2]), kLog2e, b4.z);
+          x[j + 3] = fmaf(__uint_as_float(c == 0 ? raw0[j + 3] : raw1[j + 3]), kLog2e, b4.w);
           if (n0 + j + 3 >= V) {                               // only the last tile
             if (n0 + j + 0 >= V) x[j + 0] = -FLT_MAX;
             if (n0 + j + 1 >= V) x[j + 1] = -FLT_MAX;
             if (n0 + j + 2 >= V) x[j + 2] = -FLT_MAX;
             if (n0 + j + 3 >= V) x[j + 3] = -FLT_MAX;
           }
-          c0 = fmaxf(c0, x[j + 0]); c1 = fmaxf(c1, x[j + 1]); c2 = fmaxf(c2, x[j + 2]); c3 = fmaxf(c3, x[j + 3]);
+          const float m4 = fmaxf(fmaxf(x[j], x[j + 1]), fmaxf(x[j + 2], x[j + 3]));
+          if ((j & 7) == 0) g[j >> 3] = m4; else g[j >> 3] = fmaxf(g[j >> 3], m4);
         }
-        const float cm = fmaxf(fmaxf(c0, c1), fmaxf(c2, c3));
+        const float cm = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
         if (STORE) {
           if (row < R)
             for (int j = 0; j < 32; ++j)
               if (n0 + j < V) logits_out[(size_t)row * V + n0 + j] = x[j] * kLn2;
         }
+        if (row < R && n0 < V)                                 // lanes are consecutive rows: one 512-byte store per warp
+          gmax[(size_t)(n0 >> 5) * gstride + row] = make_float4(g[0], g[1], g[2], g[3]);
         if (cm > m_run) {
           const float f = exp2f(m_run - cm);
           s0 *= f; s1 *= f; s2 *= f; s3 *= f;
@@ -260,25 +251,6 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           s0 += exp2f(x[j + 0] - m_run); s1 += exp2f(x[j + 1] - m_run);
           s2 += exp2f(x[j + 2] - m_run); s3 += exp2f(x[j + 3] - m_run);
         }
-        // Candidates.  Lanes are different rows, so "does this word enter my list" is divergent; to keep the
-        // warp's trip count at max-over-lanes (not the union of positions) each lane first builds a bit mask of
-        // the words above its threshold, then walks its own set bits.
-        float thr = cv[K2MAX - 1];
-        if (cm > thr) {
-          float* xs = xstage + ew * 1024;
-          unsigned pass = 0u;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            xs[j * 32 + lane] = x[j];
-            pass |= (x[j] > thr) ? (1u << j) : 0u;
-          }
-          while (pass) {
-            const int j = __ffs(pass) - 1;
-            pass &= pass - 1;
-            const float v = xs[j * 32 + lane];
-            cand_insert<K2MAX>(cv, ci, v, n0 + j);
-          }
-        }
       }
       tc_fence_before();
       mbar_arrive(&t_empty[acc]);
@@ -287,8 +259,6 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const size_t pi = (size_t)(range * 2 + half) * R + row;
       part_m[pi] = m_run;
       part_s[pi] = (s0 + s1) + (s2 + s3);
-#pragma unroll
-      for (int j = 0; j < K2MAX; ++j) { cand_v[pi * K2MAX + j] = cv[j]; cand_i[pi * K2MAX + j] = ci[j]; }
     }
   }
   tc_fence_before();
@@ -305,15 +275,6 @@ __global__ void round_tf32_kernel(const float* __restrict__ in, float* __restric
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(in[i]));
   out[i] = __uint_as_float(r);
-}
-
-// ---------------------------------------------------------------------------------------------
-// Merge: one block per article.
-// ---------------------------------------------------------------------------------------------
-constexpr int MERGE_EXTRA = 8;      // approx candidates re-scored beyond 2K
-
-__device__ __forceinline__ bool better_vi(float v1, int i1, float v2, int i2) {
-  return v1 > v2 || (v1 == v2 && i1 < i2);
 }
 
 // exact fp32 logits of every distinct in-vocabulary word of the article, for the K rows of the article
@@ -363,191 +324,269 @@ vocab_rescore_kernel(MergeArgs a) {
   }
 }
 
-constexpr int MERGE_THREADS = 512;
-constexpr int MERGE_PPL = 10;       // candidate lists ("parts") per lane in the tournament: up to 320 parts
 
-template <int K2MAX>
-__global__ void __launch_bounds__(MERGE_THREADS)
-vocab_merge_kernel(MergeArgs a) {
+// ---------------------------------------------------------------------------------------------
+// Candidate groups of one decoder row + exact re-scoring of their words.  One block per row.
+// ---------------------------------------------------------------------------------------------
+constexpr int SEL_THREADS = 512, SEL_WARPS = SEL_THREADS / 32;
+
+__device__ __forceinline__ float tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+constexpr int SEL_PER_LANE = 16;    // group maxima per lane: 16 warps x 32 lanes x 16 = 8192 groups = 65536 words max
+
+// Order-preserving map float -> uint32 (larger float <=> larger key).
+__device__ __forceinline__ uint32_t f2ord(float x) {
+  const uint32_t b = __float_as_uint(x);
+  return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
+}
+
+// One block per beam row, after the tensor-core pass:
+//   1. the 2K+8 best groups of 8 words by group maximum (tf32 logits), found without shuffles: every lane sorts its
+//      16 group keys once, then one redux.max + one ballot per round; the 16 warps' winners are ranked by counting;
+//   2. exact fp32 logit (and the tf32-emulated one, to take the tensor-core value back out of the sum of
+//      exponentials) of the 8 words of every selected group;
+//   3. softmax denominator from the per-part (max, sum exp2) of the tensor-core pass, corrected by step 2;
+//   4. final distribution on candidates + the article's words (model.py:146-183), top-2K with tf.nn.top_k's tie
+//      rule (larger value, then lower id) -> topk_ids / topk_logp (model.py:284-285).
+__global__ void __launch_bounds__(SEL_THREADS)
+vocab_final_kernel(MergeArgs a) {
   extern __shared__ __align__(16) float sm[];
-  const int art = blockIdx.x;
+  const int r = blockIdx.x, art = r / a.K;
   if (!a.active[art]) return;
-  const int K = a.K, K2 = a.K2, H = a.H, V = a.V, T = a.T, NP = a.n_parts, R = a.R;
-  const int C = min(K2 + MERGE_EXTRA, NP * K2MAX);
+  const int V = a.V, H = a.H, G = a.G, T = a.T, NP = a.n_parts, R = a.R, NC = a.NC, K2 = a.K2;
+  const int nch = (V + 31) / 32, ng = nch * 4;
   const int nu = a.pointer_gen ? a.uniq_cnt[art] : 0;
-  const int nc = NP * K2MAX;                                    // approx candidates per row
-  constexpr int NW = MERGE_THREADS / 32;
-  float* outs = sm;                                             // [K][H]
-  float* Ms = outs + K * H;                                     // [K]   max, log2 domain
-  float* Ss = Ms + K;                                           // [K]   sum of exp(l - M)
-  float* apv = Ss + K;                                          // [K][nc] approx logits (log2 domain), per part descending
-  int* api = reinterpret_cast<int*>(apv + (size_t)K * nc);      // [K][nc]
-  int* sel_i = api + (size_t)K * nc;                            // [K][C]
-  float* sel_a = reinterpret_cast<float*>(sel_i + K * C);       // [K][C] approx logit (log2 domain)
-  float* sel_x = sel_a + K * C;                                 // [K][C] exact logit
-  float* finv = sel_x + K * C;                                  // [K][C + T]
-  int* fini = reinterpret_cast<int*>(finv + (size_t)K * (C + T));   // [K][C + T]
-  float* att = reinterpret_cast<float*>(fini + (size_t)K * (C + T));   // [K][T]  attention of the K rows
-  float* arl = att + (size_t)K * T;                             // [K][T]  exact logits of the article's words
-  int* pss = reinterpret_cast<int*>(arl + (size_t)K * T);       // [T + 1] pos_start
-  int* pls = pss + (T + 1);                                     // [T]     pos_list
-  int* uids = pls + T;                                          // [T]     uniq_ids
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int r0 = art * K;
   const int len = a.lens[art];
+  const int nf = NC + nu;
+  // vals [ng] is dead after stage 1; the final keys fin [NC + T] (u64) reuse its space
+  const int vwords = (max((ng + 3) & ~3, 2 * (NC + T)) + 3) & ~3;
+  float* vals = sm;                                 // [ng] group maxima of this row (log2 domain)
+  unsigned long long* fin = reinterpret_cast<unsigned long long*>(sm);        // [NC + T] (value, ~id) keys
+  float* outs = vals + vwords;                      // [H] decoder output, exact
+  float* outt = outs + H;                           // [H] the tf32-rounded copy the tensor core multiplied
+  unsigned long long* ck = reinterpret_cast<unsigned long long*>(outt + H);   // [16 warps][max(G, K2)] per-warp winners
+  float* pm = reinterpret_cast<float*>(ck + SEL_WARPS * G);                   // [NP] part maxima
+  float* ps = pm + NP;                              // [NP] part sums
+  float* att = ps + NP;                             // [T] attention of this row
+  float* arl = att + T;                             // [T] exact logits of the article's words
+  float* cx = arl + T;                              // [NC] exact logits of the candidates
+  float* ca = cx + NC;                              // [NC] tf32-emulated logits of the candidates
+  int* cid = reinterpret_cast<int*>(ca + NC);       // [NC] candidate word ids
+  int* pss = cid + NC;                              // [T + 1] pos_start
+  int* pls = pss + (T + 1);                         // [T] pos_list
+  int* uids = pls + T;                              // [T] uniq_ids
+  int* sel = uids + T;                              // [G] selected group ids
+  float* MS = reinterpret_cast<float*>(sel + G);    // [2] M (natural log domain), S
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // ---- A: stage everything this article needs in shared memory
-  for (int i = threadIdx.x; i < K * H; i += MERGE_THREADS) outs[i] = a.out[(size_t)r0 * H + i];
-#pragma unroll 4
-  for (int i = threadIdx.x; i < K * nc; i += MERGE_THREADS) {
-    const int k = i / nc, c = i - k * nc, pt = c / K2MAX, j = c - pt * K2MAX;
-    const size_t pi = ((size_t)pt * R + r0 + k) * K2MAX + j;
-    apv[i] = a.cand_v[pi];
-    api[i] = a.cand_i[pi];
+  // ---- 0: everything this row needs, one round of loads
+  for (int c = threadIdx.x; c < nch; c += SEL_THREADS)
+    *reinterpret_cast<float4*>(vals + 4 * c) = a.gmax[(size_t)c * a.gstride + r];
+  for (int h = threadIdx.x; h < H; h += SEL_THREADS) {
+    const float o = a.out[(size_t)r * H + h];
+    outs[h] = o;
+    outt[h] = tf32_rna(o);
+  }
+  for (int pt = threadIdx.x; pt < NP; pt += SEL_THREADS) {
+    pm[pt] = a.part_m[(size_t)pt * R + r];
+    ps[pt] = a.part_s[(size_t)pt * R + r];
   }
   if (nu > 0) {
-    for (int i = threadIdx.x; i < K * len; i += MERGE_THREADS) {
-      const int k = i / len, t = i - k * len;
-      att[k * T + t] = a.attn[(size_t)(r0 + k) * T + t];
+    for (int t = threadIdx.x; t < len; t += SEL_THREADS) {
+      att[t] = a.attn[(size_t)r * T + t];
+      pls[t] = a.pos_list[(size_t)art * T + t];
     }
-    for (int i = threadIdx.x; i < K * nu; i += MERGE_THREADS) {
-      const int k = i / nu, u = i - k * nu;
-      arl[k * T + u] = a.artl[(size_t)(r0 + k) * T + u];
+    for (int u = threadIdx.x; u < nu; u += SEL_THREADS) {
+      arl[u] = a.artl[(size_t)r * T + u];
+      uids[u] = a.uniq_ids[(size_t)art * T + u];
     }
-    for (int i = threadIdx.x; i <= nu; i += MERGE_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
-    for (int i = threadIdx.x; i < len; i += MERGE_THREADS) pls[i] = a.pos_list[(size_t)art * T + i];
-    for (int i = threadIdx.x; i < nu; i += MERGE_THREADS) uids[i] = a.uniq_ids[(size_t)art * T + i];
+    for (int i = threadIdx.x; i <= nu; i += SEL_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
   }
-  for (int k = warp; k < K; k += NW) {                          // combine the per-part (max, sum exp2)
-    float M = -FLT_MAX;
-    for (int pt = lane; pt < NP; pt += 32) M = fmaxf(M, a.part_m[(size_t)pt * R + r0 + k]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
-    float S = 0.f;
-    for (int pt = lane; pt < NP; pt += 32)
-      S += a.part_s[(size_t)pt * R + r0 + k] * exp2f(a.part_m[(size_t)pt * R + r0 + k] - M);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
-    if (lane == 0) { Ms[k] = M; Ss[k] = S; }
+  if (threadIdx.x < G) sel[threadIdx.x] = -1;
+  if (threadIdx.x < K2) {                           // defaults, overwritten by the winners in step 4
+    a.topk_ids[(size_t)r * K2 + threadIdx.x] = 0;
+    a.topk_logp[(size_t)r * K2 + threadIdx.x] = -INFINITY;
   }
   __syncthreads();
-  // ---- B: top-C approx candidates per row: every part's list is already sorted, so a C-round tournament over
-  // the list heads suffices (warp per row; lane owns parts lane, lane+32, ...)
-  for (int k = warp; k < K; k += NW) {
-    float hv[MERGE_PPL]; int hi[MERGE_PPL], hp[MERGE_PPL];
+
+  // ---- 1a: per-warp top-G groups.  A group maximum becomes one 32-bit key: the order-preserving bits of the value
+  // with the low 4 mantissa bits replaced by (15 - register slot); selection only has to be right to tf32
+  // precision, the candidates are re-scored exactly.
+  {
+    const int per_warp = (ng + SEL_WARPS - 1) / SEL_WARPS, base = warp * per_warp, wend = min(ng, base + per_warp);
+    uint32_t key[SEL_PER_LANE];
 #pragma unroll
-    for (int q = 0; q < MERGE_PPL; ++q) {
-      const int pt = lane + 32 * q;
-      hp[q] = 0;
-      hi[q] = pt < NP ? api[k * nc + pt * K2MAX] : -1;
-      hv[q] = pt < NP ? apv[k * nc + pt * K2MAX] : -FLT_MAX;
+    for (int j = 0; j < SEL_PER_LANE; ++j) {
+      const int i = base + j * 32 + lane;
+      const float x = i < wend ? vals[i] : -FLT_MAX;
+      key[j] = x > -FLT_MAX ? ((f2ord(x) & ~15u) | (uint32_t)(15 - j)) : 0u;
     }
-    for (int round = 0; round < C; ++round) {
-      float bv = -FLT_MAX; int bi = 0x7fffffff, bq = -1;
 #pragma unroll
-      for (int q = 0; q < MERGE_PPL; ++q)
-        if (hi[q] >= 0 && better_vi(hv[q], hi[q], bv, bi)) { bv = hv[q]; bi = hi[q]; bq = q; }
-      int bl = lane;
+    for (int k = 2; k <= SEL_PER_LANE; k <<= 1) {
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        const int ol = __shfl_xor_sync(0xffffffffu, bl, o);
-        if (better_vi(ov, oi, bv, bi)) { bv = ov; bi = oi; bl = ol; }
-      }
-      const bool found = bi != 0x7fffffff;
-      if (lane == 0) { sel_i[k * C + round] = found ? bi : -1; sel_a[k * C + round] = bv; }
-      if (found && lane == bl) {                                // the winning lane advances that list's head
+      for (int j = k >> 1; j > 0; j >>= 1) {
 #pragma unroll
-        for (int q = 0; q < MERGE_PPL; ++q) {
-          if (q == bq) {
-            const int pt = lane + 32 * q;
-            ++hp[q];
-            if (hp[q] < K2MAX) { hi[q] = api[k * nc + pt * K2MAX + hp[q]]; hv[q] = apv[k * nc + pt * K2MAX + hp[q]]; }
-            else hi[q] = -1;
+        for (int i = 0; i < SEL_PER_LANE; ++i) {
+          const int l = i ^ j;
+          if (l > i) {
+            const uint32_t hi = max(key[i], key[l]), lo = min(key[i], key[l]);
+            if ((i & k) == 0) { key[i] = hi; key[l] = lo; } else { key[i] = lo; key[l] = hi; }
           }
         }
       }
     }
+    for (int round = 0; round < G; ++round) {
+      const uint32_t m = __reduce_max_sync(0xffffffffu, key[0]);
+      const uint32_t ball = __ballot_sync(0xffffffffu, key[0] == m);
+      if (lane == __ffs(ball) - 1) {
+        const int j = 15 - (int)(m & 15u);
+        ck[warp * G + round] = m ? ((unsigned long long)m << 32) | (0xffffffffu - (uint32_t)(base + j * 32 + lane)) : 0ull;
+#pragma unroll
+        for (int q = 0; q + 1 < SEL_PER_LANE; ++q) key[q] = key[q + 1];
+        key[SEL_PER_LANE - 1] = 0u;
+      }
+    }
   }
   __syncthreads();
-  // ---- C: exact fp32 logits of the K*C (row, candidate) pairs (warp per pair)
-  for (int it = warp; it < K * C; it += NW) {
-    const int k = it / C, id = sel_i[it];
-    float acc = 0.f;
-    if (id >= 0) {
-      const float* wr = a.wT + (size_t)id * H;
-      for (int h = lane * 4; h < H; h += 128) {
-        const float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + h));
-        const float4 o4 = *reinterpret_cast<const float4*>(outs + k * H + h);
-        acc = fmaf(w4.x, o4.x, acc); acc = fmaf(w4.y, o4.y, acc); acc = fmaf(w4.z, o4.z, acc); acc = fmaf(w4.w, o4.w, acc);
+  // ---- 1b: the 16 x G winners ranked by counting (keys are unique: they carry the group id); meanwhile the last
+  // warp combines the per-part softmax statistics of the tensor-core pass
+  if (threadIdx.x < SEL_WARPS * G) {
+    const unsigned long long mine = ck[threadIdx.x];
+    if (mine) {
+      int rank = 0;
+#pragma unroll 8
+      for (int e = 0; e < SEL_WARPS * G; ++e) rank += ck[e] > mine;
+      if (rank < G) sel[rank] = (int)(0xffffffffu - (uint32_t)mine);
+    }
+  }
+  if (warp == SEL_WARPS - 1) {
+    float M2 = -FLT_MAX;
+    for (int pt = lane; pt < NP; pt += 32) M2 = fmaxf(M2, pm[pt]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) M2 = fmaxf(M2, __shfl_xor_sync(0xffffffffu, M2, o));
+    float S = 0.f;
+    for (int pt = lane; pt < NP; pt += 32) S += ps[pt] * exp2f(pm[pt] - M2);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+    if (lane == 0) { MS[0] = M2 * kLn2; MS[1] = S; }
+  }
+  __syncthreads();
+  // ---- 2: exact fp32 logit and tf32-emulated logit of every word of the selected groups: warp per word, 4 in flight
+  const int nw = G * GW;
+  for (int it0 = warp * 4; it0 < nw; it0 += SEL_WARPS * 4) {
+    float4 w4[4][2];
+    int ids[4];
+    float bb[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int it = it0 + u;
+      const int grp = it < nw ? sel[it / GW] : -1;
+      const int id = grp >= 0 ? grp * GW + (it % GW) : -1;
+      ids[u] = (id >= 0 && id < V) ? id : -1;
+      bb[u] = ids[u] >= 0 ? __ldg(a.bias + ids[u]) : 0.f;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int h = lane * 4 + hh * 128;
+        w4[u][hh] = (ids[u] >= 0 && h < H) ? __ldg(reinterpret_cast<const float4*>(a.wT + (size_t)ids[u] * H + h))
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) sel_x[it] = id >= 0 ? acc + a.bias[id] : -FLT_MAX;
+    for (int u = 0; u < 4; ++u) {
+      float ex = 0.f, em = 0.f;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int h = lane * 4 + hh * 128;
+        if (h < H) {
+          const float4 o4 = *reinterpret_cast<const float4*>(outs + h);
+          const float4 t4 = *reinterpret_cast<const float4*>(outt + h);
+          const float4 w = w4[u][hh];
+          ex = fmaf(w.x, o4.x, ex); ex = fmaf(w.y, o4.y, ex); ex = fmaf(w.z, o4.z, ex); ex = fmaf(w.w, o4.w, ex);
+          em = fmaf(tf32_rna(w.x), t4.x, em); em = fmaf(tf32_rna(w.y), t4.y, em);
+          em = fmaf(tf32_rna(w.z), t4.z, em); em = fmaf(tf32_rna(w.w), t4.w, em);
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { ex += __shfl_xor_sync(0xffffffffu, ex, o); em += __shfl_xor_sync(0xffffffffu, em, o); }
+      const int it = it0 + u;
+      if (lane == 0 && it < nw) {
+        const int id = ids[u];
+        cid[it] = id;
+        cx[it] = id >= 0 ? ex + bb[u] : -FLT_MAX;
+        ca[it] = id >= 0 ? em + bb[u] : -FLT_MAX;
+      }
+    }
   }
   __syncthreads();
-  // ---- D: exact values replace the tensor-core ones inside the sum of exponentials; M stays the tf32 maximum
-  if (threadIdx.x < K) {
-    const int k = threadIdx.x;
-    float S = Ss[k];
-    const float M2 = Ms[k], M = M2 * kLn2;
-    for (int c = 0; c < C; ++c)
-      if (sel_i[k * C + c] >= 0) S += expf(sel_x[k * C + c] - M) - exp2f(sel_a[k * C + c] - M2);
-    Ss[k] = S;
+  // ---- 3: swap the tensor-core value of every re-scored word for its exact value inside the sum
+  if (warp == 0) {
+    const float M = MS[0];
+    float S = 0.f;
+    for (int c = lane; c < NC; c += 32)
+      if (cid[c] >= 0) S += expf(cx[c] - M) - expf(ca[c] - M);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+    if (lane == 0) MS[1] += S;
   }
   __syncthreads();
-  // ---- E: final distribution on the candidate set (model.py:158-181)
-  const int nf = C + nu;
-  for (int i = threadIdx.x; i < K * nf; i += MERGE_THREADS) {
-    const int k = i / nf, c = i - k * nf;
-    const int r = r0 + k;
-    const float M = Ms[k] * kLn2, S = Ss[k];
+  // ---- 4a: final distribution on the candidate set (model.py:158-181) as (value, ~id) keys
+  {
+    const float M = MS[0], S = MS[1];
     const float pg = a.pointer_gen ? a.pgen[r] : 1.f;
-    float val = -FLT_MAX; int id = -1;
-    if (c < C) {
-      id = sel_i[k * C + c];
-      if (id >= 0) {
-        int lo = 0, hi2 = nu;                                   // article words are handled below with their copy mass
-        while (lo < hi2) { const int mid = (lo + hi2) >> 1; if (uids[mid] < id) lo = mid + 1; else hi2 = mid; }
-        if (lo < nu && uids[lo] == id) id = -1;
-        else val = a.pointer_gen ? pg * (expf(sel_x[k * C + c] - M) / S) : expf(sel_x[k * C + c] - M) / S;
+    for (int c = threadIdx.x; c < nf; c += SEL_THREADS) {
+      float val = -FLT_MAX; int id = -1;
+      if (c < NC) {
+        id = cid[c];
+        if (id >= 0) {
+          int lo = 0, hi2 = nu;                                 // article words are handled below with their copy mass
+          while (lo < hi2) { const int mid = (lo + hi2) >> 1; if (uids[mid] < id) lo = mid + 1; else hi2 = mid; }
+          if (lo < nu && uids[lo] == id) id = -1;
+          else val = a.pointer_gen ? pg * (expf(cx[c] - M) / S) : expf(cx[c] - M) / S;
+        }
+      } else {
+        const int u = c - NC;
+        id = uids[u];
+        const float omp = 1.0f - pg;
+        float copy = 0.f;
+        for (int qq = pss[u]; qq < pss[u + 1]; ++qq) copy += omp * att[pls[qq]];   // scatter_nd: duplicates accumulate in t order
+        const float vocab = id < V ? pg * (expf(arl[u] - M) / S) : 0.f;
+        val = vocab + copy;
       }
-    } else {
-      const int u = c - C;
-      id = uids[u];
-      const float omp = 1.0f - pg;
-      float copy = 0.f;
-      for (int qq = pss[u]; qq < pss[u + 1]; ++qq) copy += omp * att[k * T + pls[qq]];   // scatter_nd: duplicates accumulate in t order
-      const float vocab = id < V ? pg * (expf(arl[k * T + u] - M) / S) : 0.f;
-      val = vocab + copy;
+      fin[c] = id >= 0 ? ((unsigned long long)f2ord(val) << 32) | (0xffffffffu - (uint32_t)id) : 0ull;
     }
-    finv[i] = val; fini[i] = id;
   }
   __syncthreads();
-  // ---- F: top-2K with the tf.nn.top_k tie rule (warp per row)
-  for (int k = warp; k < K; k += NW) {
-    const int r = r0 + k;
+  // ---- 4b: per-warp top-2K over a contiguous sixteenth of the keys, then ranking by counting
+  {
+    const int cw = (nf + SEL_WARPS - 1) / SEL_WARPS, c0 = warp * cw, c1 = min(nf, c0 + cw);
     for (int round = 0; round < K2; ++round) {
-      float bv = -FLT_MAX; int bi = 0x7fffffff, bp = -1;
-      for (int c = lane; c < nf; c += 32) {
-        const int id = fini[k * nf + c];
-        if (id >= 0 && better_vi(finv[k * nf + c], id, bv, bi)) { bv = finv[k * nf + c]; bi = id; bp = c; }
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        const int op = __shfl_xor_sync(0xffffffffu, bp, o);
-        if (better_vi(ov, oi, bv, bi)) { bv = ov; bi = oi; bp = op; }
-      }
-      if (lane == 0) {
-        a.topk_ids[(size_t)r * K2 + round] = bp >= 0 ? bi : 0;
-        a.topk_logp[(size_t)r * K2 + round] = bp >= 0 ? logf(bv) : -INFINITY;   // model.py:285
-        if (bp >= 0) fini[k * nf + bp] = -1;
-      }
+      unsigned long long best = 0ull; int bp = -1;
+      for (int c = c0 + lane; c < c1; c += 32) { const unsigned long long k = fin[c]; if (k > best) { best = k; bp = c; } }
+      const uint32_t hi = __reduce_max_sync(0xffffffffu, (uint32_t)(best >> 32));
+      const uint32_t lo = __reduce_max_sync(0xffffffffu, (uint32_t)(best >> 32) == hi ? (uint32_t)best : 0u);
+      const bool win = best != 0ull && (uint32_t)(best >> 32) == hi && (uint32_t)best == lo;
+      if (win) fin[bp] = 0ull;
+      if (lane == 0) ck[warp * K2 + round] = ((unsigned long long)hi << 32) | lo;
       __syncwarp();
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < SEL_WARPS * K2) {
+    const unsigned long long mine = ck[threadIdx.x];
+    if (mine >> 32) {
+      int rank = 0;
+#pragma unroll 8
+      for (int e = 0; e < SEL_WARPS * K2; ++e) rank += ck[e] > mine;
+      if (rank < K2) {
+        const uint32_t o = (uint32_t)(mine >> 32);
+        const float v = __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu));
+        a.topk_ids[(size_t)r * K2 + rank] = (int)(0xffffffffu - (uint32_t)mine);
+        a.topk_logp[(size_t)r * K2 + rank] = logf(v);            // model.py:285
+      }
     }
   }
 }
@@ -570,14 +609,15 @@ std::string make_map(EncodeTiledFn fn, CUtensorMap* map, const float* base, int 
 
 }  // namespace
 
-size_t VocabTC::smem_bytes() const { return (size_t)(KB + STAGES) * TILE_BYTES + 1024 + 256 + 8 * 64 * 4 + 8 * 1024 * 4; }
+size_t VocabTC::smem_bytes() const { return (size_t)(KB + STAGES) * TILE_BYTES + 1024 + 256 + 8 * 64 * 4; }
 
 std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out_tf32, int Rcap, int K2_, int n_sms) {
   V = V_; H = H_; K2 = K2_;
   if (H % BK != 0 || H > 256) return "tensor-core vocabulary path needs hidden_dim % 32 == 0 and <= 256";
   if (K2 > 16) return "tensor-core vocabulary path needs beam_size <= 8";
+  if (V > SEL_WARPS * 32 * SEL_PER_LANE * GW) return "tensor-core vocabulary path needs vocab_size <= 65536";
   KB = H / BK;
-  K2MAX = K2 <= 8 ? 8 : 16;
+  G = K2 + 8;                                          // candidate groups per row: the top 2K lie in the top 2K groups
   n_tiles = (V + BN - 1) / BN;
   sms = n_sms;
   void* fnp = nullptr;
@@ -588,9 +628,8 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
   std::string err = make_map(fn, &tmA, out_tf32, Rcap, H);
   if (err.empty()) err = make_map(fn, &tmB, wT_tf32, V, H);
   if (!err.empty()) return err;
-  cudaError_t e = cudaFuncSetAttribute(vocab_tc_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_tc_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_tc_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
+  cudaError_t e = cudaFuncSetAttribute(vocab_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(vocab_tc_kernel): ") + cudaGetErrorString(e);
   ready = true;
   return "";
@@ -599,37 +638,21 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
 void VocabTC::plan(int R, int* n_mblocks, int* n_ranges) const {
   *n_mblocks = (R + BM - 1) / BM;
   int nr = sms / *n_mblocks;
-  // the merge kernel stages every candidate list of an article in shared memory: K rows x 2 parts per range x K2MAX
-  // entries x 8 bytes.  Keep that below ~96 KB (only binds for wide beams on small batches).
-  const int K = K2 / 2 > 0 ? K2 / 2 : 1;
-  const int cap = (96 * 1024) / (16 * K * K2MAX);
-  if (nr > cap) nr = cap;
   if (nr < 1) nr = 1;
   if (nr > n_tiles) nr = n_tiles;
   *n_ranges = nr;
 }
 
-int VocabTC::launch(int R, const float* bias, float* part_m, float* part_s, float* cand_v, int* cand_i,
+int VocabTC::launch(int R, const float* bias, float* part_m, float* part_s, float4* gmax, int gstride,
                     float* logits_dbg, cudaStream_t st) const {
   int nmb, nr;
   plan(R, &nmb, &nr);
   dim3 grid(nmb * nr);
   if (logits_dbg)
-    vocab_tc_kernel<8, true><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, cand_v, cand_i, logits_dbg);
-  else if (K2MAX == 8)
-    vocab_tc_kernel<8, false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, cand_v, cand_i, nullptr);
+    vocab_tc_kernel<true><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, gmax, gstride, logits_dbg);
   else
-    vocab_tc_kernel<16, false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, cand_v, cand_i, nullptr);
+    vocab_tc_kernel<false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, gmax, gstride, nullptr);
   return 1;
-}
-
-size_t VocabTC::merge_smem(int K, int T, int n_parts) const {
-  const int nc = n_parts * K2MAX;
-  int C = K2 + MERGE_EXTRA;
-  if (C > nc) C = nc;
-  size_t fl = (size_t)K * H + 2 * K + 2 * (size_t)K * nc + 3 * (size_t)K * C + 2 * (size_t)K * (C + T) +
-              2 * (size_t)K * T + 3 * (size_t)T + 1;
-  return fl * 4 + 64;
 }
 
 int VocabTC::launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const {
@@ -639,17 +662,23 @@ int VocabTC::launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const {
   return 1;
 }
 
-int VocabTC::launch_merge(MergeArgs a, int B, cudaStream_t st) const {
-  a.K2MAX = K2MAX;
-  const size_t smem = merge_smem(a.K, a.T, a.n_parts);
-  static size_t set8 = 0, set16 = 0;
-  if (K2MAX == 8) {
-    if (smem > 48 * 1024 && smem > set8) { cudaFuncSetAttribute(vocab_merge_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); set8 = smem; }
-    vocab_merge_kernel<8><<<B, MERGE_THREADS, smem, st>>>(a);
-  } else {
-    if (smem > 48 * 1024 && smem > set16) { cudaFuncSetAttribute(vocab_merge_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); set16 = smem; }
-    vocab_merge_kernel<16><<<B, MERGE_THREADS, smem, st>>>(a);
+size_t VocabTC::final_smem(int T, int n_parts) const {
+  const int ng = ((V + 31) / 32) * 4, NC = G * GW;
+  const size_t vwords = (size_t)(std::max((ng + 3) & ~3, 2 * (NC + T)) + 3) & ~(size_t)3;
+  return (vwords + 2 * (size_t)H + 2 * (size_t)SEL_WARPS * G + 2 * (size_t)n_parts + 2 * (size_t)T + 3 * (size_t)NC +
+          (3 * (size_t)T + 1) + G + 2) * sizeof(float);
+}
+
+int VocabTC::launch_final(const MergeArgs& a, cudaStream_t st) const {
+  const size_t smem = final_smem(a.T, a.n_parts);
+  static size_t set[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (smem > 48 * 1024 && smem > set[dev & 63]) {
+    cudaFuncSetAttribute(vocab_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    set[dev & 63] = smem;
   }
+  vocab_final_kernel<<<a.R, SEL_THREADS, smem, st>>>(a);
   return 1;
 }
 

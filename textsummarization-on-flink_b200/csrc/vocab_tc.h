@@ -1,5 +1,5 @@
-// Tensor-core (tcgen05, tf32) vocabulary projection fused with softmax statistics and candidate
-// selection, and the exact-fp32 merge kernel.  See vocab_tc.cu.
+// Tensor-core (tcgen05, tf32) vocabulary projection fused with softmax statistics and candidate-group maxima, the
+// per-row group selection + exact re-scoring, and the merge kernel.  See vocab_tc.cu.
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -12,14 +12,14 @@ struct MergeArgs {
   const float* out;        // [R, H] unrounded decoder outputs
   const float* wT;         // [V, H] unrounded output_projection/w (transposed)
   const float* bias;       // [V]
-  const float* part_m; const float* part_s;      // [n_parts, R]   log2 domain (max, sum exp2)
-  const float* cand_v; const int* cand_i;        // [n_parts, R, K2MAX]   log2-domain tf32 logits
+  const float* part_m; const float* part_s;      // [n_parts, R]   log2 domain (max, sum exp2) of the tf32 logits
+  const float4* gmax; int gstride;               // [ceil(V/32), gstride] maxima of the 4 groups of 8 words of each chunk
   float* artl;                                   // [R, T] exact logits of the article's distinct words
   const float* pgen; const float* attn;          // [R], [R, T]
   const int* uniq_ids; const int* uniq_cnt; const int* pos_start; const int* pos_list;
   const int* active; const int* lens;
   int* topk_ids; float* topk_logp;               // [R, 2K]
-  int K, K2, K2MAX, H, V, T, R, n_parts, pointer_gen;
+  int K, K2, G, NC, H, V, T, R, n_parts, pointer_gen;
 };
 
 class VocabTC {
@@ -28,14 +28,14 @@ class VocabTC {
   // addresses stay fixed (they are baked into the TMA descriptors).
   std::string init(const float* wT_tf32, int V, int H, const float* out_tf32, int Rcap, int K2, int n_sms);
   void plan(int R, int* n_mblocks, int* n_ranges) const;
-  int launch(int R, const float* bias, float* part_m, float* part_s, float* cand_v, int* cand_i,
-             float* logits_dbg, cudaStream_t st) const;
-  int launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const;
-  int launch_merge(MergeArgs a, int B, cudaStream_t st) const;
+  int launch(int R, const float* bias, float* part_m, float* part_s, float4* gmax, int gstride, float* logits_dbg,
+             cudaStream_t st) const;
+  int launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const;     // article words
+  int launch_final(const MergeArgs& a, cudaStream_t st) const;              // candidates, final distribution, top-2K
   size_t smem_bytes() const;
-  size_t merge_smem(int K, int T, int n_parts) const;
+  size_t final_smem(int T, int n_parts) const;
   bool ready = false;
-  int K2MAX = 8;
+  int G = 16;                       // candidate groups (of 8 words) re-scored per row = 2K + 8
 
  private:
   CUtensorMap tmA, tmB;

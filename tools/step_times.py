@@ -20,5 +20,5 @@ with native.Decoder(flags) as dec:
         dec.stage_upload(*b0); dec.stage_run(); dec.stage_sync()
         st = dec.stats()
         n = max(1.0, st["prof_steps"])
-        print(opt, "encoder %.3f ms decoder %.3f ms | per step: attention %.1f us, vocab gemm %.1f us (steps %d)" % (
-            st["ms_encoder"], st["ms_decoder"], 1e3 * st["ms_attention"] / n, 1e3 * st["ms_vocab"] / n, n))
+        print(opt, "encoder %.3f ms decoder %.3f ms | per step: attention %.1f us, vocab gemm %.1f us, select+merge %.1f us (steps %d)" % (
+            st["ms_encoder"], st["ms_decoder"], 1e3 * st["ms_attention"] / n, 1e3 * st["ms_vocab"] / n, 1e3 * st["ms_select"] / n, n))
