@@ -29,9 +29,10 @@ namespace pgn {
 
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 32;          // tile: 128 rows x 128 words x 32 tf32 (= 128 bytes of K)
+constexpr int BM = 128, BN = 256, BK = 32;          // CTA-pair tile: 2 x 128 rows, 256 words (128 staged per CTA), 32 tf32 of K
+constexpr int BNH = BN / 2;                          // words of a tile staged by each CTA of the pair
 constexpr int STAGES = 4;
-constexpr int TILE_BYTES = 128 * 128;                // one [128 x 128B] operand tile
+constexpr int TILE_BYTES = 128 * 128;                // one [128 rows x 128 B] operand tile (A row block or B half tile)
 constexpr int NTHREADS = 320;                        // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
 constexpr int EPI_THREADS = 256;
 constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
@@ -44,9 +45,6 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -63,22 +61,37 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (++spins > (1u << 26)) __trap();              // a protocol bug becomes an error, not a hang
   }
 }
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+// TMA load issued by either CTA of a pair into its own shared memory, completing on a barrier that may live in the
+// other CTA (a shared::cluster address from mapa)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1) : "memory");
 }
-// D[tmem] (+)= A[smem] . B[smem]^T, one 128 x 128 x 8 tf32 MMA
-__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+__device__ __forceinline__ uint32_t mapa_rank(const void* p, uint32_t rank) {     // same offset in CTA `rank` of the cluster
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrives on the same barrier of both CTAs of the pair once every MMA issued so far has retired
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+// D[tmem of both CTAs] (+)= A[smem, 128 rows per CTA] . B[smem, 128 words per CTA]^T: one 256 x 256 x 8 tf32 MMA
+__device__ __forceinline__ void tc_mma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 // K-major operand tile with 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart.
@@ -91,8 +104,8 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   d |= (uint64_t)2 << 61;                            // SWIZZLE_128B
   return d;
 }
-// instruction descriptor: D fp32, A/B tf32, both K-major, M = 128, N = 128
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// instruction descriptor: D fp32, A/B tf32, both K-major, M = 256 (pair), N = 256
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
 
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
@@ -105,72 +118,86 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ float ex2_ftz(float x) {           // one MUFU.EX2, no denormal fix-up: tiny terms may flush to 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------
-// GEMM + softmax statistics + group maxima.  grid = n_mblocks * n_ranges;  CTA (mb, range) handles the vocabulary
-// tiles range, range + n_ranges, ...
+// GEMM + softmax statistics + group maxima.  One cluster = one CTA pair (cta_group::2): CTA `crank` keeps row block
+// 2 * mp + crank of `out` resident and stages words [crank * 128, crank * 128 + 128) of every 256-word tile, so
+// that each byte of the projection matrix is delivered to exactly one SM and each SM's tensor core reads only
+// half of B from its own shared memory.  The leader (rank 0) issues the MMAs for both; both run an epilogue on
+// their own 128 rows.  grid = 2 * n_mpairs * n_ranges;  pair (mp, range) handles tiles range, range + n_ranges, ...
 // ---------------------------------------------------------------------------------------------
 template <bool STORE>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                const float* __restrict__ bias, int R, int V, int KB, int n_tiles, int n_mblocks, int n_ranges,
+                const float* __restrict__ bias, int R, int V, int KB, int n_tiles, int n_mpairs, int n_ranges,
                 float* __restrict__ part_m, float* __restrict__ part_s, float4* __restrict__ gmax, int gstride,
                 float* __restrict__ logits_out) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   unsigned char* smA = smem;                                   // KB tiles
-  unsigned char* smB = smem + (size_t)KB * TILE_BYTES;         // STAGES tiles
+  unsigned char* smB = smem + (size_t)KB * TILE_BYTES;         // STAGES half tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(smB + (size_t)STAGES * TILE_BYTES);
-  uint64_t* full = bars;                 // [STAGES]
-  uint64_t* empty = bars + STAGES;       // [STAGES]
-  uint64_t* a_full = bars + 2 * STAGES;  // [1]
-  uint64_t* t_full = a_full + 1;         // [2]
-  uint64_t* t_empty = t_full + 2;        // [2]
+  uint64_t* full = bars;                 // [STAGES]  leader's: both CTAs' halves have landed
+  uint64_t* empty = bars + STAGES;       // [STAGES]  each CTA's: the MMAs reading the stage have retired
+  uint64_t* a_full = bars + 2 * STAGES;  // [1]       leader's: both row blocks have landed
+  uint64_t* t_full = a_full + 1;         // [2]       each CTA's: accumulator complete
+  uint64_t* t_empty = t_full + 2;        // [2]       leader's: both CTAs' epilogues have drained the accumulator
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
-  float* bias_s = reinterpret_cast<float*>(bars + 16);           // [8 epilogue warps][64], 16-byte aligned
+  float* bias_s = reinterpret_cast<float*>(bars + 16);           // [8 epilogue warps][128], 16-byte aligned
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int mb = blockIdx.x % n_mblocks, range = blockIdx.x / n_mblocks;
+  uint32_t crank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+  const int pair = blockIdx.x >> 1;
+  const int mp = pair % n_mpairs, range = pair / n_mpairs;
+  const int mb = mp * 2 + (int)crank;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(a_full, 1);
-    for (int a = 0; a < 2; ++a) { mbar_init(&t_full[a], 1); mbar_init(&t_empty[a], EPI_THREADS); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&t_full[a], 1); mbar_init(&t_empty[a], 2 * (EPI_THREADS / 32)); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) {                                             // TMEM: 2 accumulators x 128 columns
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  if (warp == 1) {                                             // TMEM: 2 accumulators x 256 columns, in both CTAs
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
   }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();                                          // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (both CTAs; completion is signalled on the leader's barriers) =====
     if (lane == 0) {
-      mbar_expect_tx(a_full, (uint32_t)KB * TILE_BYTES);
-      for (int kb = 0; kb < KB; ++kb) tma_load_2d(smA + (size_t)kb * TILE_BYTES, &tmA, a_full, kb * BK, mb * BM);
+      if (crank == 0) mbar_expect_tx(a_full, 2u * (uint32_t)KB * TILE_BYTES);
+      const uint32_t a_full_l = mapa_rank(a_full, 0);
+      for (int kb = 0; kb < KB; ++kb) tma_load_2d_pair(smA + (size_t)kb * TILE_BYTES, &tmA, a_full_l, kb * BK, mb * BM);
       uint32_t it = 0;
       for (int tile = range; tile < n_tiles; tile += n_ranges) {
         for (int kb = 0; kb < KB; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
-          mbar_expect_tx(&full[s], TILE_BYTES);
-          tma_load_2d(smB + (size_t)s * TILE_BYTES, &tmB, &full[s], kb * BK, tile * BN);
+          if (crank == 0) mbar_expect_tx(&full[s], 2u * TILE_BYTES);
+          tma_load_2d_pair(smB + (size_t)s * TILE_BYTES, &tmB, mapa_rank(&full[s], 0), kb * BK, tile * BN + (int)crank * BNH);
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer (leader only) =====
+    if (lane == 0 && crank == 0) {
       mbar_wait(a_full, 0);
       uint32_t it = 0, tcount = 0;
       for (int tile = range; tile < n_tiles; tile += n_ranges, ++tcount) {
         const int acc = tcount & 1;
-        mbar_wait(&t_empty[acc], ((tcount >> 1) & 1) ^ 1);     // epilogue has drained this accumulator
+        mbar_wait(&t_empty[acc], ((tcount >> 1) & 1) ^ 1);     // both epilogues have drained this accumulator
         tc_fence_after();
         for (int kb = 0; kb < KB; ++kb, ++it) {
           const int s = it % STAGES;
@@ -180,58 +207,60 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint64_t bd = smem_desc_sw128(smem_u32(smB + (size_t)s * TILE_BYTES));
 #pragma unroll
           for (int k4 = 0; k4 < 4; ++k4)                       // 4 x (K = 8 tf32 = 32 bytes) inside the swizzle atom
-            tc_mma_tf32(tmem_base + acc * BN, ad + (uint64_t)(k4 * 2), bd + (uint64_t)(k4 * 2), kIdesc, (kb | k4) != 0);
-          tc_commit(&empty[s]);                                // frees the stage when these MMAs retire
+            tc_mma_tf32_pair(tmem_base + acc * BN, ad + (uint64_t)(k4 * 2), bd + (uint64_t)(k4 * 2), kIdesc, (kb | k4) != 0);
+          tc_commit_pair(&empty[s]);                           // frees the stage in both CTAs when these MMAs retire
         }
-        tc_commit(&t_full[acc]);                               // accumulator complete
+        tc_commit_pair(&t_full[acc]);                          // accumulator complete, in both CTAs
       }
     }
   } else {
-    // ===== epilogue: thread == row, two warps per TMEM lane quarter, each taking 64 of the tile's 128 words.
+    // ===== epilogue: thread == row, two warps per TMEM lane quarter, each taking 128 of the tile's 256 words.
     // Everything runs in the log2 domain (x2 = logit * log2 e) so that one FFMA applies the bias and one
     // MUFU.EX2 gives the exponential.
     const int ew = warp - 2;                                   // 0..7
     const int q = warp & 3;                                    // TMEM lane quarter this warp may read
-    const int half = ew >> 2;                                  // which 64 words of the tile
+    const int half = ew >> 2;                                  // which 128 words of the tile
     const int row = mb * BM + q * 32 + lane;
-    float* bsm = bias_s + ew * 64;                             // warp-private bias staging
+    float* bsm = bias_s + ew * 128;                            // warp-private bias staging
+    const uint32_t t_empty_l0 = mapa_rank(&t_empty[0], 0), t_empty_l1 = mapa_rank(&t_empty[1], 0);
     float m_run = -FLT_MAX, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     uint32_t tcount = 0;
     for (int tile = range; tile < n_tiles; tile += n_ranges, ++tcount) {
       const int acc = tcount & 1;
-      const int nb = tile * BN + half * 64;
+      const int nb = tile * BN + half * 128;
       __syncwarp();
-      bsm[lane] = (nb + lane < V) ? __ldg(bias + nb + lane) * kLog2e : 0.f;
-      bsm[lane + 32] = (nb + 32 + lane < V) ? __ldg(bias + nb + 32 + lane) * kLog2e : 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        bsm[lane + 32 * i] = (nb + 32 * i + lane < V) ? __ldg(bias + nb + 32 * i + lane) * kLog2e : 0.f;
       __syncwarp();
       mbar_wait(&t_full[acc], (tcount >> 1) & 1);
       tc_fence_after();
-      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * 64);
-      uint32_t raw0[32], raw1[32];
-      tmem_ld32(tbase, raw0);
-      tmem_ld_wait();
-      tmem_ld32(tbase + 32, raw1);                             // in flight while chunk 0 is processed
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * 128);
+      uint32_t raw[2][32];
+      tmem_ld32(tbase, raw[0]);
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        if (c == 1) tmem_ld_wait();
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld_wait();
+        if (c < 3) tmem_ld32(tbase + 32 * (c + 1), raw[(c + 1) & 1]);      // in flight while chunk c is processed
         const int n0 = nb + c * 32;
         float x[32];
         float g[4];                                            // maxima of the 4 groups of 8 words of this chunk
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const float4 b4 = *reinterpret_cast<const float4*>(bsm + c * 32 + j);
-          x[j + 0] = fmaf(__uint_as_float(c == 0 ? raw0[j + 0] : raw1[j + 0]), kLog2e, b4.x);
-          x[j + 1] = fmaf(__uint_as_float(c == 0 ? raw0[j + 1] : raw1[j + 1]), kLog2e, b4.y);
-          x[j + 2] = fmaf(__uint_as_float(c == 0 ? raw0[j + 2] : raw1[j + 2]), kLog2e, b4.z);
-          x[j + 3] = fmaf(__uint_as_float(c == 0 ? raw0[j + 3] : raw1[j + 3]), kLog2e, b4.w);
-          if (n0 + j + 3 >= V) {                               // only the last tile
-            if (n0 + j + 0 >= V) x[j + 0] = -FLT_MAX;
-            if (n0 + j + 1 >= V) x[j + 1] = -FLT_MAX;
-            if (n0 + j + 2 >= V) x[j + 2] = -FLT_MAX;
-            if (n0 + j + 3 >= V) x[j + 3] = -FLT_MAX;
-          }
-          const float m4 = fmaxf(fmaxf(x[j], x[j + 1]), fmaxf(x[j + 2], x[j + 3]));
-          if ((j & 7) == 0) g[j >> 3] = m4; else g[j >> 3] = fmaxf(g[j >> 3], m4);
+          x[j + 0] = fmaf(__uint_as_float(raw[c & 1][j + 0]), kLog2e, b4.x);
+          x[j + 1] = fmaf(__uint_as_float(raw[c & 1][j + 1]), kLog2e, b4.y);
+          x[j + 2] = fmaf(__uint_as_float(raw[c & 1][j + 2]), kLog2e, b4.z);
+          x[j + 3] = fmaf(__uint_as_float(raw[c & 1][j + 3]), kLog2e, b4.w);
+        }
+        if (n0 + 32 > V) {                                     // only in the last tile
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (n0 + j >= V) x[j] = -FLT_MAX;
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          g[j >> 3] = fmaxf(fmaxf(fmaxf(x[j], x[j + 1]), fmaxf(x[j + 2], x[j + 3])),
+                            fmaxf(fmaxf(x[j + 4], x[j + 5]), fmaxf(x[j + 6], x[j + 7])));
         }
         const float cm = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
         if (STORE) {
@@ -242,18 +271,19 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         if (row < R && n0 < V)                                 // lanes are consecutive rows: one 512-byte store per warp
           gmax[(size_t)(n0 >> 5) * gstride + row] = make_float4(g[0], g[1], g[2], g[3]);
         if (cm > m_run) {
-          const float f = exp2f(m_run - cm);
+          const float f = ex2_ftz(m_run - cm);
           s0 *= f; s1 *= f; s2 *= f; s3 *= f;
           m_run = cm;
         }
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {                      // masked words give exp2(-huge) = 0
-          s0 += exp2f(x[j + 0] - m_run); s1 += exp2f(x[j + 1] - m_run);
-          s2 += exp2f(x[j + 2] - m_run); s3 += exp2f(x[j + 3] - m_run);
+          s0 += ex2_ftz(x[j + 0] - m_run); s1 += ex2_ftz(x[j + 1] - m_run);
+          s2 += ex2_ftz(x[j + 2] - m_run); s3 += ex2_ftz(x[j + 3] - m_run);
         }
       }
       tc_fence_before();
-      mbar_arrive(&t_empty[acc]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(acc ? t_empty_l1 : t_empty_l0);      // one arrival per epilogue warp of either CTA
     }
     if (row < R) {
       const size_t pi = (size_t)(range * 2 + half) * R + row;
@@ -263,9 +293,10 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();                                          // neither CTA leaves while the other can still signal it
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
   }
 }
 
@@ -609,7 +640,7 @@ std::string make_map(EncodeTiledFn fn, CUtensorMap* map, const float* base, int 
 
 }  // namespace
 
-size_t VocabTC::smem_bytes() const { return (size_t)(KB + STAGES) * TILE_BYTES + 1024 + 256 + 8 * 64 * 4; }
+size_t VocabTC::smem_bytes() const { return (size_t)(KB + STAGES) * TILE_BYTES + 1024 + 256 + 8 * 128 * 4; }
 
 std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out_tf32, int Rcap, int K2_, int n_sms) {
   V = V_; H = H_; K2 = K2_;
@@ -626,7 +657,7 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
     return "cuTensorMapEncodeTiled is not available from the driver";
   EncodeTiledFn fn = (EncodeTiledFn)fnp;
   std::string err = make_map(fn, &tmA, out_tf32, Rcap, H);
-  if (err.empty()) err = make_map(fn, &tmB, wT_tf32, V, H);
+  if (err.empty()) err = make_map(fn, &tmB, wT_tf32, V, H);               // box = one CTA's half tile (128 words)
   if (!err.empty()) return err;
   cudaError_t e = cudaFuncSetAttribute(vocab_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
   if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes());
@@ -635,9 +666,9 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
   return "";
 }
 
-void VocabTC::plan(int R, int* n_mblocks, int* n_ranges) const {
-  *n_mblocks = (R + BM - 1) / BM;
-  int nr = sms / *n_mblocks;
+void VocabTC::plan(int R, int* n_mpairs, int* n_ranges) const {
+  *n_mpairs = (R + 2 * BM - 1) / (2 * BM);
+  int nr = (sms / 2) / *n_mpairs;
   if (nr < 1) nr = 1;
   if (nr > n_tiles) nr = n_tiles;
   *n_ranges = nr;
@@ -645,13 +676,13 @@ void VocabTC::plan(int R, int* n_mblocks, int* n_ranges) const {
 
 int VocabTC::launch(int R, const float* bias, float* part_m, float* part_s, float4* gmax, int gstride,
                     float* logits_dbg, cudaStream_t st) const {
-  int nmb, nr;
-  plan(R, &nmb, &nr);
-  dim3 grid(nmb * nr);
+  int nmp, nr;
+  plan(R, &nmp, &nr);
+  dim3 grid(2 * nmp * nr);                                     // __cluster_dims__(2, 1, 1): consecutive CTAs are a pair
   if (logits_dbg)
-    vocab_tc_kernel<true><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, gmax, gstride, logits_dbg);
+    vocab_tc_kernel<true><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmp, nr, part_m, part_s, gmax, gstride, logits_dbg);
   else
-    vocab_tc_kernel<false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmb, nr, part_m, part_s, gmax, gstride, nullptr);
+    vocab_tc_kernel<false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmp, nr, part_m, part_s, gmax, gstride, nullptr);
   return 1;
 }
 

@@ -27,7 +27,7 @@ class VocabTC {
   // wT_tf32 [V, H] and out_tf32 [Rcap (multiple of 128), H] are tf32-rounded device copies whose
   // addresses stay fixed (they are baked into the TMA descriptors).
   std::string init(const float* wT_tf32, int V, int H, const float* out_tf32, int Rcap, int K2, int n_sms);
-  void plan(int R, int* n_mblocks, int* n_ranges) const;
+  void plan(int R, int* n_mpairs, int* n_ranges) const;
   int launch(int R, const float* bias, float* part_m, float* part_s, float4* gmax, int gstride, float* logits_dbg,
              cudaStream_t st) const;
   int launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const;     // article words
