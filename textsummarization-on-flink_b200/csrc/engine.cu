@@ -424,6 +424,7 @@ void Engine::decoder() {
     // output = [h; ctx] . AttnOutputProjection + b                                (:173)
     g = GemmArgs(); g.A0 = state_[n] + A + H; g.lda0 = SW; g.k0 = H; g.A1 = state_[n]; g.lda1 = SW; g.k1 = A;
     g.B = w_.out_MT; g.ldb = H + A; g.bias = w_.out_b; g.C = out_; g.ldc = H; g.M = R; g.N = H; g.skinny = 1;
+    if (vocab_tc_) { g.C_tf32 = out_tf32_; g.ldc_tf32 = H; }   // the tensor-core pass multiplies the tf32-rounded copy
     nl += launch_gemm_nt(g, st_);
     if (vocab_tc_) {
       // vocabulary scores on the tensor cores, candidates + softmax statistics in the epilogue   (model.py:236-238)
@@ -437,7 +438,6 @@ void Engine::decoder() {
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
       if (profile_) cudaEventRecord(pev_[5 * s + 2], st_);
-      nl += launch_round_tf32(out_, out_tf32_, (size_t)R * H, st_);
       nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, nullptr, st_);
       if (profile_) cudaEventRecord(pev_[5 * s + 3], st_);
       nl += vtc_.launch_rescore(ma, B, st_);                 // exact fp32 logits of the article's words

@@ -92,6 +92,11 @@ gemm_nt_kernel(GemmArgs g) {
       float v = acc[i][j] + (g.bias ? g.bias[n] : 0.f);
       if (g.act == 1) v = fmaxf(v, 0.f);
       g.C[(long long)m * g.ldc + n] = v;
+      if (g.C_tf32) {
+        uint32_t r;
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+        g.C_tf32[(long long)m * g.ldc_tf32 + n] = __uint_as_float(r);
+      }
     }
   }
 }
@@ -177,6 +182,11 @@ gemm_skinny_kernel(GemmArgs g) {
     v += g.bias ? g.bias[n] : 0.f;
     if (g.act == 1) v = fmaxf(v, 0.f);
     g.C[(long long)m * g.ldc + n] = v;
+    if (g.C_tf32) {
+      uint32_t r;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+      g.C_tf32[(long long)m * g.ldc_tf32 + n] = __uint_as_float(r);
+    }
   }
 }
 static_assert(8 * 2 * GBK * 36 >= 8 * 1024, "reduction buffer must fit in the tile storage");

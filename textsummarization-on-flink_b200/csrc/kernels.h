@@ -14,6 +14,7 @@ struct GemmArgs {
   const float* B = nullptr;  int ldb = 0;
   const float* bias = nullptr;
   float* C = nullptr; int ldc = 0;
+  float* C_tf32 = nullptr; int ldc_tf32 = 0;   // optional second output: C rounded to tf32 (rna), operand of the tensor-core pass
   int M = 0, N = 0;
   int act = 0;            // 0 none, 1 relu
   int skinny = 0;         // per-step decoder GEMM (few hundred rows): split-K tile kernel.  Chosen by the call

@@ -123,6 +123,28 @@ __device__ __forceinline__ float ex2_ftz(float x) {           // one MUFU.EX2, n
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// packed fp32 pairs (FFMA2 / FADD2): two results per issue slot -- the epilogue is issue-bound
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------
@@ -145,11 +167,11 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* bars = reinterpret_cast<uint64_t*>(smB + (size_t)STAGES * TILE_BYTES);
   uint64_t* full = bars;                 // [STAGES]  leader's: both CTAs' halves have landed
   uint64_t* empty = bars + STAGES;       // [STAGES]  each CTA's: the MMAs reading the stage have retired
-  uint64_t* a_full = bars + 2 * STAGES;  // [1]       leader's: both row blocks have landed
-  uint64_t* t_full = a_full + 1;         // [2]       each CTA's: accumulator complete
+  uint64_t* a_full = bars + 2 * STAGES;  // [8]       leader's: k-block kb of both row blocks has landed
+  uint64_t* t_full = a_full + 8;         // [2]       each CTA's: accumulator complete
   uint64_t* t_empty = t_full + 2;        // [2]       leader's: both CTAs' epilogues have drained the accumulator
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
-  float* bias_s = reinterpret_cast<float*>(bars + 16);           // [8 epilogue warps][128], 16-byte aligned
+  float* bias_s = reinterpret_cast<float*>(bars + 24);           // [8 epilogue warps][128], 16-byte aligned
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint32_t crank;
@@ -160,7 +182,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    mbar_init(a_full, 1);
+    for (int kb = 0; kb < 8; ++kb) mbar_init(&a_full[kb], 1);
     for (int a = 0; a < 2; ++a) { mbar_init(&t_full[a], 1); mbar_init(&t_empty[a], 2 * (EPI_THREADS / 32)); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -177,13 +199,16 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp == 0) {
     // ===== TMA producer (both CTAs; completion is signalled on the leader's barriers) =====
     if (lane == 0) {
-      if (crank == 0) mbar_expect_tx(a_full, 2u * (uint32_t)KB * TILE_BYTES);
-      const uint32_t a_full_l = mapa_rank(a_full, 0);
-      for (int kb = 0; kb < KB; ++kb) tma_load_2d_pair(smA + (size_t)kb * TILE_BYTES, &tmA, a_full_l, kb * BK, mb * BM);
+      // the row block is loaded k-block by k-block, interleaved with the first tile's stages, so that the first
+      // MMA waits for 2 x 16 KB instead of the whole 128 KB block
       uint32_t it = 0;
       for (int tile = range; tile < n_tiles; tile += n_ranges) {
         for (int kb = 0; kb < KB; ++kb, ++it) {
           const int s = it % STAGES;
+          if (it < (uint32_t)KB) {
+            if (crank == 0) mbar_expect_tx(&a_full[kb], 2u * TILE_BYTES);
+            tma_load_2d_pair(smA + (size_t)kb * TILE_BYTES, &tmA, mapa_rank(&a_full[kb], 0), kb * BK, mb * BM);
+          }
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
           if (crank == 0) mbar_expect_tx(&full[s], 2u * TILE_BYTES);
           tma_load_2d_pair(smB + (size_t)s * TILE_BYTES, &tmB, mapa_rank(&full[s], 0), kb * BK, tile * BN + (int)crank * BNH);
@@ -193,7 +218,6 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == 1) {
     // ===== MMA issuer (leader only) =====
     if (lane == 0 && crank == 0) {
-      mbar_wait(a_full, 0);
       uint32_t it = 0, tcount = 0;
       for (int tile = range; tile < n_tiles; tile += n_ranges, ++tcount) {
         const int acc = tcount & 1;
@@ -201,6 +225,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         tc_fence_after();
         for (int kb = 0; kb < KB; ++kb, ++it) {
           const int s = it % STAGES;
+          if (it < (uint32_t)KB) mbar_wait(&a_full[kb], 0);
           mbar_wait(&full[s], (it / STAGES) & 1);
           tc_fence_after();
           const uint64_t ad = smem_desc_sw128(smem_u32(smA + (size_t)kb * TILE_BYTES));
@@ -223,7 +248,9 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int row = mb * BM + q * 32 + lane;
     float* bsm = bias_s + ew * 128;                            // warp-private bias staging
     const uint32_t t_empty_l0 = mapa_rank(&t_empty[0], 0), t_empty_l1 = mapa_rank(&t_empty[1], 0);
-    float m_run = -FLT_MAX, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    float m_run = -FLT_MAX;
+    uint64_t s01 = pack2(0.f, 0.f), s23 = s01;                 // four partial sums of exp2(x - m_run)
+    const uint64_t kL2 = pack2(kLog2e, kLog2e);
     uint32_t tcount = 0;
     for (int tile = range; tile < n_tiles; tile += n_ranges, ++tcount) {
       const int acc = tcount & 1;
@@ -248,10 +275,8 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const float4 b4 = *reinterpret_cast<const float4*>(bsm + c * 32 + j);
-          x[j + 0] = fmaf(__uint_as_float(raw[c & 1][j + 0]), kLog2e, b4.x);
-          x[j + 1] = fmaf(__uint_as_float(raw[c & 1][j + 1]), kLog2e, b4.y);
-          x[j + 2] = fmaf(__uint_as_float(raw[c & 1][j + 2]), kLog2e, b4.z);
-          x[j + 3] = fmaf(__uint_as_float(raw[c & 1][j + 3]), kLog2e, b4.w);
+          unpack2(fma2(pack2(__uint_as_float(raw[c & 1][j + 0]), __uint_as_float(raw[c & 1][j + 1])), kL2, pack2(b4.x, b4.y)), x[j + 0], x[j + 1]);
+          unpack2(fma2(pack2(__uint_as_float(raw[c & 1][j + 2]), __uint_as_float(raw[c & 1][j + 3])), kL2, pack2(b4.z, b4.w)), x[j + 2], x[j + 3]);
         }
         if (n0 + 32 > V) {                                     // only in the last tile
 #pragma unroll
@@ -272,13 +297,18 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           gmax[(size_t)(n0 >> 5) * gstride + row] = make_float4(g[0], g[1], g[2], g[3]);
         if (cm > m_run) {
           const float f = ex2_ftz(m_run - cm);
-          s0 *= f; s1 *= f; s2 *= f; s3 *= f;
+          const uint64_t f2 = pack2(f, f);
+          s01 = mul2(s01, f2); s23 = mul2(s23, f2);
           m_run = cm;
         }
+        const uint64_t nm = pack2(-m_run, -m_run);
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {                      // masked words give exp2(-huge) = 0
-          s0 += ex2_ftz(x[j + 0] - m_run); s1 += ex2_ftz(x[j + 1] - m_run);
-          s2 += ex2_ftz(x[j + 2] - m_run); s3 += ex2_ftz(x[j + 3] - m_run);
+          float y0, y1, y2, y3;
+          unpack2(add2(pack2(x[j + 0], x[j + 1]), nm), y0, y1);
+          unpack2(add2(pack2(x[j + 2], x[j + 3]), nm), y2, y3);
+          s01 = add2(s01, pack2(ex2_ftz(y0), ex2_ftz(y1)));
+          s23 = add2(s23, pack2(ex2_ftz(y2), ex2_ftz(y3)));
         }
       }
       tc_fence_before();
@@ -288,6 +318,8 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (row < R) {
       const size_t pi = (size_t)(range * 2 + half) * R + row;
       part_m[pi] = m_run;
+      float s0, s1, s2, s3;
+      unpack2(s01, s0, s1); unpack2(s23, s2, s3);
       part_s[pi] = (s0 + s1) + (s2 + s3);
     }
   }
