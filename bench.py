@@ -48,7 +48,7 @@ def config_dict(n_gpus: int) -> dict:
     return {"workload": "BASELINE.json configs[2]: full beam-4 decode, 64 articles per device batch, "
                         "max_enc_steps=400, max_dec_steps=100, min_dec_steps=35, coverage=1, pointer_gen (OOV copy "
                         "scatter), vocab 50000, hidden 256, emb 128, W1 synthetic weights",
-            "articles_per_step_per_gpu": ARTICLES_PER_STEP, "slots_in_flight": "library default (--slots=3) unless PGEN_BENCH_EXTRA overrides", "beam_size": BEAM, "max_enc_steps": T_ENC,
+            "articles_per_step_per_gpu": ARTICLES_PER_STEP, "slots_in_flight": "library default (--slots=4) unless PGEN_BENCH_EXTRA overrides", "beam_size": BEAM, "max_enc_steps": T_ENC,
             "max_dec_steps": S_DEC, "vocab_size": V,
             "sharding": "articles sharded by rank, one GPU per rank, no collective on the data path (x%d)" % n_gpus,
             "l2": "each step streams > 400 MB of per-batch tensors (zx 210 MB, enc states/features 105 MB, logits "
@@ -230,6 +230,8 @@ def main():
                                      extra="--articles_per_batch=%d --flush_ms=-1 %s"
                                            % (ARTICLES_PER_STEP, os.environ.get("PGEN_BENCH_EXTRA", "")))
     dec = native.Decoder(flags, device=local_rank)
+    for opt in filter(None, os.environ.get("PGEN_BENCH_OPTS", "").split(",")):   # experiments only, e.g. encoder=steps
+        dec.set_option(opt)
     n_total = args.warmup + args.steps
     # every rank decodes its own shard of the synthetic stream (weak scaling: per-GPU work is fixed)
     art_ids = synth.make_article_ids(ARTICLES_PER_STEP * n_total, vsize=V, seed=1234 + 1000 * rank)

@@ -131,7 +131,7 @@ PGEN_API int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids
 PGEN_API int pgen_stage_run(pgen_t* h);
 PGEN_API int pgen_stage_sync(pgen_t* h);
 PGEN_API int pgen_stage_download(pgen_t* h, int32_t* out_tokens, int32_t* out_lens, float* out_logprobs, double* out_avg);
-/* A handle keeps `--slots` (default 3) device batches in flight, each on its own stream; the stage calls above
+/* A handle keeps `--slots` (default 4) device batches in flight, each on its own stream; the stage calls above
  * and pgen_stream / pgen_debug_fetch address the slot chosen here (default 0). */
 PGEN_API int pgen_stage_slot(pgen_t* h, int slot);
 /* The handle's cudaStream_t (as void*), so that a harness can record CUDA events on it. */

@@ -23,7 +23,7 @@ struct HyperParams {                       // run_summarization.py:48-88 (names 
   // Flags that only this library knows; the reference's parser ignores them (known_only=True).
   int64_t articles_per_batch = 64;         // device-level article batching
   int64_t flush_ms = 50;                   // deadline after which poll() decodes a partial batch
-  int64_t slots = 3;                       // device batches in flight per handle (each with its own stream)
+  int64_t slots = 4;                       // device batches in flight per handle (each with its own stream)
   std::string weights_path;                // overrides <log_root>/<exp_name>/train/model.pgenw
 };
 

@@ -340,7 +340,35 @@ __global__ void round_tf32_kernel(const float* __restrict__ in, float* __restric
   out[i] = __uint_as_float(r);
 }
 
-// exact fp32 logits of every distinct in-vocabulary word of the article, for the K rows of the article
+// Sum of N per-lane values over the warp with N - 1 (+ log2(32 / N)) shuffles instead of 5 N: every stage halves the
+// number of values a lane carries.  Afterwards lane l holds the total of value l * N / 32 (order fixed -> deterministic).
+template <int N>
+__device__ __forceinline__ float warp_multi_reduce(float (&v)[N], int lane) {
+  int n = N;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    if (n > 1) {
+      const int hlf = n >> 1;
+      const bool up = (lane & o) != 0;
+#pragma unroll
+      for (int i = 0; i < N / 2; ++i) {
+        if (i < hlf) {
+          const float send = up ? v[i] : v[i + hlf];
+          const float keep = up ? v[i + hlf] : v[i];
+          v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+      }
+      n = hlf;
+    } else {
+      v[0] += __shfl_xor_sync(0xffffffffu, v[0], o);
+    }
+  }
+  return v[0];
+}
+
+// exact fp32 logits of every distinct in-vocabulary word of the article, for the K rows of the article.
+// A warp takes 4 words: all of their weight rows are requested before the first is used.
+template <int KP>
 __global__ void __launch_bounds__(256)
 vocab_rescore_kernel(MergeArgs a) {
   extern __shared__ __align__(16) float sm[];
@@ -351,42 +379,58 @@ vocab_rescore_kernel(MergeArgs a) {
   if (u0 >= nu) return;
   const int K = a.K, H = a.H, T = a.T, V = a.V;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int ids[4];
+  float4 w4[4][2];
+  float bb[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int u = u0 + warp * 4 + i;
+    const int id = u < nu ? __ldg(a.uniq_ids + (size_t)art * T + u) : -1;
+    ids[i] = id < V ? id : -1;                                  // in-article OOV: no vocabulary term
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    bb[i] = ids[i] >= 0 ? __ldg(a.bias + ids[i]) : 0.f;
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int h = lane * 4 + hh * 128;
+      w4[i][hh] = (ids[i] >= 0 && h < H) ? __ldg(reinterpret_cast<const float4*>(a.wT + (size_t)ids[i] * H + h))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
   float* outs = sm;                                             // [K][H]
   for (int i = threadIdx.x; i < K * H; i += 256) outs[i] = a.out[(size_t)art * K * H + i];
   __syncthreads();
-  for (int i = 0; i < 4; ++i) {
-    const int u = u0 + warp * 4 + i;
-    if (u >= nu) break;
-    const int id = a.uniq_ids[(size_t)art * T + u];
-    if (id >= V) continue;                                      // in-article OOV: no vocabulary term
-    const float* wr = a.wT + (size_t)id * H;
-    float acc[16];
+  float acc[4 * KP];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) acc[k] = 0.f;
-    for (int h = lane * 4; h < H; h += 128) {
-      const float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + h));
+  for (int i = 0; i < 4 * KP; ++i) acc[i] = 0.f;
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {
+  for (int hh = 0; hh < 2; ++hh) {
+    const int h = lane * 4 + hh * 128;
+    if (h < H) {
+#pragma unroll
+      for (int k = 0; k < KP; ++k) {
         if (k < K) {
           const float4 o4 = *reinterpret_cast<const float4*>(outs + k * H + h);
-          acc[k] = fmaf(w4.x, o4.x, acc[k]); acc[k] = fmaf(w4.y, o4.y, acc[k]);
-          acc[k] = fmaf(w4.z, o4.z, acc[k]); acc[k] = fmaf(w4.w, o4.w, acc[k]);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float s = acc[i * KP + k];
+            s = fmaf(w4[i][hh].x, o4.x, s); s = fmaf(w4[i][hh].y, o4.y, s);
+            s = fmaf(w4[i][hh].z, o4.z, s); s = fmaf(w4[i][hh].w, o4.w, s);
+            acc[i * KP + k] = s;
+          }
         }
       }
     }
-    const float b = a.bias[id];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      if (k < K) {
-        float v = acc[k];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) a.artl[(size_t)(art * K + k) * T + u] = v + b;
-      }
-    }
   }
+  const float tot = warp_multi_reduce<4 * KP>(acc, lane);
+  const int idx = lane * (4 * KP) / 32;                         // (word slot, row) this lane ended up with
+  const int i = idx / KP, k = idx % KP;
+  const bool writer = (4 * KP == 32) || (lane & 1) == 0;
+  int id = ids[0]; float b = bb[0];
+  if (i == 1) { id = ids[1]; b = bb[1]; } else if (i == 2) { id = ids[2]; b = bb[2]; } else if (i == 3) { id = ids[3]; b = bb[3]; }
+  if (writer && id >= 0 && k < K) a.artl[(size_t)(art * K + k) * T + u0 + warp * 4 + i] = tot + b;
 }
-
 
 // ---------------------------------------------------------------------------------------------
 // Candidate groups of one decoder row + exact re-scoring of their words.  One block per row.
@@ -721,7 +765,8 @@ int VocabTC::launch(int R, const float* bias, float* part_m, float* part_s, floa
 int VocabTC::launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const {
   if (!a.pointer_gen) return 0;
   dim3 grid((a.T + 31) / 32, B);
-  vocab_rescore_kernel<<<grid, 256, (size_t)a.K * a.H * sizeof(float), st>>>(a);
+  if (a.K <= 4) vocab_rescore_kernel<4><<<grid, 256, (size_t)a.K * a.H * sizeof(float), st>>>(a);
+  else vocab_rescore_kernel<8><<<grid, 256, (size_t)a.K * a.H * sizeof(float), st>>>(a);
   return 1;
 }
 
