@@ -235,8 +235,10 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     else DALLOC(proj_wT_tf32_, float, V * H);
     DALLOC(out_tf32_, float, Rpad * H);
     DALLOC(part_m_, float, (size_t)2 * n_sms_ * R); DALLOC(part_s_, float, (size_t)2 * n_sms_ * R);
-    gstride_ = (int)Rpad;
-    DALLOC(gmax_, float4, ((V + 31) / 32) * Rpad);
+    gstride_ = (int)((((V + 31) / 32) + 7) & ~(size_t)7);      // float4 per row, rows 128-byte aligned
+    DALLOC(gmax_, float4, (size_t)gstride_ * Rpad);
+    sstride_ = (int)((((V + 255) / 256) * 2 + 31) & ~(size_t)31);
+    DALLOC(smax_, float, (size_t)sstride_ * Rpad);
     DALLOC(artl_, float, R * T);
     if (!share) launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
@@ -432,13 +434,13 @@ void Engine::decoder() {
       vtc_.plan(R, &nmb, &nr);
       MergeArgs ma;
       ma.out = out_; ma.wT = w_.proj_wT; ma.bias = w_.proj_v; ma.part_m = part_m_; ma.part_s = part_s_;
-      ma.gmax = gmax_; ma.gstride = gstride_;
+      ma.gmax = gmax_; ma.gstride = gstride_; ma.smax = smax_; ma.sstride = sstride_;
       ma.artl = artl_; ma.pgen = pgen_; ma.attn = attn_[n]; ma.uniq_ids = uniq_;
       ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active; ma.lens = lens_;
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
       if (profile_) cudaEventRecord(pev_[5 * s + 2], st_);
-      nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, nullptr, st_);
+      nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, nullptr, st_);
       if (profile_) cudaEventRecord(pev_[5 * s + 3], st_);
       nl += vtc_.launch_rescore(ma, B, st_);                 // exact fp32 logits of the article's words
       nl += vtc_.launch_final(ma, st_);                      // candidates re-scored in fp32, copy mass, top-2K   (model.py:146-183, 284-285)
@@ -553,7 +555,7 @@ std::string Engine::vocab_logits_op(int rows, const float* out_dev, float* logit
   if (use_tc) {
     if (!vtc_.ready) return "tensor-core vocabulary path unavailable: " + vtc_why_;
     launch_round_tf32(out_dev, out_tf32_, (size_t)rows * H, st_);
-    vtc_.launch(rows, w_.proj_v, part_m_, part_s_, gmax_, gstride_, logits_dev, st_);
+    vtc_.launch(rows, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, logits_dev, st_);
   } else {
     GemmArgs g;
     g.A0 = out_dev; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;

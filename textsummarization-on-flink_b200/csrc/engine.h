@@ -73,6 +73,8 @@ class Engine {
   float *proj_wT_tf32_ = nullptr, *out_tf32_ = nullptr, *part_m_ = nullptr, *part_s_ = nullptr, *artl_ = nullptr;
   float4* gmax_ = nullptr;
   int gstride_ = 0;
+  float* smax_ = nullptr;
+  int sstride_ = 0;
   int n_sms_ = 148;
   std::vector<cudaEvent_t> pev_;   // 4 events per step when profiling: attn begin, attn end/vocab begin... 
   int pev_used_ = 0;

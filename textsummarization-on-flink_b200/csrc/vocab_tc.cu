@@ -159,7 +159,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const float* __restrict__ bias, int R, int V, int KB, int n_tiles, int n_mpairs, int n_ranges,
                 float* __restrict__ part_m, float* __restrict__ part_s, float4* __restrict__ gmax, int gstride,
-                float* __restrict__ logits_out) {
+                float* __restrict__ smax, int sstride, float* __restrict__ logits_out) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   unsigned char* smA = smem;                                   // KB tiles
@@ -264,6 +264,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * 128);
       uint32_t raw[2][32];
+      float tmx = -FLT_MAX;                                    // maximum of this thread's 128 words of the tile
       tmem_ld32(tbase, raw[0]);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -293,8 +294,9 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int j = 0; j < 32; ++j)
               if (n0 + j < V) logits_out[(size_t)row * V + n0 + j] = x[j] * kLn2;
         }
-        if (row < R && n0 < V)                                 // lanes are consecutive rows: one 512-byte store per warp
-          gmax[(size_t)(n0 >> 5) * gstride + row] = make_float4(g[0], g[1], g[2], g[3]);
+        if (row < R && n0 < V)                                 // row-major: the 4 chunks of a tile are 64 contiguous bytes of the row
+          gmax[(size_t)row * gstride + (n0 >> 5)] = make_float4(g[0], g[1], g[2], g[3]);
+        tmx = fmaxf(tmx, cm);
         if (cm > m_run) {
           const float f = ex2_ftz(m_run - cm);
           const uint64_t f2 = pack2(f, f);
@@ -311,6 +313,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           s23 = add2(s23, pack2(ex2_ftz(y2), ex2_ftz(y3)));
         }
       }
+      if (row < R) smax[(size_t)row * sstride + (nb >> 7)] = tmx;
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(acc ? t_empty_l1 : t_empty_l0);      // one arrival per epilogue warp of either CTA
@@ -443,7 +446,6 @@ __device__ __forceinline__ float tf32_rna(float x) {
   return __uint_as_float(r);
 }
 
-constexpr int SEL_PER_LANE = 16;    // group maxima per lane: 16 warps x 32 lanes x 16 = 8192 groups = 65536 words max
 
 // Order-preserving map float -> uint32 (larger float <=> larger key).
 __device__ __forceinline__ uint32_t f2ord(float x) {
@@ -451,9 +453,40 @@ __device__ __forceinline__ uint32_t f2ord(float x) {
   return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
 }
 
+// One warp extracts the `rounds` largest of the 32 keys its lanes hold (0 = nothing) into list[0..rounds), sorted
+// descending, with ids[] alongside: one redux.max + one ballot per round, no shuffles.
+__device__ __forceinline__ void warp_top_rounds(uint32_t key, int id, int rounds, uint32_t* list, int* ids, int lane) {
+  for (int round = 0; round < rounds; ++round) {
+    const uint32_t m = __reduce_max_sync(0xffffffffu, key);
+    const uint32_t ball = __ballot_sync(0xffffffffu, key == m);
+    if (lane == __ffs(ball) - 1) {
+      list[round] = m;
+      ids[round] = m ? id : -1;
+      key = 0u;
+    }
+  }
+}
+// Warp 0 merges n_lists (<= 32) descending lists of `len` keys into the `rounds` largest overall: lane l walks list l.
+__device__ __forceinline__ void warp_merge_heads(const uint32_t* lists, const int* ids, int n_lists, int len, int rounds,
+                                                 int* out, int lane) {
+  int head = 0;
+  uint32_t cur = lane < n_lists ? lists[lane * len] : 0u;
+  for (int round = 0; round < rounds; ++round) {
+    const uint32_t m = __reduce_max_sync(0xffffffffu, cur);
+    const uint32_t ball = __ballot_sync(0xffffffffu, cur == m);
+    if (lane == __ffs(ball) - 1) {
+      out[round] = m ? ids[lane * len + head] : -1;
+      ++head;
+      cur = (m && head < len) ? lists[lane * len + head] : 0u;
+    }
+  }
+}
+
 // One block per beam row, after the tensor-core pass:
-//   1. the 2K+8 best groups of 8 words by group maximum (tf32 logits), found without shuffles: every lane sorts its
-//      16 group keys once, then one redux.max + one ballot per round; the 16 warps' winners are ranked by counting;
+//   1. the 2K+8 best groups of 8 words by group maximum (tf32 logits), hierarchically and without shuffles: first
+//      the 2K+8 best 128-word supergroups (one key per thread, redux.max + ballot rounds per warp, warp 0 merges
+//      the warps' sorted lists), then the same over the 16 groups of each selected supergroup -- the best groups
+//      necessarily lie inside the best supergroups;
 //   2. exact fp32 logit (and the tf32-emulated one, to take the tensor-core value back out of the sum of
 //      exponentials) of the 8 words of every selected group;
 //   3. softmax denominator from the per-part (max, sum exp2) of the tensor-core pass, corrected by step 2;
@@ -465,18 +498,17 @@ vocab_final_kernel(MergeArgs a) {
   const int r = blockIdx.x, art = r / a.K;
   if (!a.active[art]) return;
   const int V = a.V, H = a.H, G = a.G, T = a.T, NP = a.n_parts, R = a.R, NC = a.NC, K2 = a.K2;
-  const int nch = (V + 31) / 32, ng = nch * 4;
+  const int nsg = (V + 127) >> 7;                   // supergroups of 128 words (16 groups)
   const int nu = a.pointer_gen ? a.uniq_cnt[art] : 0;
   const int len = a.lens[art];
   const int nf = NC + nu;
-  // vals [ng] is dead after stage 1; the final keys fin [NC + T] (u64) reuse its space
-  const int vwords = (max((ng + 3) & ~3, 2 * (NC + T)) + 3) & ~3;
-  float* vals = sm;                                 // [ng] group maxima of this row (log2 domain)
   unsigned long long* fin = reinterpret_cast<unsigned long long*>(sm);        // [NC + T] (value, ~id) keys
-  float* outs = vals + vwords;                      // [H] decoder output, exact
+  unsigned long long* ck = fin + (NC + T);          // [16 warps][K2] per-warp winners of the final top-2K
+  float* outs = reinterpret_cast<float*>(ck + SEL_WARPS * K2);                // [H] decoder output, exact
   float* outt = outs + H;                           // [H] the tf32-rounded copy the tensor core multiplied
-  unsigned long long* ck = reinterpret_cast<unsigned long long*>(outt + H);   // [16 warps][max(G, K2)] per-warp winners
-  float* pm = reinterpret_cast<float*>(ck + SEL_WARPS * G);                   // [NP] part maxima
+  uint32_t* wk = reinterpret_cast<uint32_t*>(outt + H);                       // [16 warps][G] selection lists: keys
+  int* wi = reinterpret_cast<int*>(wk + SEL_WARPS * G);                       // [16 warps][G]                  ids
+  float* pm = reinterpret_cast<float*>(wi + SEL_WARPS * G);                   // [NP] part maxima
   float* ps = pm + NP;                              // [NP] part sums
   float* att = ps + NP;                             // [T] attention of this row
   float* arl = att + T;                             // [T] exact logits of the article's words
@@ -486,13 +518,13 @@ vocab_final_kernel(MergeArgs a) {
   int* pss = cid + NC;                              // [T + 1] pos_start
   int* pls = pss + (T + 1);                         // [T] pos_list
   int* uids = pls + T;                              // [T] uniq_ids
-  int* sel = uids + T;                              // [G] selected group ids
+  int* sels = uids + T;                             // [G] selected supergroups
+  int* sel = sels + G;                              // [G] selected groups
   float* MS = reinterpret_cast<float*>(sel + G);    // [2] M (natural log domain), S
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- 0: everything this row needs, one round of loads
-  for (int c = threadIdx.x; c < nch; c += SEL_THREADS)
-    *reinterpret_cast<float4*>(vals + 4 * c) = a.gmax[(size_t)c * a.gstride + r];
+  const float sgv = (int)threadIdx.x < nsg ? a.smax[(size_t)r * a.sstride + threadIdx.x] : -FLT_MAX;
   for (int h = threadIdx.x; h < H; h += SEL_THREADS) {
     const float o = a.out[(size_t)r * H + h];
     outs[h] = o;
@@ -513,63 +545,15 @@ vocab_final_kernel(MergeArgs a) {
     }
     for (int i = threadIdx.x; i <= nu; i += SEL_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
   }
-  if (threadIdx.x < G) sel[threadIdx.x] = -1;
   if (threadIdx.x < K2) {                           // defaults, overwritten by the winners in step 4
     a.topk_ids[(size_t)r * K2 + threadIdx.x] = 0;
     a.topk_logp[(size_t)r * K2 + threadIdx.x] = -INFINITY;
   }
+  // ---- 1a: the G best supergroups: per-warp lists, then warp 0 merges them; meanwhile the last warp combines
+  // the per-part softmax statistics of the tensor-core pass
+  warp_top_rounds(sgv > -FLT_MAX ? f2ord(sgv) : 0u, threadIdx.x, G, wk + warp * G, wi + warp * G, lane);
   __syncthreads();
-
-  // ---- 1a: per-warp top-G groups.  A group maximum becomes one 32-bit key: the order-preserving bits of the value
-  // with the low 4 mantissa bits replaced by (15 - register slot); selection only has to be right to tf32
-  // precision, the candidates are re-scored exactly.
-  {
-    const int per_warp = (ng + SEL_WARPS - 1) / SEL_WARPS, base = warp * per_warp, wend = min(ng, base + per_warp);
-    uint32_t key[SEL_PER_LANE];
-#pragma unroll
-    for (int j = 0; j < SEL_PER_LANE; ++j) {
-      const int i = base + j * 32 + lane;
-      const float x = i < wend ? vals[i] : -FLT_MAX;
-      key[j] = x > -FLT_MAX ? ((f2ord(x) & ~15u) | (uint32_t)(15 - j)) : 0u;
-    }
-#pragma unroll
-    for (int k = 2; k <= SEL_PER_LANE; k <<= 1) {
-#pragma unroll
-      for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-        for (int i = 0; i < SEL_PER_LANE; ++i) {
-          const int l = i ^ j;
-          if (l > i) {
-            const uint32_t hi = max(key[i], key[l]), lo = min(key[i], key[l]);
-            if ((i & k) == 0) { key[i] = hi; key[l] = lo; } else { key[i] = lo; key[l] = hi; }
-          }
-        }
-      }
-    }
-    for (int round = 0; round < G; ++round) {
-      const uint32_t m = __reduce_max_sync(0xffffffffu, key[0]);
-      const uint32_t ball = __ballot_sync(0xffffffffu, key[0] == m);
-      if (lane == __ffs(ball) - 1) {
-        const int j = 15 - (int)(m & 15u);
-        ck[warp * G + round] = m ? ((unsigned long long)m << 32) | (0xffffffffu - (uint32_t)(base + j * 32 + lane)) : 0ull;
-#pragma unroll
-        for (int q = 0; q + 1 < SEL_PER_LANE; ++q) key[q] = key[q + 1];
-        key[SEL_PER_LANE - 1] = 0u;
-      }
-    }
-  }
-  __syncthreads();
-  // ---- 1b: the 16 x G winners ranked by counting (keys are unique: they carry the group id); meanwhile the last
-  // warp combines the per-part softmax statistics of the tensor-core pass
-  if (threadIdx.x < SEL_WARPS * G) {
-    const unsigned long long mine = ck[threadIdx.x];
-    if (mine) {
-      int rank = 0;
-#pragma unroll 8
-      for (int e = 0; e < SEL_WARPS * G; ++e) rank += ck[e] > mine;
-      if (rank < G) sel[rank] = (int)(0xffffffffu - (uint32_t)mine);
-    }
-  }
+  if (warp == 0) warp_merge_heads(wk, wi, SEL_WARPS, G, G, sels, lane);
   if (warp == SEL_WARPS - 1) {
     float M2 = -FLT_MAX;
     for (int pt = lane; pt < NP; pt += 32) M2 = fmaxf(M2, pm[pt]);
@@ -580,6 +564,20 @@ vocab_final_kernel(MergeArgs a) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
     if (lane == 0) { MS[0] = M2 * kLn2; MS[1] = S; }
+  }
+  __syncthreads();
+  // ---- 1b: the G best groups among the 16 G groups of those supergroups (thread = group, 64 contiguous bytes of
+  // the row's group maxima per supergroup)
+  {
+    const int n2 = G * 16, nw2 = (n2 + 31) >> 5;    // <= 512 threads, <= 16 warps
+    if (warp < nw2) {
+      const int sg = (int)threadIdx.x < n2 ? sels[threadIdx.x >> 4] : -1;
+      const int grp = sg >= 0 ? sg * 16 + (int)(threadIdx.x & 15) : -1;
+      const float gv = grp >= 0 ? reinterpret_cast<const float*>(a.gmax + (size_t)r * a.gstride)[grp] : -FLT_MAX;
+      warp_top_rounds(gv > -FLT_MAX ? f2ord(gv) : 0u, grp, G, wk + warp * G, wi + warp * G, lane);
+    }
+    __syncthreads();
+    if (warp == 0) warp_merge_heads(wk, wi, nw2, G, G, sel, lane);
   }
   __syncthreads();
   // ---- 2: exact fp32 logit and tf32-emulated logit of every word of the selected groups: warp per word, 4 in flight
@@ -602,6 +600,7 @@ vocab_final_kernel(MergeArgs a) {
                                            : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
+    float acc[8];                                   // (word u, exact) at 2u, (word u, tf32-emulated) at 2u + 1
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       float ex = 0.f, em = 0.f;
@@ -617,15 +616,15 @@ vocab_final_kernel(MergeArgs a) {
           em = fmaf(tf32_rna(w.z), t4.z, em); em = fmaf(tf32_rna(w.w), t4.w, em);
         }
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) { ex += __shfl_xor_sync(0xffffffffu, ex, o); em += __shfl_xor_sync(0xffffffffu, em, o); }
-      const int it = it0 + u;
-      if (lane == 0 && it < nw) {
-        const int id = ids[u];
-        cid[it] = id;
-        cx[it] = id >= 0 ? ex + bb[u] : -FLT_MAX;
-        ca[it] = id >= 0 ? em + bb[u] : -FLT_MAX;
-      }
+      acc[2 * u] = ex; acc[2 * u + 1] = em;
+    }
+    const float tot = warp_multi_reduce<8>(acc, lane);          // lane l holds value l / 4
+    const int vi = lane >> 2, u = vi >> 1, it = it0 + u;
+    int id = ids[0]; float b = bb[0];
+    if (u == 1) { id = ids[1]; b = bb[1]; } else if (u == 2) { id = ids[2]; b = bb[2]; } else if (u == 3) { id = ids[3]; b = bb[3]; }
+    if ((lane & 3) == 0 && it < nw) {
+      if (vi & 1) ca[it] = id >= 0 ? tot + b : -FLT_MAX;
+      else { cx[it] = id >= 0 ? tot + b : -FLT_MAX; cid[it] = id; }
     }
   }
   __syncthreads();
@@ -667,32 +666,43 @@ vocab_final_kernel(MergeArgs a) {
     }
   }
   __syncthreads();
-  // ---- 4b: per-warp top-2K over a contiguous sixteenth of the keys, then ranking by counting
+  // ---- 4b: per-warp top-2K over a contiguous sixteenth of the keys (descending lists), then warp 0 merges the lists.
+  // Keys are unique ((value, ~id), ids distinct); equal values are rare, so the second redux runs only then.
   {
     const int cw = (nf + SEL_WARPS - 1) / SEL_WARPS, c0 = warp * cw, c1 = min(nf, c0 + cw);
     for (int round = 0; round < K2; ++round) {
       unsigned long long best = 0ull; int bp = -1;
       for (int c = c0 + lane; c < c1; c += 32) { const unsigned long long k = fin[c]; if (k > best) { best = k; bp = c; } }
       const uint32_t hi = __reduce_max_sync(0xffffffffu, (uint32_t)(best >> 32));
-      const uint32_t lo = __reduce_max_sync(0xffffffffu, (uint32_t)(best >> 32) == hi ? (uint32_t)best : 0u);
-      const bool win = best != 0ull && (uint32_t)(best >> 32) == hi && (uint32_t)best == lo;
-      if (win) fin[bp] = 0ull;
-      if (lane == 0) ck[warp * K2 + round] = ((unsigned long long)hi << 32) | lo;
+      uint32_t ball = __ballot_sync(0xffffffffu, best != 0ull && (uint32_t)(best >> 32) == hi);
+      if (__popc(ball) > 1) {
+        const uint32_t lo = __reduce_max_sync(0xffffffffu, ((ball >> lane) & 1u) ? (uint32_t)best : 0u);
+        ball = __ballot_sync(0xffffffffu, ((ball >> lane) & 1u) && (uint32_t)best == lo);
+      }
+      if (ball == 0u) { if (lane == 0) ck[warp * K2 + round] = 0ull; }
+      else if (lane == __ffs(ball) - 1) { ck[warp * K2 + round] = best; fin[bp] = 0ull; }
       __syncwarp();
     }
   }
   __syncthreads();
-  if (threadIdx.x < SEL_WARPS * K2) {
-    const unsigned long long mine = ck[threadIdx.x];
-    if (mine >> 32) {
-      int rank = 0;
-#pragma unroll 8
-      for (int e = 0; e < SEL_WARPS * K2; ++e) rank += ck[e] > mine;
-      if (rank < K2) {
-        const uint32_t o = (uint32_t)(mine >> 32);
+  if (warp == 0) {
+    int head = 0;
+    unsigned long long cur = lane < SEL_WARPS ? ck[lane * K2] : 0ull;
+    for (int round = 0; round < K2; ++round) {
+      const uint32_t hi = __reduce_max_sync(0xffffffffu, (uint32_t)(cur >> 32));
+      uint32_t ball = __ballot_sync(0xffffffffu, cur != 0ull && (uint32_t)(cur >> 32) == hi);
+      if (__popc(ball) > 1) {
+        const uint32_t lo = __reduce_max_sync(0xffffffffu, ((ball >> lane) & 1u) ? (uint32_t)cur : 0u);
+        ball = __ballot_sync(0xffffffffu, ((ball >> lane) & 1u) && (uint32_t)cur == lo);
+      }
+      if (ball == 0u) break;                        // fewer than 2K entries: the defaults stay
+      if (lane == __ffs(ball) - 1) {
+        const uint32_t o = (uint32_t)(cur >> 32);
         const float v = __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu));
-        a.topk_ids[(size_t)r * K2 + rank] = (int)(0xffffffffu - (uint32_t)mine);
-        a.topk_logp[(size_t)r * K2 + rank] = logf(v);            // model.py:285
+        a.topk_ids[(size_t)r * K2 + round] = (int)(0xffffffffu - (uint32_t)cur);
+        a.topk_logp[(size_t)r * K2 + round] = logf(v);           // model.py:285
+        ++head;
+        cur = head < K2 ? ck[lane * K2 + head] : 0ull;
       }
     }
   }
@@ -722,7 +732,7 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
   V = V_; H = H_; K2 = K2_;
   if (H % BK != 0 || H > 256) return "tensor-core vocabulary path needs hidden_dim % 32 == 0 and <= 256";
   if (K2 > 16) return "tensor-core vocabulary path needs beam_size <= 8";
-  if (V > SEL_WARPS * 32 * SEL_PER_LANE * GW) return "tensor-core vocabulary path needs vocab_size <= 65536";
+  if (V > SEL_THREADS * 128) return "tensor-core vocabulary path needs vocab_size <= 65536";   // one 128-word supergroup per thread
   KB = H / BK;
   G = K2 + 8;                                          // candidate groups per row: the top 2K lie in the top 2K groups
   n_tiles = (V + BN - 1) / BN;
@@ -751,14 +761,14 @@ void VocabTC::plan(int R, int* n_mpairs, int* n_ranges) const {
 }
 
 int VocabTC::launch(int R, const float* bias, float* part_m, float* part_s, float4* gmax, int gstride,
-                    float* logits_dbg, cudaStream_t st) const {
+                    float* smax, int sstride, float* logits_dbg, cudaStream_t st) const {
   int nmp, nr;
   plan(R, &nmp, &nr);
   dim3 grid(2 * nmp * nr);                                     // __cluster_dims__(2, 1, 1): consecutive CTAs are a pair
   if (logits_dbg)
-    vocab_tc_kernel<true><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmp, nr, part_m, part_s, gmax, gstride, logits_dbg);
+    vocab_tc_kernel<true><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmp, nr, part_m, part_s, gmax, gstride, smax, sstride, logits_dbg);
   else
-    vocab_tc_kernel<false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmp, nr, part_m, part_s, gmax, gstride, nullptr);
+    vocab_tc_kernel<false><<<grid, NTHREADS, smem_bytes(), st>>>(tmA, tmB, bias, R, V, KB, n_tiles, nmp, nr, part_m, part_s, gmax, gstride, smax, sstride, nullptr);
   return 1;
 }
 
@@ -771,10 +781,9 @@ int VocabTC::launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const {
 }
 
 size_t VocabTC::final_smem(int T, int n_parts) const {
-  const int ng = ((V + 31) / 32) * 4, NC = G * GW;
-  const size_t vwords = (size_t)(std::max((ng + 3) & ~3, 2 * (NC + T)) + 3) & ~(size_t)3;
-  return (vwords + 2 * (size_t)H + 2 * (size_t)SEL_WARPS * G + 2 * (size_t)n_parts + 2 * (size_t)T + 3 * (size_t)NC +
-          (3 * (size_t)T + 1) + G + 2) * sizeof(float);
+  const size_t NC = (size_t)G * GW;
+  return 8 * (NC + T) + 8 * (size_t)SEL_WARPS * K2 + 4 * (2 * (size_t)H + 2 * (size_t)SEL_WARPS * G + 2 * (size_t)n_parts +
+         2 * (size_t)T + 3 * NC + (3 * (size_t)T + 1) + 2 * (size_t)G + 2);
 }
 
 int VocabTC::launch_final(const MergeArgs& a, cudaStream_t st) const {
