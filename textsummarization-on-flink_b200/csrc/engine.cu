@@ -33,6 +33,7 @@ T* Engine::dalloc(size_t n) {
 
 Engine::~Engine() {
   if (device_ >= 0) cudaSetDevice(device_);
+  for (auto& kv : graphs_) cudaGraphExecDestroy(kv.second);
   for (void* p : allocs_) cudaFree(p);
   for (void* p : {(void*)h_ids_, (void*)h_ext_, (void*)h_lens_, (void*)h_noov_, (void*)h_uniq_, (void*)h_ucnt_,
                   (void*)h_pstart_, (void*)h_plist_, (void*)h_nactive_, (void*)h_out_tok_, (void*)h_out_len_,
@@ -255,6 +256,8 @@ std::string Engine::set_option(const std::string& kv) {
   const size_t eq = kv.find('=');
   if (eq == std::string::npos) return "option must be key=value";
   const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
+  if (k == "graph") { use_graph_ = v != "0"; return ""; }
+  if (k == "graph_steps") { graph_steps_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "check_every") { check_every_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "encoder") { enc_persistent_ = (v != "steps"); return ""; }
   if (k == "vocab") {
@@ -380,25 +383,12 @@ void Engine::encoder() {
   }
 }
 
-// --------------------------------------------------------------------------------------
-// Decoder: initial attention pass + step loop
-// --------------------------------------------------------------------------------------
-void Engine::decoder() {
-  const int B = nB_, T = d_.T, H = d_.H, A = d_.A, E = d_.E, K = d_.K, R = B * K, SW = d_.SW;
-  uint64_t& nl = stats.kernel_launches;
-  nl += launch_init_beam(d_, B, lens_, bb_, st_);
-  if (d_.use_cov) cudaMemsetAsync(cov_[0], 0, (size_t)R * T * sizeof(float), st_);   // beam_search.py:105
-  {  // attention_decoder.py:138-140: context of the initial state (row b*K only; all K hyps are identical)
-    GemmArgs g;
-    g.A0 = state_[0] + A; g.lda0 = K * SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
-    g.C = dfeat_; g.ldc = K * A; g.M = B; g.N = A;
-    nl += launch_gemm_nt(g, st_);
-    nl += launch_attn_energy(d_, B, 1, lens_, bb_.active, enc_feat_, dfeat_, cov_[0], w_.v, w_.w_c, e_, st_);
-    nl += launch_attn_context(d_, B, 1, lens_, bb_.active, enc_states_, e_, attn_[0], state_[0], st_);
-  }
-  int steps = 0;
-  for (int s = 0; s < d_.S; ++s) {
-    const int o = s & 1, n = o ^ 1;
+// One decode step (beam_search.py:109-156) for buffer parity o (old) -> n (new).  Nothing in it depends on the step
+// number on the host side (beam_step reads it from steps_done), so a captured step can be replayed.
+int Engine::step_launch(int B, int o, int ps) {
+  const int T = d_.T, H = d_.H, A = d_.A, E = d_.E, K = d_.K, R = B * K, SW = d_.SW;
+  const int n = o ^ 1;
+  int nl = 0;
     StepBufs sb;
     sb.lens = lens_; sb.n_oov = noov_; sb.active = bb_.active; sb.sel_parent = bb_.sel_parent; sb.sel_token = bb_.sel_token;
     sb.emb = w_.emb; sb.state_old = state_[o]; sb.state_new = state_[n]; sb.attn_old = attn_[o]; sb.attn_new = attn_[n];
@@ -418,10 +408,10 @@ void Engine::decoder() {
     g = GemmArgs(); g.A0 = state_[n] + A; g.lda0 = SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
     g.C = dfeat_; g.ldc = A; g.M = R; g.N = A; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
-    if (profile_) cudaEventRecord(pev_[5 * s + 0], st_);
+    if (profile_) cudaEventRecord(pev_[5 * ps + 0], st_);
     nl += launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[n], w_.v, w_.w_c, e_, st_);
     nl += launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[n], state_[n], st_);
-    if (profile_) cudaEventRecord(pev_[5 * s + 1], st_);
+    if (profile_) cudaEventRecord(pev_[5 * ps + 1], st_);
     if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, st_);   // :166-167
     // output = [h; ctx] . AttnOutputProjection + b                                (:173)
     g = GemmArgs(); g.A0 = state_[n] + A + H; g.lda0 = SW; g.k0 = H; g.A1 = state_[n]; g.lda1 = SW; g.k1 = A;
@@ -439,28 +429,98 @@ void Engine::decoder() {
       ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active; ma.lens = lens_;
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
-      if (profile_) cudaEventRecord(pev_[5 * s + 2], st_);
+      if (profile_) cudaEventRecord(pev_[5 * ps + 2], st_);
       nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, nullptr, st_);
-      if (profile_) cudaEventRecord(pev_[5 * s + 3], st_);
+      if (profile_) cudaEventRecord(pev_[5 * ps + 3], st_);
       nl += vtc_.launch_rescore(ma, B, st_);                 // exact fp32 logits of the article's words
       nl += vtc_.launch_final(ma, st_);                      // candidates re-scored in fp32, copy mass, top-2K   (model.py:146-183, 284-285)
-      if (profile_) cudaEventRecord(pev_[5 * s + 4], st_);
+      if (profile_) cudaEventRecord(pev_[5 * ps + 4], st_);
     } else {
     // vocabulary scores                                                           (model.py:236)
     g = GemmArgs(); g.A0 = out_; g.lda0 = H; g.k0 = H; g.B = w_.proj_wT; g.ldb = H; g.bias = w_.proj_v;
     g.C = logits_; g.ldc = d_.V; g.M = R; g.N = d_.V;
-    if (profile_) cudaEventRecord(pev_[5 * s + 2], st_);
+    if (profile_) cudaEventRecord(pev_[5 * ps + 2], st_);
     nl += launch_gemm_nt(g, st_);
-    if (profile_) cudaEventRecord(pev_[5 * s + 3], st_);
+    if (profile_) cudaEventRecord(pev_[5 * ps + 3], st_);
     nl += launch_softmax_stats(d_, R, logits_, rowmax_, rowsum_, bb_.active, st_);
     FinalArgs fa;
     fa.logits = logits_; fa.rowmax = rowmax_; fa.rowsum = rowsum_; fa.pgen = pgen_; fa.attn = attn_[n];
     fa.uniq_ids = uniq_; fa.uniq_cnt = ucnt_; fa.pos_start = pstart_; fa.pos_list = plist_; fa.n_oov = noov_;
     fa.active = bb_.active; fa.topk_ids = topk_ids_; fa.topk_logp = topk_logp_;
     nl += launch_final_topk(d_, B, fa, st_);
-    if (profile_) cudaEventRecord(pev_[5 * s + 4], st_);
+    if (profile_) cudaEventRecord(pev_[5 * ps + 4], st_);
     }
-    nl += launch_beam_step(d_, B, s, topk_ids_, topk_logp_, bb_, st_);
+    nl += launch_beam_step(d_, B, topk_ids_, topk_logp_, bb_, st_);
+  return nl;
+}
+
+// `chunk` consecutive steps (even count) captured once per batch size into an executable graph: a kernel node costs
+// ~0.6 us of launch overhead instead of the ~4 us (quantised) of a stream launch on this platform.
+cudaGraphExec_t Engine::step_graph(int B, int chunk, bool capture) {
+  if (graph_failed_) return nullptr;
+  if (graph_chunk_ != chunk) {
+    for (auto& kv : graphs_) cudaGraphExecDestroy(kv.second);
+    graphs_.clear();
+    graph_chunk_ = chunk;
+  }
+  auto it = graphs_.find(B);
+  if (it != graphs_.end()) return it->second;
+  if (!capture) return nullptr;
+  cudaGraph_t g = nullptr;
+  cudaGraphExec_t ge = nullptr;
+  int nodes = 0;
+  if (cudaStreamBeginCapture(st_, cudaStreamCaptureModeRelaxed) != cudaSuccess) { graph_failed_ = true; cudaGetLastError(); return nullptr; }
+  for (int i = 0; i < chunk; ++i) nodes += step_launch(B, i & 1, 0);
+  if (cudaStreamEndCapture(st_, &g) != cudaSuccess || !g || cudaGraphInstantiate(&ge, g, 0) != cudaSuccess) {
+    if (g) cudaGraphDestroy(g);
+    graph_failed_ = true; cudaGetLastError();
+    return nullptr;
+  }
+  cudaGraphDestroy(g);
+  graph_nodes_ = nodes;
+  graphs_[B] = ge;
+  return ge;
+}
+
+// --------------------------------------------------------------------------------------
+// Decoder: initial attention pass + step loop
+// --------------------------------------------------------------------------------------
+void Engine::decoder() {
+  const int B = nB_, T = d_.T, H = d_.H, A = d_.A, K = d_.K, R = B * K, SW = d_.SW;
+  uint64_t& nl = stats.kernel_launches;
+  nl += launch_init_beam(d_, B, lens_, bb_, st_);
+  if (d_.use_cov) cudaMemsetAsync(cov_[0], 0, (size_t)R * T * sizeof(float), st_);   // beam_search.py:105
+  {  // attention_decoder.py:138-140: context of the initial state (row b*K only; all K hyps are identical)
+    GemmArgs g;
+    g.A0 = state_[0] + A; g.lda0 = K * SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
+    g.C = dfeat_; g.ldc = K * A; g.M = B; g.N = A;
+    nl += launch_gemm_nt(g, st_);
+    nl += launch_attn_energy(d_, B, 1, lens_, bb_.active, enc_feat_, dfeat_, cov_[0], w_.v, w_.w_c, e_, st_);
+    nl += launch_attn_context(d_, B, 1, lens_, bb_.active, enc_states_, e_, attn_[0], state_[0], st_);
+  }
+  int steps = 0;
+  const bool graphs = use_graph_ && !profile_ && graph_steps_ >= 2;
+  const int chunk = graphs ? (graph_steps_ & ~1) : 0;          // an even number of steps per graph: buffer parity restarts
+  cudaGraphExec_t ge = graphs ? step_graph(B, chunk, false) : nullptr;
+  if (graphs && !ge && chunk <= d_.S) {
+    // first batch of this size: one chunk with plain launches (which also sets the kernels' lazy function attributes
+    // outside any capture), then capture; a failed capture leaves plain launches for good
+    for (int i = 0; i < chunk; ++i) nl += step_launch(B, i & 1, i);
+    steps = chunk;
+    ge = step_graph(B, chunk, true);
+  }
+  while (ge && steps + chunk <= d_.S) {
+    cudaGraphLaunch(ge, st_);
+    nl += (uint64_t)graph_nodes_;
+    steps += chunk;
+    if (check_every_ > 0 && steps < d_.S && steps > d_.min_dec_steps) {
+      cudaMemcpyAsync(h_nactive_, bb_.n_active, sizeof(int), cudaMemcpyDeviceToHost, st_);
+      cudaStreamSynchronize(st_);
+      if (*h_nactive_ == 0) { stats.decode_steps += steps; pev_used_ = 0; goto done; }
+    }
+  }
+  for (int s = steps; s < d_.S; ++s) {
+    nl += step_launch(B, s & 1, s);
     ++steps;
     if (check_every_ > 0 && s + 1 < d_.S && s + 1 > d_.min_dec_steps && (s + 1) % check_every_ == 0) {
       cudaMemcpyAsync(h_nactive_, bb_.n_active, sizeof(int), cudaMemcpyDeviceToHost, st_);
@@ -470,6 +530,7 @@ void Engine::decoder() {
   }
   stats.decode_steps += steps;
   pev_used_ = profile_ ? steps : 0;
+done:
   nl += launch_finalize(d_, B, lens_, bb_, out_tok_, out_len_, out_lp_, out_avg_, st_);
 }
 

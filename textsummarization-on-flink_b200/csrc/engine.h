@@ -62,6 +62,13 @@ class Engine {
   Dims d_{};
   int device_ = 0, Bcap_ = 0, R_ = 0, nB_ = 0, max_len_ = 0;
   bool staged_ = false, ran_ = false, synced_ = false, counted_ = false;
+  bool use_graph_ = true;            // replay captured steps instead of launching ~13 kernels per step
+  int graph_steps_ = 10;             // steps per graph (even); the early-stop poll happens between graphs
+  int graph_chunk_ = 0, graph_nodes_ = 0;
+  bool graph_failed_ = false;
+  std::map<int, cudaGraphExec_t> graphs_;     // by articles in the batch
+  int step_launch(int B, int o, int ps);
+  cudaGraphExec_t step_graph(int B, int chunk, bool capture);
   int check_every_ = 0;              // > 0: poll the device every N steps (after min_dec_steps) to stop early;
                                      // 0: never block the host -- run() is fully asynchronous
   bool profile_ = false;

@@ -9,6 +9,7 @@
 #include <cooperative_groups.h>
 
 #include <cfloat>
+#include <cstdlib>
 #include <cmath>
 
 namespace pgn {
@@ -189,11 +190,173 @@ gemm_skinny_kernel(GemmArgs g) {
     }
   }
 }
+// Second-generation skinny GEMM.  Same 32 x 32 output tile and the same in-CTA split of the K loop over 4 groups of
+// 64 threads, but (1) every group streams its k-tiles through a 3-stage cp.async ring, so the L2 latency is paid
+// once instead of once per k-tile, and (2) the K range is also split over the CZ CTAs of a cluster (grid z),
+// whose partial tiles are added in rank order inside the leader's shared memory (DSMEM) -- four times as many SMs
+// work on the narrow GEMMs.  CZ depends on N and K only, never on M, so an article's rounding does not depend on
+// the batch.  Thread (ty, tx) of a group owns rows ty + 8 i and columns tx + 8 j: with a row pitch of 20 floats
+// the 128-bit shared-memory reads of a quarter warp fall into 8 different 16-byte banks.
+constexpr int SK_LD = 20, SK_STAGES = 3, SK_GROUPS = 4;
+constexpr int SK_STAGE_FLOATS = 2 * 32 * SK_LD;                                 // A tile + B tile of one stage
+constexpr int SK_PIPE_FLOATS = SK_GROUPS * SK_STAGES * SK_STAGE_FLOATS;         // 15360 floats = 60 KB
+inline size_t sk_smem_bytes(int cz) { return (size_t)(SK_PIPE_FLOATS + (cz - 1) * 1024) * sizeof(float); }
+
+__device__ __forceinline__ void cp_async16(float* dst, const float* src, bool valid) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+  const int sz = valid ? 16 : 0;                                                // 0 -> the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+
+__global__ void __launch_bounds__(64 * SK_GROUPS)
+gemm_skinny2_kernel(GemmArgs g, int cz) {
+  extern __shared__ __align__(16) float sk_sm[];
+  const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
+  const int tx = t & 7, ty = t >> 3;
+  const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  const int rank = blockIdx.z;                                                  // cluster = (1, 1, cz)
+  const int ktiles = (g.k0 + g.k1) / GBK;
+  const int per = (ktiles + cz - 1) / cz, kt_lo = rank * per, kt_hi = min(ktiles, kt_lo + per);
+  const int n_my = kt_hi > kt_lo + grp ? (kt_hi - kt_lo - grp + SK_GROUPS - 1) / SK_GROUPS : 0;   // tiles kt_lo + grp + 4 i
+  float* pipe = sk_sm + grp * SK_STAGES * SK_STAGE_FLOATS;
+
+  auto issue = [&](int i) {                                                     // tile i of this group -> stage i % 3
+    if (i < n_my) {
+      const int kt = (kt_lo + grp + i * SK_GROUPS) * GBK;
+      float* As = pipe + (i % SK_STAGES) * SK_STAGE_FLOATS;
+      float* Bs = As + 32 * SK_LD;
+      const bool seg0 = kt < g.k0;
+#pragma unroll
+      for (int rep = 0; rep < 2; ++rep) {
+        const int idx = t + rep * 64, row = idx >> 2, ch = (idx & 3) * 4;
+        const int m = m0 + row, n = n0 + row;
+        const float* sa = seg0 ? g.A0 + (long long)min(m, g.M - 1) * g.lda0 + kt + ch
+                               : g.A1 + (long long)min(m, g.M - 1) * g.lda1 + (kt - g.k0) + ch;
+        cp_async16(As + row * SK_LD + ch, sa, m < g.M);
+        cp_async16(Bs + row * SK_LD + ch, g.B + (long long)min(n, g.N - 1) * g.ldb + kt + ch, n < g.N);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  // packed fp32 pairs (FFMA2): acc2[i][j] = (sum over even k, sum over odd k) of a[i][k] * b[j][k]; the two halves are
+  // added once at the end.  Half the issue slots of scalar FFMA -- the kernel is issue-bound.
+  unsigned long long acc2[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc2[i][j] = 0ull;
+  issue(0);
+  issue(1);
+  for (int i = 0; i < n_my; ++i) {
+    asm volatile("cp.async.wait_group 1;" ::: "memory");                        // tile i has landed (this thread's part)
+    asm volatile("bar.sync %0, 64;" ::"r"(grp + 1) : "memory");                 // ... everybody's, and tile i - 1 is consumed
+    issue(i + 2);
+    const float* As = pipe + (i % SK_STAGES) * SK_STAGE_FLOATS;
+    const float* Bs = As + 32 * SK_LD;
+#pragma unroll
+    for (int k4 = 0; k4 < GBK; k4 += 4) {
+      ulonglong2 a[4], b[4];                                                    // (k, k+1) and (k+2, k+3) as packed pairs
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        a[q] = *reinterpret_cast<const ulonglong2*>(As + (ty + 8 * q) * SK_LD + k4);
+        b[q] = *reinterpret_cast<const ulonglong2*>(Bs + (tx + 8 * q) * SK_LD + k4);
+      }
+#pragma unroll
+      for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc2[ii][jj]) : "l"(a[ii].x), "l"(b[jj].x));
+          asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc2[ii][jj]) : "l"(a[ii].y), "l"(b[jj].y));
+        }
+    }
+  }
+  float acc[4][4];
+#pragma unroll
+  for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      float lo, hi;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc2[ii][jj]));
+      acc[ii][jj] = lo + hi;
+    }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  float* red = sk_sm;                                                           // [4 groups][32][32], aliases the ring
+#pragma unroll
+  for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) red[grp * 1024 + (ty + 8 * ii) * 32 + tx + 8 * jj] = acc[ii][jj];
+  __syncthreads();
+  float part[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int o = tid + e * 256;
+    part[e] = ((red[o] + red[1024 + o]) + red[2048 + o]) + red[3072 + o];       // group order: deterministic
+  }
+  float* cred = sk_sm + SK_PIPE_FLOATS;                                         // leader: [cz - 1][32][32] partial tiles
+  if (cz > 1) {
+    if (rank > 0) {
+      const uint32_t local = (uint32_t)__cvta_generic_to_shared(cred + (rank - 1) * 1024);
+      uint32_t remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(0));
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + (uint32_t)(tid + e * 256) * 4u), "f"(part[e]) : "memory");
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (rank > 0) return;
+  }
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int o = tid + e * 256;
+    const int m = m0 + (o >> 5), n = n0 + (o & 31);
+    if (m >= g.M || n >= g.N) continue;
+    float v = part[e];
+    for (int q = 1; q < cz; ++q) v += cred[(q - 1) * 1024 + o];                 // rank order: deterministic
+    v += g.bias ? g.bias[n] : 0.f;
+    if (g.act == 1) v = fmaxf(v, 0.f);
+    g.C[(long long)m * g.ldc + n] = v;
+    if (g.C_tf32) {
+      uint32_t r;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+      g.C_tf32[(long long)m * g.ldc_tf32 + n] = __uint_as_float(r);
+    }
+  }
+}
+
+static int launch_gemm_skinny2(const GemmArgs& a, cudaStream_t st) {
+  const int ktiles = (a.k0 + a.k1) / GBK, tiles_n = (a.N + 31) / 32;
+  int cz = tiles_n <= 8 ? 4 : tiles_n <= 16 ? 2 : 1;                            // from N and K only -- never from M
+  while (cz > 1 && ktiles / cz < 8) cz >>= 1;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    cudaFuncSetAttribute(gemm_skinny2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sk_smem_bytes(4));
+    attr_set[dev & 63] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(tiles_n, (a.M + 31) / 32, cz);
+  cfg.blockDim = dim3(64 * SK_GROUPS);
+  cfg.dynamicSmemBytes = sk_smem_bytes(cz);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = cz;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, gemm_skinny2_kernel, a, cz);
+  return 1;
+}
+
 static_assert(8 * 2 * GBK * 36 >= 8 * 1024, "reduction buffer must fit in the tile storage");
 
 int launch_gemm_nt(const GemmArgs& a, cudaStream_t st) {
   if (a.M <= 0 || a.N <= 0) return 0;
   const int ktiles = (a.k0 + a.k1) / GBK;
+  if (a.skinny && ktiles >= 16 && !a.gather0 && a.k0 % GBK == 0 && a.k1 % GBK == 0 && a.lda0 % 4 == 0 && a.lda1 % 4 == 0 &&
+      a.ldb % 4 == 0 && !getenv("PGEN_SKINNY1"))
+    return launch_gemm_skinny2(a, st);
   if (a.skinny && ktiles >= 8) {
     dim3 grid((a.N + 31) / 32, (a.M + 31) / 32);
     if (a.N <= 512 && ktiles >= 16) gemm_skinny_kernel<8><<<grid, 512, 0, st>>>(a);
@@ -930,13 +1093,14 @@ constexpr int kStop = 3, kStart = 2;
 constexpr int BEAM_MAXC = 512;      // K * 2K candidates, K <= 16
 
 __global__ void __launch_bounds__(128)
-beam_step_kernel(Dims d, int step, const int* __restrict__ topk_ids, const float* __restrict__ topk_logp, BeamBufs b) {
+beam_step_kernel(Dims d, const int* __restrict__ topk_ids, const float* __restrict__ topk_logp, BeamBufs b) {
   __shared__ double keys[BEAM_MAXC];
   __shared__ double sums[BEAM_MAXC];
   __shared__ int order[BEAM_MAXC];
   __shared__ int n_new_s;
   const int art = blockIdx.x;
   if (!b.active[art]) return;
+  const int step = b.steps_done[art];                                   // an active article has done every step so far
   const int K = d.K, K2 = d.K2;
   const int num_orig = step == 0 ? 1 : K;                               // :127-129
   const int nc = num_orig * K2;
@@ -1002,9 +1166,9 @@ beam_step_kernel(Dims d, int step, const int* __restrict__ topk_ids, const float
   for (int sidx = threadIdx.x; sidx < n_new_s; sidx += 128) b.beam_sum[art * K + sidx] = sums[order[sidx]];
 }
 
-int launch_beam_step(const Dims& d, int B, int step, const int* topk_ids, const float* topk_logp,
+int launch_beam_step(const Dims& d, int B, const int* topk_ids, const float* topk_logp,
                      const BeamBufs& b, cudaStream_t st) {
-  beam_step_kernel<<<B, 128, 0, st>>>(d, step, topk_ids, topk_logp, b);
+  beam_step_kernel<<<B, 128, 0, st>>>(d, topk_ids, topk_logp, b);
   return 1;
 }
 

@@ -90,7 +90,7 @@ struct BeamBufs {
   int* best_kind; int* best_idx;                                        // [B] 0: result idx, 1: live beam slot
 };
 // run_beam_search's per-step bookkeeping (beam_search.py:126-156), one block per article.
-int launch_beam_step(const Dims& d, int B, int step, const int* topk_ids, const float* topk_logp,
+int launch_beam_step(const Dims& d, int B, const int* topk_ids, const float* topk_logp,
                      const BeamBufs& b, cudaStream_t st);
 // beam_search.py:160-168 + token back-trace of the winning hypothesis.
 int launch_finalize(const Dims& d, int B, const int* lens, const BeamBufs& b, int* out_tokens, int* out_len,
