@@ -219,6 +219,8 @@ gemm_skinny2_kernel(GemmArgs g, int cz) {
   const int per = (ktiles + cz - 1) / cz, kt_lo = rank * per, kt_hi = min(ktiles, kt_lo + per);
   const int n_my = kt_hi > kt_lo + grp ? (kt_hi - kt_lo - grp + SK_GROUPS - 1) / SK_GROUPS : 0;   // tiles kt_lo + grp + 4 i
   float* pipe = sk_sm + grp * SK_STAGES * SK_STAGE_FLOATS;
+  // split-phase cluster barrier: nobody may touch a peer's shared memory before that peer has started running
+  if (cz > 1) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 
   auto issue = [&](int i) {                                                     // tile i of this group -> stage i % 3
     if (i < n_my) {
@@ -296,6 +298,7 @@ gemm_skinny2_kernel(GemmArgs g, int cz) {
   }
   float* cred = sk_sm + SK_PIPE_FLOATS;                                         // leader: [cz - 1][32][32] partial tiles
   if (cz > 1) {
+    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");              // every CTA of the cluster is running
     if (rank > 0) {
       const uint32_t local = (uint32_t)__cvta_generic_to_shared(cred + (rank - 1) * 1024);
       uint32_t remote;
