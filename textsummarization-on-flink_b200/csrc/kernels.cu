@@ -190,176 +190,11 @@ gemm_skinny_kernel(GemmArgs g) {
     }
   }
 }
-// Second-generation skinny GEMM.  Same 32 x 32 output tile and the same in-CTA split of the K loop over 4 groups of
-// 64 threads, but (1) every group streams its k-tiles through a 3-stage cp.async ring, so the L2 latency is paid
-// once instead of once per k-tile, and (2) the K range is also split over the CZ CTAs of a cluster (grid z),
-// whose partial tiles are added in rank order inside the leader's shared memory (DSMEM) -- four times as many SMs
-// work on the narrow GEMMs.  CZ depends on N and K only, never on M, so an article's rounding does not depend on
-// the batch.  Thread (ty, tx) of a group owns rows ty + 8 i and columns tx + 8 j: with a row pitch of 20 floats
-// the 128-bit shared-memory reads of a quarter warp fall into 8 different 16-byte banks.
-constexpr int SK_LD = 20, SK_STAGES = 3, SK_GROUPS = 4;
-constexpr int SK_STAGE_FLOATS = 2 * 32 * SK_LD;                                 // A tile + B tile of one stage
-constexpr int SK_PIPE_FLOATS = SK_GROUPS * SK_STAGES * SK_STAGE_FLOATS;         // 15360 floats = 60 KB
-inline size_t sk_smem_bytes(int cz) { return (size_t)(SK_PIPE_FLOATS + (cz - 1) * 1024) * sizeof(float); }
-
-__device__ __forceinline__ void cp_async16(float* dst, const float* src, bool valid) {
-  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
-  const int sz = valid ? 16 : 0;                                                // 0 -> the 16 bytes are zero-filled
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
-}
-
-__global__ void __launch_bounds__(64 * SK_GROUPS)
-gemm_skinny2_kernel(GemmArgs g, int cz) {
-  extern __shared__ __align__(16) float sk_sm[];
-  const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
-  const int tx = t & 7, ty = t >> 3;
-  const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
-  const int rank = blockIdx.z;                                                  // cluster = (1, 1, cz)
-  const int ktiles = (g.k0 + g.k1) / GBK;
-  const int per = (ktiles + cz - 1) / cz, kt_lo = rank * per, kt_hi = min(ktiles, kt_lo + per);
-  const int n_my = kt_hi > kt_lo + grp ? (kt_hi - kt_lo - grp + SK_GROUPS - 1) / SK_GROUPS : 0;   // tiles kt_lo + grp + 4 i
-  float* pipe = sk_sm + grp * SK_STAGES * SK_STAGE_FLOATS;
-  // split-phase cluster barrier: nobody may touch a peer's shared memory before that peer has started running
-  if (cz > 1) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
-
-  auto issue = [&](int i) {                                                     // tile i of this group -> stage i % 3
-    if (i < n_my) {
-      const int kt = (kt_lo + grp + i * SK_GROUPS) * GBK;
-      float* As = pipe + (i % SK_STAGES) * SK_STAGE_FLOATS;
-      float* Bs = As + 32 * SK_LD;
-      const bool seg0 = kt < g.k0;
-#pragma unroll
-      for (int rep = 0; rep < 2; ++rep) {
-        const int idx = t + rep * 64, row = idx >> 2, ch = (idx & 3) * 4;
-        const int m = m0 + row, n = n0 + row;
-        const float* sa = seg0 ? g.A0 + (long long)min(m, g.M - 1) * g.lda0 + kt + ch
-                               : g.A1 + (long long)min(m, g.M - 1) * g.lda1 + (kt - g.k0) + ch;
-        cp_async16(As + row * SK_LD + ch, sa, m < g.M);
-        cp_async16(Bs + row * SK_LD + ch, g.B + (long long)min(n, g.N - 1) * g.ldb + kt + ch, n < g.N);
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-
-  // packed fp32 pairs (FFMA2): acc2[i][j] = (sum over even k, sum over odd k) of a[i][k] * b[j][k]; the two halves are
-  // added once at the end.  Half the issue slots of scalar FFMA -- the kernel is issue-bound.
-  unsigned long long acc2[4][4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc2[i][j] = 0ull;
-  issue(0);
-  issue(1);
-  for (int i = 0; i < n_my; ++i) {
-    asm volatile("cp.async.wait_group 1;" ::: "memory");                        // tile i has landed (this thread's part)
-    asm volatile("bar.sync %0, 64;" ::"r"(grp + 1) : "memory");                 // ... everybody's, and tile i - 1 is consumed
-    issue(i + 2);
-    const float* As = pipe + (i % SK_STAGES) * SK_STAGE_FLOATS;
-    const float* Bs = As + 32 * SK_LD;
-#pragma unroll
-    for (int k4 = 0; k4 < GBK; k4 += 4) {
-      ulonglong2 a[4], b[4];                                                    // (k, k+1) and (k+2, k+3) as packed pairs
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        a[q] = *reinterpret_cast<const ulonglong2*>(As + (ty + 8 * q) * SK_LD + k4);
-        b[q] = *reinterpret_cast<const ulonglong2*>(Bs + (tx + 8 * q) * SK_LD + k4);
-      }
-#pragma unroll
-      for (int ii = 0; ii < 4; ++ii)
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
-          asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc2[ii][jj]) : "l"(a[ii].x), "l"(b[jj].x));
-          asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc2[ii][jj]) : "l"(a[ii].y), "l"(b[jj].y));
-        }
-    }
-  }
-  float acc[4][4];
-#pragma unroll
-  for (int ii = 0; ii < 4; ++ii)
-#pragma unroll
-    for (int jj = 0; jj < 4; ++jj) {
-      float lo, hi;
-      asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc2[ii][jj]));
-      acc[ii][jj] = lo + hi;
-    }
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncthreads();
-  float* red = sk_sm;                                                           // [4 groups][32][32], aliases the ring
-#pragma unroll
-  for (int ii = 0; ii < 4; ++ii)
-#pragma unroll
-    for (int jj = 0; jj < 4; ++jj) red[grp * 1024 + (ty + 8 * ii) * 32 + tx + 8 * jj] = acc[ii][jj];
-  __syncthreads();
-  float part[4];
-#pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const int o = tid + e * 256;
-    part[e] = ((red[o] + red[1024 + o]) + red[2048 + o]) + red[3072 + o];       // group order: deterministic
-  }
-  float* cred = sk_sm + SK_PIPE_FLOATS;                                         // leader: [cz - 1][32][32] partial tiles
-  if (cz > 1) {
-    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");              // every CTA of the cluster is running
-    if (rank > 0) {
-      const uint32_t local = (uint32_t)__cvta_generic_to_shared(cred + (rank - 1) * 1024);
-      uint32_t remote;
-      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(0));
-#pragma unroll
-      for (int e = 0; e < 4; ++e)
-        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + (uint32_t)(tid + e * 256) * 4u), "f"(part[e]) : "memory");
-    }
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-    if (rank > 0) return;
-  }
-#pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const int o = tid + e * 256;
-    const int m = m0 + (o >> 5), n = n0 + (o & 31);
-    if (m >= g.M || n >= g.N) continue;
-    float v = part[e];
-    for (int q = 1; q < cz; ++q) v += cred[(q - 1) * 1024 + o];                 // rank order: deterministic
-    v += g.bias ? g.bias[n] : 0.f;
-    if (g.act == 1) v = fmaxf(v, 0.f);
-    g.C[(long long)m * g.ldc + n] = v;
-    if (g.C_tf32) {
-      uint32_t r;
-      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-      g.C_tf32[(long long)m * g.ldc_tf32 + n] = __uint_as_float(r);
-    }
-  }
-}
-
-static int launch_gemm_skinny2(const GemmArgs& a, cudaStream_t st) {
-  const int ktiles = (a.k0 + a.k1) / GBK, tiles_n = (a.N + 31) / 32;
-  int cz = tiles_n <= 8 ? 4 : tiles_n <= 16 ? 2 : 1;                            // from N and K only -- never from M
-  while (cz > 1 && ktiles / cz < 8) cz >>= 1;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
-    cudaFuncSetAttribute(gemm_skinny2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sk_smem_bytes(4));
-    attr_set[dev & 63] = true;
-  }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(tiles_n, (a.M + 31) / 32, cz);
-  cfg.blockDim = dim3(64 * SK_GROUPS);
-  cfg.dynamicSmemBytes = sk_smem_bytes(cz);
-  cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = cz;
-  cfg.attrs = at; cfg.numAttrs = 1;
-  cudaLaunchKernelEx(&cfg, gemm_skinny2_kernel, a, cz);
-  return 1;
-}
-
 static_assert(8 * 2 * GBK * 36 >= 8 * 1024, "reduction buffer must fit in the tile storage");
 
 int launch_gemm_nt(const GemmArgs& a, cudaStream_t st) {
   if (a.M <= 0 || a.N <= 0) return 0;
   const int ktiles = (a.k0 + a.k1) / GBK;
-  if (a.skinny && ktiles >= 16 && !a.gather0 && a.k0 % GBK == 0 && a.k1 % GBK == 0 && a.lda0 % 4 == 0 && a.lda1 % 4 == 0 &&
-      a.ldb % 4 == 0 && !getenv("PGEN_SKINNY1"))
-    return launch_gemm_skinny2(a, st);
   if (a.skinny && ktiles >= 8) {
     dim3 grid((a.N + 31) / 32, (a.M + 31) / 32);
     if (a.N <= 512 && ktiles >= 16) gemm_skinny_kernel<8><<<grid, 512, 0, st>>>(a);
@@ -463,9 +298,12 @@ int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const flo
 // shared memory through DSMEM; one cluster barrier per time step.  c stays in registers.
 // --------------------------------------------------------------------------------------
 namespace cgx = cooperative_groups;
-constexpr int PE_H = 256, PE_AG = 8, PE_THREADS = 512;
-constexpr size_t PE_SMEM = (size_t)(PE_H * 128 + 2 * PE_H * PE_AG + 2 * 8 * PE_AG * 128) * sizeof(float) + 64;
-constexpr uint32_t PE_H_BYTES = PE_H * PE_AG * sizeof(float);   // one full h(s) for the group: 8 KB
+constexpr int PE_H = 256, PE_THREADS = 512;
+template <int AG> struct PeCfg {                      // AG articles per cluster
+  static constexpr int AGP = (AG + 3) & ~3;           // row pitch of the h buffers (float4 loads)
+  static constexpr size_t SMEM = (size_t)(PE_H * 128 + 2 * PE_H * AGP + 8 * AG * 128) * sizeof(float) + 64;
+  static constexpr uint32_t H_BYTES = PE_H * AG * sizeof(float);   // one full h(s) of the group
+};
 
 __device__ __forceinline__ uint32_t pe_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t pe_mapa(uint32_t saddr, uint32_t rank) {
@@ -488,18 +326,29 @@ __device__ __forceinline__ void pe_bar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Persistent BiLSTM recurrence (model.py:76-93): one cluster of 8 CTAs per (direction, group of AG articles) runs all
+// time steps.  CTA c keeps the recurrent weights of hidden units [32c, 32c+32) (4 gates = 128 columns, 128 KB) in
+// shared memory for the whole kernel, computes its slice of h.Kh with the K range split over 8 thread groups, adds
+// the partial sums in fixed order, applies the gates and sends its 32 x AG new h values to every CTA of the cluster
+// with st.async, which also signals the receiver's mbarrier: no cluster-wide barrier per step.
+// AG is chosen so that ALL clusters are co-resident: a B200 runs at most 15 clusters of 8 CTAs with this footprint,
+// and a 16th would cost a whole second wave (tools/micro/cluster_occ.cu).  Every article's arithmetic is the same
+// for every AG.
+template <int AG>
 __global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(PE_THREADS, 1)
 enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const float* __restrict__ zx,
                            const float* __restrict__ kh, float* __restrict__ h_fin, float* __restrict__ c_fin,
                            float* __restrict__ enc_states) {
+  constexpr int AGP = PeCfg<AG>::AGP;
+  constexpr uint32_t H_BYTES = PeCfg<AG>::H_BYTES;
   extern __shared__ __align__(16) float sm[];
   float* Ws = sm;                                  // [256 k][128 local cols]
-  float* hs = Ws + PE_H * 128;                     // [2][256 k][8 articles]
-  float* red = hs + 2 * PE_H * PE_AG;              // [2][8 kq][8 articles][128 cols]
-  uint64_t* hbar = reinterpret_cast<uint64_t*>(red + 2 * 8 * PE_AG * 128);   // [2] "h buffer b is complete"
+  float* hs = Ws + PE_H * 128;                     // [2][256 k][AGP articles]
+  float* red = hs + 2 * PE_H * AGP;                // [8 kq][AG articles][128 cols]
+  uint64_t* hbar = reinterpret_cast<uint64_t*>(red + 8 * AG * 128);   // [2] "h buffer b is complete"
   cgx::cluster_group cluster = cgx::this_cluster();
   const int c = (int)cluster.block_rank();         // which 32 hidden units
-  const int dir = blockIdx.y, b0 = blockIdx.z * PE_AG;
+  const int dir = blockIdx.y, b0 = blockIdx.z * AG;
   const int tid = threadIdx.x;
   constexpr int H4 = 4 * PE_H;
 
@@ -509,27 +358,28 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
     const int k = i >> 7, lc = i & 127, g = lc >> 5, ul = lc & 31;
     Ws[i] = khd[(size_t)k * H4 + g * PE_H + 32 * c + ul];
   }
-  for (int i = tid; i < 2 * PE_H * PE_AG; i += PE_THREADS) hs[i] = 0.f;
+  for (int i = tid; i < 2 * PE_H * AGP; i += PE_THREADS) hs[i] = 0.f;
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(pe_smem_u32(&hbar[b])));
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[b])), "r"(PE_H_BYTES) : "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[b])), "r"(H_BYTES) : "memory");
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   int grp_max = 0;
-  for (int a = 0; a < PE_AG; ++a) if (b0 + a < B) grp_max = max(grp_max, lens[b0 + a]);
+  for (int a = 0; a < AG; ++a) if (b0 + a < B) grp_max = max(grp_max, lens[b0 + a]);
   // roles
   const int kq = tid >> 6, cp = tid & 63;          // mat-vec: k range [32kq, 32kq+32), columns cp and cp+64
-  const int ful = tid & 31, fa = (tid >> 5) & 7;   // gate math (threads < 256): unit ful, article fa
+  const int ful = tid & 31, fa = tid >> 5;         // gate math (threads < 32 AG): unit ful, article fa
+  const bool gate_thread = fa < AG;
   const int fb = b0 + fa;
-  const int flen = (tid < 256 && fb < B) ? lens[fb] : 0;
+  const int flen = (gate_thread && fb < B) ? lens[fb] : 0;
   float c_reg = 0.f, h_reg = 0.f;
   // remote addresses of "my" h element and of the two barriers in each CTA of the cluster
   uint32_t r_h[8], r_bar[8];
 #pragma unroll
   for (int rk = 0; rk < 8; ++rk) {
-    r_h[rk] = pe_mapa(pe_smem_u32(hs + (32 * c + ful) * PE_AG + fa), rk);
+    r_h[rk] = pe_mapa(pe_smem_u32(hs + (32 * c + ful) * AGP + (gate_thread ? fa : 0)), rk);
     r_bar[rk] = pe_mapa(pe_smem_u32(&hbar[0]), rk);
   }
   cluster.sync();
@@ -539,7 +389,7 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
     // prefetch this step's input projection (x.Kx + b) for the gate-math threads
     float zi = 0.f, zj = 0.f, zf = 0.f, zo = 0.f;
     int t = -1;
-    if (tid < 256 && s < flen) {
+    if (gate_thread && s < flen) {
       t = dir == 0 ? s : flen - 1 - s;             // backward: reversed over the article's own length
       const float* zp = zx + ((size_t)dir * B * T + (size_t)fb * T + t) * H4 + 32 * c + ful;
       zi = __ldg(zp); zj = __ldg(zp + PE_H); zf = __ldg(zp + 2 * PE_H); zo = __ldg(zp + 3 * PE_H);
@@ -547,38 +397,43 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
     if (s > 0) {                                   // h(s-1) from all 8 CTAs has landed in hs[cur]
       pe_bar_wait(&hbar[cur], ((s - 1) >> 1) & 1);
       if (tid == 0 && s + 1 < grp_max)             // arm the same barrier for h(s+1), which reuses this buffer
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[cur])), "r"(PE_H_BYTES) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[cur])), "r"(H_BYTES) : "memory");
     }
     // partial h . Kh over this thread's k range
-    float acc0[PE_AG], acc1[PE_AG];
+    float acc0[AGP], acc1[AGP];
 #pragma unroll
-    for (int a = 0; a < PE_AG; ++a) { acc0[a] = 0.f; acc1[a] = 0.f; }
-    const float* hcur = hs + cur * PE_H * PE_AG;
-#pragma unroll 8
+    for (int a = 0; a < AGP; ++a) { acc0[a] = 0.f; acc1[a] = 0.f; }
+    const float* hcur = hs + cur * PE_H * AGP;
+#pragma unroll 4
     for (int kk = 0; kk < 32; ++kk) {
       const int k = kq * 32 + kk;
       const float w0 = Ws[k * 128 + cp], w1 = Ws[k * 128 + cp + 64];
-      const float4 ha = *reinterpret_cast<const float4*>(hcur + k * PE_AG);
-      const float4 hb = *reinterpret_cast<const float4*>(hcur + k * PE_AG + 4);
-      acc0[0] = fmaf(ha.x, w0, acc0[0]); acc0[1] = fmaf(ha.y, w0, acc0[1]); acc0[2] = fmaf(ha.z, w0, acc0[2]); acc0[3] = fmaf(ha.w, w0, acc0[3]);
-      acc0[4] = fmaf(hb.x, w0, acc0[4]); acc0[5] = fmaf(hb.y, w0, acc0[5]); acc0[6] = fmaf(hb.z, w0, acc0[6]); acc0[7] = fmaf(hb.w, w0, acc0[7]);
-      acc1[0] = fmaf(ha.x, w1, acc1[0]); acc1[1] = fmaf(ha.y, w1, acc1[1]); acc1[2] = fmaf(ha.z, w1, acc1[2]); acc1[3] = fmaf(ha.w, w1, acc1[3]);
-      acc1[4] = fmaf(hb.x, w1, acc1[4]); acc1[5] = fmaf(hb.y, w1, acc1[5]); acc1[6] = fmaf(hb.z, w1, acc1[6]); acc1[7] = fmaf(hb.w, w1, acc1[7]);
-    }
-    float* redc = red + cur * (8 * PE_AG * 128);   // double-buffered: step s+1 may write while step s is still read
 #pragma unroll
-    for (int a = 0; a < PE_AG; ++a) {
-      redc[(kq * PE_AG + a) * 128 + cp] = acc0[a];
-      redc[(kq * PE_AG + a) * 128 + cp + 64] = acc1[a];
+      for (int q = 0; q < AGP / 4; ++q) {
+        const float4 h4 = *reinterpret_cast<const float4*>(hcur + k * AGP + 4 * q);
+        acc0[4 * q + 0] = fmaf(h4.x, w0, acc0[4 * q + 0]); acc1[4 * q + 0] = fmaf(h4.x, w1, acc1[4 * q + 0]);
+        acc0[4 * q + 1] = fmaf(h4.y, w0, acc0[4 * q + 1]); acc1[4 * q + 1] = fmaf(h4.y, w1, acc1[4 * q + 1]);
+        if (4 * q + 2 < AG) {
+          acc0[4 * q + 2] = fmaf(h4.z, w0, acc0[4 * q + 2]); acc1[4 * q + 2] = fmaf(h4.z, w1, acc1[4 * q + 2]);
+          acc0[4 * q + 3] = fmaf(h4.w, w0, acc0[4 * q + 3]); acc1[4 * q + 3] = fmaf(h4.w, w1, acc1[4 * q + 3]);
+        }
+      }
+    }
+    // The partial sums of step s overwrite those of step s-1: every thread that read them has since issued its
+    // st.async, and nobody gets here before ALL of those have landed (the wait above).
+#pragma unroll
+    for (int a = 0; a < AG; ++a) {
+      red[(kq * AG + a) * 128 + cp] = acc0[a];
+      red[(kq * AG + a) * 128 + cp + 64] = acc1[a];
     }
     __syncthreads();
-    if (tid < 256) {
+    if (gate_thread) {
       float hn = h_reg;
       if (t >= 0) {
         float gi = zi, gj = zj, gf = zf, go = zo;
 #pragma unroll
         for (int q = 0; q < 8; ++q) {              // fixed order: deterministic
-          const float* r = redc + (q * PE_AG + fa) * 128 + ful;
+          const float* r = red + (q * AG + fa) * 128 + ful;
           gi += r[0]; gj += r[32]; gf += r[64]; go += r[96];
         }
         c_reg = sigmoidf_(gf + 1.0f) * c_reg + sigmoidf_(gi) * tanhf(gj);   // LSTMCell, forget_bias 1
@@ -589,29 +444,62 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
       // new h (or the frozen one past the article's end) into buffer cur^1 of every CTA of the cluster; each
       // store adds its 4 bytes to that CTA's barrier for the buffer
       if (s + 1 < grp_max) {
-        const uint32_t boff = (uint32_t)(cur ^ 1) * PE_H_BYTES, bar_off = (uint32_t)(cur ^ 1) * 8u;
+        const uint32_t boff = (uint32_t)(cur ^ 1) * (uint32_t)(PE_H * AGP * sizeof(float)), bar_off = (uint32_t)(cur ^ 1) * 8u;
 #pragma unroll
         for (int rk = 0; rk < 8; ++rk) pe_st_async(r_h[rk] + boff, hn, r_bar[rk] + bar_off);
       }
     }
   }
   cluster.sync();                                  // nobody leaves while remote stores may still target it
-  if (tid < 256 && fb < B) {
+  if (gate_thread && fb < B) {
     h_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = h_reg;
     c_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = c_reg;
   }
 }
 
+template <int AG>
+static int pe_launch(const Dims& d, int B, const int* lens, const float* zx, const float* kh, float* h_fin, float* c_fin,
+                     float* enc_states, cudaStream_t st) {
+  static bool set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!set[dev & 63]) {
+    cudaFuncSetAttribute(enc_lstm_persistent_kernel<AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PeCfg<AG>::SMEM);
+    set[dev & 63] = true;
+  }
+  dim3 grid(8, 2, (B + AG - 1) / AG);
+  enc_lstm_persistent_kernel<AG><<<grid, PE_THREADS, PeCfg<AG>::SMEM, st>>>(d.T, B, lens, zx, kh, h_fin, c_fin, enc_states);
+  return 1;
+}
+
+// How many clusters of 8 CTAs with this kernel's footprint run at once on the current device.
+static int pe_max_clusters() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (cached[dev & 63] > 0) return cached[dev & 63];
+  cudaFuncSetAttribute(enc_lstm_persistent_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PeCfg<8>::SMEM);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(8, 2, 8); cfg.blockDim = dim3(PE_THREADS); cfg.dynamicSmemBytes = PeCfg<8>::SMEM;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 8; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, enc_lstm_persistent_kernel<8>, &cfg) != cudaSuccess || n < 2) { cudaGetLastError(); n = 14; }
+  cached[dev & 63] = n;
+  return n;
+}
+
 int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const float* kh,
                                float* h_fin, float* c_fin, float* enc_states, cudaStream_t st) {
-  static bool set = false;
-  if (!set) {
-    cudaFuncSetAttribute(enc_lstm_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PE_SMEM);
-    set = true;
-  }
-  dim3 grid(8, 2, (B + PE_AG - 1) / PE_AG);
-  enc_lstm_persistent_kernel<<<grid, PE_THREADS, PE_SMEM, st>>>(d.T, B, lens, zx, kh, h_fin, c_fin, enc_states);
-  return 1;
+  // the smallest group size whose 2 x ceil(B / AG) clusters are all co-resident
+  const int per_dir = pe_max_clusters() / 2;
+  static const char* force = getenv("PGEN_LSTM_AG");
+  const int forced = force ? atoi(force) : 0;
+  if (forced == 8 || (!forced && (B + 7) / 8 <= per_dir)) return pe_launch<8>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
+  if (forced == 10 || (!forced && (B + 9) / 10 <= per_dir)) return pe_launch<10>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
+  if (forced == 12 || (!forced && (B + 11) / 12 <= per_dir)) return pe_launch<12>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
+  return pe_launch<16>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
 }
 
 // ======================================================================================

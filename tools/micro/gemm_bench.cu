@@ -12,8 +12,7 @@ int main() {
   cudaMemset(a0, 0, R * 1024 * 4); cudaMemset(a1, 0, R * 1024 * 4); cudaMemset(b, 0, 1024 * 1024 * 4); cudaMemset(bias, 0, 4096);
   cudaStream_t st; cudaStreamCreate(&st);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-  for (int mode = 0; mode < 2; ++mode) {
-    if (mode == 1) setenv("PGEN_SKINNY1", "1", 1);
+  for (int mode = 0; mode < 1; ++mode) {
     for (auto& cs : cases) {
       GemmArgs g; g.A0 = a0; g.lda0 = 1024; g.k0 = cs.k0; g.A1 = a1; g.lda1 = 1024; g.k1 = cs.k1; g.B = b; g.ldb = cs.k0 + cs.k1;
       g.bias = bias; g.C = c; g.ldc = 1024; g.M = R; g.N = cs.N; g.skinny = 1;
@@ -22,10 +21,9 @@ int main() {
       for (int i = 0; i < 200; ++i) launch_gemm_nt(g, st);
       cudaEventRecord(e1, st); cudaEventSynchronize(e1);
       float ms; cudaEventElapsedTime(&ms, e0, e1);
-      printf("%s %s: %.2f us per launch (%s)\n", mode ? "old" : "new", cs.name, ms * 1000 / 200, cudaGetErrorString(cudaGetLastError()));
+      printf("%s: %.2f us per launch (%s)\n", cs.name, ms * 1000 / 200, cudaGetErrorString(cudaGetLastError()));
     }
   }
-  unsetenv("PGEN_SKINNY1");
   for (int M : {32, 128, 256}) for (int N : {128, 512, 1024}) for (int K : {256, 512, 1024}) {
     GemmArgs g; g.A0 = a0; g.lda0 = 1024; g.k0 = K; g.B = b; g.ldb = K; g.bias = bias; g.C = c; g.ldc = 1024; g.M = M; g.N = N; g.skinny = 1;
     for (int i = 0; i < 20; ++i) launch_gemm_nt(g, st);
