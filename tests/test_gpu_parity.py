@@ -262,3 +262,21 @@ def test_early_stop_polling_does_not_change_results(small_cfg, small_model_dir):
         got = dec.decode_ids(*native.pack_articles(arts, dec.max_enc_steps))
     for x, y in zip(ref, got):
         assert np.array_equal(x, y)
+
+
+def test_word_table_and_graph_replay_do_not_change_results(model_dir):
+    """The per-word input-projection table (--encoder_table) and the CUDA-graph replay of the decode steps are
+    pure re-arrangements: tokens and log-probs are bit-identical with either switched off."""
+    arts = synth.make_article_ids(6, seed=31)
+    outs = []
+    for extra, opts in (("--articles_per_batch=8", []), ("--articles_per_batch=8 --encoder_table=0", []),
+                        ("--articles_per_batch=8", ["graph=0"]), ("--articles_per_batch=8", ["graph_steps=4"])):
+        with native.Decoder(synth.hyperparams_string(model_dir, extra=extra)) as dec:
+            for o in opts:
+                dec.set_option(o)
+            packed = native.pack_articles(arts, dec.max_enc_steps)
+            dec.decode_ids(*packed)                      # first batch: plain launches, then the capture
+            outs.append(dec.decode_ids(*packed))         # second batch: replay
+    for got in outs[1:]:
+        for x, y in zip(outs[0], got):
+            assert np.array_equal(x, y)

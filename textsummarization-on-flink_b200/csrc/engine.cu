@@ -242,6 +242,20 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     DALLOC(smax_, float, (size_t)sstride_ * Rpad);
     DALLOC(artl_, float, R * T);
     if (!share) launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
+    if (H == 256 && hp.encoder_table) {
+      // The encoder's input projection depends on the token only: x.Kx + b of every vocabulary word, once per model
+      // (same GEMM kernel, so the rows are bit-identical to the per-batch projection), read by the recurrence by id.
+      if (share) zx_tab_ = share->zx_tab_;
+      else {
+        DALLOC(zx_tab_, float, 2 * V * 4 * H);
+        for (int dir = 0; dir < 2; ++dir) {
+          GemmArgs g;
+          g.A0 = w_.emb; g.lda0 = (int)E; g.k0 = (int)E; g.B = w_.enc_kxT[dir]; g.ldb = (int)E; g.bias = w_.enc_b[dir];
+          g.C = zx_tab_ + (size_t)dir * V * 4 * H; g.ldc = (int)(4 * H); g.M = (int)V; g.N = (int)(4 * H);
+          launch_gemm_nt(g, st_);
+        }
+      }
+    }
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
     else vtc_why_ = "vocabulary smaller than one 128-word tile";
     vocab_tc_ = vtc_.ready;
@@ -349,7 +363,8 @@ void Engine::encoder() {
   cudaMemsetAsync(enc_states_, 0, (size_t)B * T * A * sizeof(float), st_);   // outputs past enc_len are zero
   cudaMemsetAsync(h_enc_[0], 0, (size_t)2 * B * H * sizeof(float), st_);
   cudaMemsetAsync(c_enc_, 0, (size_t)2 * B * H * sizeof(float), st_);
-  for (int dir = 0; dir < 2; ++dir) {                  // zx = emb[ids] . Kx + bias   (model.py:213, LSTMCell)
+  const bool table = zx_tab_ && H == 256 && enc_persistent_;
+  for (int dir = 0; dir < 2 && !table; ++dir) {        // zx = emb[ids] . Kx + bias   (model.py:213, LSTMCell)
     GemmArgs g;
     g.A0 = w_.emb; g.lda0 = E; g.k0 = E; g.gather0 = ids_;
     g.B = w_.enc_kxT[dir]; g.ldb = E; g.bias = w_.enc_b[dir];
@@ -358,7 +373,8 @@ void Engine::encoder() {
   }
   const float* hfin;
   if (H == 256 && enc_persistent_) {                   // model.py:90-93, one launch
-    nl += launch_enc_lstm_persistent(d_, B, lens_, zx_, w_.enc_kh[0], h_enc_[1], c_enc_, enc_states_, st_);
+    nl += launch_enc_lstm_persistent(d_, B, lens_, table ? zx_tab_ : zx_, table ? ids_ : nullptr, w_.enc_kh[0], h_enc_[1], c_enc_,
+                                     enc_states_, st_);
     hfin = h_enc_[1];
   } else {
     for (int s = 0; s < max_len_; ++s)                 // model.py:90-93, one launch per time step

@@ -97,6 +97,7 @@ class Engine {
   double* h_out_avg_ = nullptr;
   // device batch slot
   int *ids_, *ext_, *lens_, *noov_, *uniq_, *ucnt_, *pstart_, *plist_;
+  float* zx_tab_ = nullptr;          // [2][V][4H] input projection of every word (shared by the handle's engines)
   float *zx_, *enc_states_, *enc_feat_, *h_enc_[2], *c_enc_;
   float *state_[2], *attn_[2], *cov_[2], *xin_, *hprev_, *cprev_, *z_, *dfeat_, *e_, *out_, *pgen_, *logits_,
       *rowmax_, *rowsum_, *topk_logp_;

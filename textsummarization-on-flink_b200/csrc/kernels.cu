@@ -337,6 +337,7 @@ __device__ __forceinline__ void pe_bar_wait(uint64_t* bar, uint32_t parity) {
 template <int AG>
 __global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(PE_THREADS, 1)
 enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const float* __restrict__ zx,
+                           const int* __restrict__ ids, int V,
                            const float* __restrict__ kh, float* __restrict__ h_fin, float* __restrict__ c_fin,
                            float* __restrict__ enc_states) {
   constexpr int AGP = PeCfg<AG>::AGP;
@@ -375,6 +376,7 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
   const int fb = b0 + fa;
   const int flen = (gate_thread && fb < B) ? lens[fb] : 0;
   float c_reg = 0.f, h_reg = 0.f;
+  int id_cur = (ids && flen > 0) ? __ldg(ids + (size_t)fb * T + (dir == 0 ? 0 : flen - 1)) : 0;
   // remote addresses of "my" h element and of the two barriers in each CTA of the cluster
   uint32_t r_h[8], r_bar[8];
 #pragma unroll
@@ -391,8 +393,12 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
     int t = -1;
     if (gate_thread && s < flen) {
       t = dir == 0 ? s : flen - 1 - s;             // backward: reversed over the article's own length
-      const float* zp = zx + ((size_t)dir * B * T + (size_t)fb * T + t) * H4 + 32 * c + ful;
+      // ids != 0: zx is the per-word table [2][V][4H] (x.Kx + b of every vocabulary word, computed once per model)
+      // and the row is the token's; otherwise zx is this batch's projection [2][B][T][4H]
+      const float* zp = ids ? zx + ((size_t)dir * V + id_cur) * H4 + 32 * c + ful
+                            : zx + ((size_t)dir * B * T + (size_t)fb * T + t) * H4 + 32 * c + ful;
       zi = __ldg(zp); zj = __ldg(zp + PE_H); zf = __ldg(zp + 2 * PE_H); zo = __ldg(zp + 3 * PE_H);
+      if (ids && s + 1 < flen) id_cur = __ldg(ids + (size_t)fb * T + (dir == 0 ? s + 1 : flen - 2 - s));   // next step's token
     }
     if (s > 0) {                                   // h(s-1) from all 8 CTAs has landed in hs[cur]
       pe_bar_wait(&hbar[cur], ((s - 1) >> 1) & 1);
@@ -458,8 +464,8 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
 }
 
 template <int AG>
-static int pe_launch(const Dims& d, int B, const int* lens, const float* zx, const float* kh, float* h_fin, float* c_fin,
-                     float* enc_states, cudaStream_t st) {
+static int pe_launch(const Dims& d, int B, const int* lens, const float* zx, const int* ids, const float* kh, float* h_fin,
+                     float* c_fin, float* enc_states, cudaStream_t st) {
   static bool set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -468,7 +474,7 @@ static int pe_launch(const Dims& d, int B, const int* lens, const float* zx, con
     set[dev & 63] = true;
   }
   dim3 grid(8, 2, (B + AG - 1) / AG);
-  enc_lstm_persistent_kernel<AG><<<grid, PE_THREADS, PeCfg<AG>::SMEM, st>>>(d.T, B, lens, zx, kh, h_fin, c_fin, enc_states);
+  enc_lstm_persistent_kernel<AG><<<grid, PE_THREADS, PeCfg<AG>::SMEM, st>>>(d.T, B, lens, zx, ids, d.V, kh, h_fin, c_fin, enc_states);
   return 1;
 }
 
@@ -490,16 +496,16 @@ static int pe_max_clusters() {
   return n;
 }
 
-int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const float* kh,
+int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const int* ids, const float* kh,
                                float* h_fin, float* c_fin, float* enc_states, cudaStream_t st) {
   // the smallest group size whose 2 x ceil(B / AG) clusters are all co-resident
   const int per_dir = pe_max_clusters() / 2;
   static const char* force = getenv("PGEN_LSTM_AG");
   const int forced = force ? atoi(force) : 0;
-  if (forced == 8 || (!forced && (B + 7) / 8 <= per_dir)) return pe_launch<8>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
-  if (forced == 10 || (!forced && (B + 9) / 10 <= per_dir)) return pe_launch<10>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
-  if (forced == 12 || (!forced && (B + 11) / 12 <= per_dir)) return pe_launch<12>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
-  return pe_launch<16>(d, B, lens, zx, kh, h_fin, c_fin, enc_states, st);
+  if (forced == 8 || (!forced && (B + 7) / 8 <= per_dir)) return pe_launch<8>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
+  if (forced == 10 || (!forced && (B + 9) / 10 <= per_dir)) return pe_launch<10>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
+  if (forced == 12 || (!forced && (B + 11) / 12 <= per_dir)) return pe_launch<12>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
+  return pe_launch<16>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
 }
 
 // ======================================================================================

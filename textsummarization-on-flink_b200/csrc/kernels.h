@@ -40,7 +40,9 @@ int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const flo
 
 // The whole recurrence in one launch (hidden_dim == 256 only): clusters of 8 CTAs, recurrent weights resident in
 // shared memory, h exchanged through DSMEM.  Writes the final (h, c) of both directions to h_fin / c_fin [2][B][H].
-int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const float* kh,
+// ids == nullptr: zx is the batch's input projection [2][B][T][4H];  ids != nullptr: zx is the per-word table
+// [2][V][4H] and ids [B][T] are the encoder tokens.
+int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const float* zx, const int* ids, const float* kh,
                                float* h_fin, float* c_fin, float* enc_states, cudaStream_t st);
 
 // ---- decoder step ----

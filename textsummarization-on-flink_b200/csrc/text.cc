@@ -57,7 +57,7 @@ std::vector<FlagRef> flag_table(HyperParams* h) {
       {"pointer_gen", 2, &h->pointer_gen}, {"coverage", 2, &h->coverage},
       {"convert_to_coverage_model", 2, &h->convert_to_coverage_model},
       {"restore_best_model", 2, &h->restore_best_model}, {"debug", 2, &h->debug},
-      {"articles_per_batch", 1, &h->articles_per_batch}, {"flush_ms", 1, &h->flush_ms}, {"slots", 1, &h->slots},
+      {"articles_per_batch", 1, &h->articles_per_batch}, {"flush_ms", 1, &h->flush_ms}, {"slots", 1, &h->slots}, {"encoder_table", 1, &h->encoder_table},
       {"weights_path", 0, &h->weights_path},
   };
 }

@@ -21,6 +21,7 @@ struct HyperParams {                       // run_summarization.py:48-88 (names 
   bool single_pass = false, inference = false, pointer_gen = true, coverage = false,
        convert_to_coverage_model = false, restore_best_model = false, debug = false;
   // Flags that only this library knows; the reference's parser ignores them (known_only=True).
+  int64_t encoder_table = 1;               // 1: keep x.Kx + b of every vocabulary word on the device (8 V H bytes x 4)
   int64_t articles_per_batch = 64;         // device-level article batching
   int64_t flush_ms = 50;                   // deadline after which poll() decodes a partial batch
   int64_t slots = 4;                       // device batches in flight per handle (each with its own stream)
