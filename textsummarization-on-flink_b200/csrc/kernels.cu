@@ -579,9 +579,12 @@ __device__ __forceinline__ float tanh_mufu(float x) {
   return fmaf(-2.0f, r, 1.0f);
 }
 
-template <int KMAX>
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+template <int KMAX, bool FULL>                     // FULL: all KMAX rows of the article are computed (rpa == KMAX)
 __global__ void __launch_bounds__(256)
-attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __restrict__ active,
+attn_energy_kernel(Dims d, int rpa_arg, const int* __restrict__ lens, const int* __restrict__ active,
                    const float* __restrict__ enc_feat, const float* __restrict__ dfeat,
                    const float* __restrict__ cov, const float* __restrict__ v, const float* __restrict__ w_c,
                    float* __restrict__ e) {
@@ -592,16 +595,24 @@ attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __r
   const int t0 = blockIdx.x * ATT_TCH;
   if (t0 >= len) return;
   const int A = d.A;
-  float* ds = sm;                 // [rpa][A]
+  const int rpa = FULL ? KMAX : rpa_arg;
+  constexpr float kS = 2.885390081777927f;          // 2 log2(e): everything below is pre-scaled, e^{2x} = 2^{kS x}
+  float* ds = sm;                 // [rpa][A]   kS * decoder features
   float* vs = ds + KMAX * A;      // [A]
   float* ws = vs + A;             // [A]
   for (int k = 0; k < rpa; ++k) {                       // no i / A here: a runtime integer division per element
     const float* src = dfeat + (size_t)(art * d.K + k) * A;           // costs more than the loads it indexes
-    for (int a = threadIdx.x; a < A; a += 256) ds[k * A + a] = src[a];
+    for (int a = threadIdx.x; a < A; a += 256) ds[k * A + a] = kS * src[a];
   }
-  for (int i = threadIdx.x; i < A; i += 256) { vs[i] = v[i]; ws[i] = d.use_cov ? w_c[i] : 0.f; }
+  for (int i = threadIdx.x; i < A; i += 256) { vs[i] = -2.0f * v[i]; ws[i] = d.use_cov ? kS * w_c[i] : 0.f; }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // sum of v over a: e = sum_a v_a tanh(x_a) = sum_a v_a - 2 sum_a v_a / (1 + exp(2 x_a))
+  float vsum = 0.f;
+  for (int a = lane; a < A; a += 32) vsum += vs[a];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) vsum += __shfl_xor_sync(0xffffffffu, vsum, o);
+  vsum *= -0.5f;
   for (int tt = warp; tt < ATT_TCH; tt += 8) {
     const int t = t0 + tt;
     if (t >= len) break;
@@ -612,19 +623,30 @@ attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __r
       cv[k] = (d.use_cov && k < rpa) ? cov[(size_t)(art * d.K + k) * d.T + t] : 0.f;
     }
     const float4* f4 = reinterpret_cast<const float4*>(enc_feat + ((size_t)art * d.T + t) * A);
+#pragma unroll 4
     for (int a4 = lane; a4 < A / 4; a4 += 32) {
       const float4 f = __ldg(f4 + a4);
-      const float4 vv = *reinterpret_cast<const float4*>(vs + a4 * 4);
-      const float4 ww = *reinterpret_cast<const float4*>(ws + a4 * 4);
+      const float4 vv = *reinterpret_cast<const float4*>(vs + a4 * 4);      // -2 v
+      const float4 ww = *reinterpret_cast<const float4*>(ws + a4 * 4);      // kS w_c
 #pragma unroll
       for (int k = 0; k < KMAX; ++k) {
-        if (k < rpa) {
+        if (FULL || k < rpa) {
           const float4 dd = *reinterpret_cast<const float4*>(ds + k * A + a4 * 4);
-          float x;
-          x = f.x + dd.x + cv[k] * ww.x; acc[k] = fmaf(vv.x, tanh_mufu(x), acc[k]);
-          x = f.y + dd.y + cv[k] * ww.y; acc[k] = fmaf(vv.y, tanh_mufu(x), acc[k]);
-          x = f.z + dd.z + cv[k] * ww.z; acc[k] = fmaf(vv.z, tanh_mufu(x), acc[k]);
-          x = f.w + dd.w + cv[k] * ww.w; acc[k] = fmaf(vv.w, tanh_mufu(x), acc[k]);
+          // tanh(x) = 1 - 2 / (1 + e^{2x}).  The four reciprocals share ONE rcp: r = 1 / (A0 A1 A2 A3), 1/A0 = r A1 A2 A3, ...
+          // x is clamped at 10 (tanh(10) rounds to 1.0f), so A_i <= 1 + e^20 and the product stays below 6e34.
+          const float y0 = fminf(fmaf(cv[k], ww.x, fmaf(f.x, kS, dd.x)), 10.f * kS);
+          const float y1 = fminf(fmaf(cv[k], ww.y, fmaf(f.y, kS, dd.y)), 10.f * kS);
+          const float y2 = fminf(fmaf(cv[k], ww.z, fmaf(f.z, kS, dd.z)), 10.f * kS);
+          const float y3 = fminf(fmaf(cv[k], ww.w, fmaf(f.w, kS, dd.w)), 10.f * kS);
+          const float A0 = 1.0f + ex2_approx(y0), A1 = 1.0f + ex2_approx(y1);
+          const float A2 = 1.0f + ex2_approx(y2), A3 = 1.0f + ex2_approx(y3);
+          const float p01 = A0 * A1, p23 = A2 * A3;
+          const float r = rcp_approx(p01 * p23);
+          const float r01 = r * p23, r23 = r * p01;                          // 1 / (A0 A1), 1 / (A2 A3)
+          float s = acc[k];
+          s = fmaf(vv.x, r01 * A1, s); s = fmaf(vv.y, r01 * A0, s);
+          s = fmaf(vv.z, r23 * A3, s); s = fmaf(vv.w, r23 * A2, s);
+          acc[k] = s;
         }
       }
     }
@@ -634,7 +656,126 @@ attn_energy_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __r
         float s = acc[k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) e[(size_t)(art * d.K + k) * d.T + t] = s;
+        if (lane == 0) e[(size_t)(art * d.K + k) * d.T + t] = vsum + s;
+      }
+    }
+  }
+}
+
+// All-rows variant (rpa == KMAX, KMAX even) on packed fp32 pairs: the two halves of every FFMA2 / FMUL2 / FADD2 are
+// the same encoder feature for two beam rows of the article, so the arithmetic of a row is exactly that of the scalar
+// kernel above at half the issue slots.  Lane l owns elements l, l + 32, l + 64, l + 96 of every 128-element chunk
+// (they share the reciprocal); the decoder features sit in shared memory as [a][row], one 128-bit read per element.
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ unsigned long long fma2_(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned long long mul2_(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ unsigned long long add2_(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+template <int KMAX, int ACH>                       // A = 128 ACH attention features
+__global__ void __launch_bounds__(256)
+attn_energy_pair_kernel(Dims d, const int* __restrict__ lens, const int* __restrict__ active,
+                        const float* __restrict__ enc_feat, const float* __restrict__ dfeat,
+                        const float* __restrict__ cov, const float* __restrict__ v, const float* __restrict__ w_c,
+                        float* __restrict__ e) {
+  static_assert(KMAX % 2 == 0, "rows are processed in pairs");
+  constexpr int NP = KMAX / 2;
+  extern __shared__ __align__(16) float sm[];
+  const int art = blockIdx.y;
+  if (!active[art]) return;
+  const int len = lens[art];
+  const int t0 = blockIdx.x * ATT_TCH;
+  if (t0 >= len) return;
+  constexpr int A = 128 * ACH;
+  constexpr float kS = 2.885390081777927f;          // 2 log2(e): operands are pre-scaled, e^{2x} = 2^{kS x}
+  float* ds = sm;                 // [A][KMAX]  kS * decoder features, row fastest
+  float* vs = ds + KMAX * A;      // [A]        -2 v
+  float* ws = vs + A;             // [A]        kS w_c
+  for (int k = 0; k < KMAX; ++k) {
+    const float* src = dfeat + (size_t)(art * d.K + k) * A;
+    for (int a = threadIdx.x; a < A; a += 256) ds[a * KMAX + k] = kS * src[a];
+  }
+  for (int i = threadIdx.x; i < A; i += 256) { vs[i] = -2.0f * v[i]; ws[i] = d.use_cov ? kS * w_c[i] : 0.f; }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float vsum = 0.f;
+  for (int a = lane; a < A; a += 32) vsum += vs[a];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) vsum += __shfl_xor_sync(0xffffffffu, vsum, o);
+  vsum *= -0.5f;                                    // sum of v: e = sum_a v_a - 2 sum_a v_a / (1 + e^{2 x_a})
+  const unsigned long long kS2 = pk2(kS, kS), one2 = pk2(1.0f, 1.0f);
+  for (int tt = warp; tt < ATT_TCH; tt += 8) {
+    const int t = t0 + tt;
+    if (t >= len) break;
+    unsigned long long cv2[NP], acc2[NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      acc2[p] = 0ull;
+      cv2[p] = d.use_cov ? pk2(cov[(size_t)(art * d.K + 2 * p) * d.T + t], cov[(size_t)(art * d.K + 2 * p + 1) * d.T + t]) : 0ull;
+    }
+    const float* fr = enc_feat + ((size_t)art * d.T + t) * A + lane;
+    float f[4 * ACH];                               // the whole feature row of this position is requested up front
+#pragma unroll
+    for (int i = 0; i < 4 * ACH; ++i) f[i] = __ldg(fr + 32 * i);
+#pragma unroll
+    for (int c = 0; c < ACH; ++c) {
+      unsigned long long vv2[4], ww2[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float vv = vs[c * 128 + lane + 32 * i], ww = ws[c * 128 + lane + 32 * i];
+        vv2[i] = pk2(vv, vv); ww2[i] = pk2(ww, ww);
+      }
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        unsigned long long Aq[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const unsigned long long dd = *reinterpret_cast<const unsigned long long*>(ds + (c * 128 + lane + 32 * i) * KMAX + 2 * p);
+          const unsigned long long y = fma2_(cv2[p], ww2[i], fma2_(pk2(f[4 * c + i], f[4 * c + i]), kS2, dd));
+          float y0, y1;
+          upk2(y, y0, y1);
+          // x is clamped at 10 (tanh(10) rounds to 1.0f): 1 + e^{2x} <= 1 + e^20 and the product of four stays below 6e34
+          Aq[i] = add2_(one2, pk2(ex2_approx(fminf(y0, 10.f * kS)), ex2_approx(fminf(y1, 10.f * kS))));
+        }
+        // the four reciprocals of a row share ONE rcp: r = 1 / (A0 A1 A2 A3), 1/A0 = r A1 A2 A3, ...
+        const unsigned long long p01 = mul2_(Aq[0], Aq[1]), p23 = mul2_(Aq[2], Aq[3]);
+        float q0, q1;
+        upk2(mul2_(p01, p23), q0, q1);
+        const unsigned long long r = pk2(rcp_approx(q0), rcp_approx(q1));
+        const unsigned long long r01 = mul2_(r, p23), r23 = mul2_(r, p01);
+        unsigned long long s2 = acc2[p];
+        s2 = fma2_(vv2[0], mul2_(r01, Aq[1]), s2);
+        s2 = fma2_(vv2[1], mul2_(r01, Aq[0]), s2);
+        s2 = fma2_(vv2[2], mul2_(r23, Aq[3]), s2);
+        s2 = fma2_(vv2[3], mul2_(r23, Aq[2]), s2);
+        acc2[p] = s2;
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      float s0, s1;
+      upk2(acc2[p], s0, s1);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o); }
+      if (lane == 0) {
+        e[(size_t)(art * d.K + 2 * p) * d.T + t] = vsum + s0;
+        e[(size_t)(art * d.K + 2 * p + 1) * d.T + t] = vsum + s1;
       }
     }
   }
@@ -646,15 +787,17 @@ int launch_attn_energy(const Dims& d, int B, int rpa, const int* lens, const int
   dim3 grid((d.T + ATT_TCH - 1) / ATT_TCH, B);
   if (d.K <= 4) {
     const size_t smem = (size_t)(4 * d.A + 2 * d.A) * sizeof(float);
-    attn_energy_kernel<4><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+    if (rpa == 4 && d.K == 4 && d.A == 512) attn_energy_pair_kernel<4, 4><<<grid, 256, smem, st>>>(d, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+    else attn_energy_kernel<4, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   } else if (d.K <= 8) {
     const size_t smem = (size_t)(8 * d.A + 2 * d.A) * sizeof(float);
-    attn_energy_kernel<8><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+    if (rpa == 8 && d.K == 8 && d.A == 512) attn_energy_pair_kernel<8, 4><<<grid, 256, smem, st>>>(d, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+    else attn_energy_kernel<8, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   } else {
     const size_t smem = (size_t)(16 * d.A + 2 * d.A) * sizeof(float);
     static bool set = false;
-    if (!set) { cudaFuncSetAttribute(attn_energy_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); set = true; }
-    attn_energy_kernel<16><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
+    if (!set) { cudaFuncSetAttribute(attn_energy_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); set = true; }
+    attn_energy_kernel<16, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   }
   return 1;
 }
