@@ -689,7 +689,7 @@ __device__ __forceinline__ unsigned long long add2_(unsigned long long a, unsign
 }
 
 template <int KMAX, int ACH>                       // A = 128 ACH attention features
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
 attn_energy_pair_kernel(Dims d, const int* __restrict__ lens, const int* __restrict__ active,
                         const float* __restrict__ enc_feat, const float* __restrict__ dfeat,
                         const float* __restrict__ cov, const float* __restrict__ v, const float* __restrict__ w_c,
@@ -854,48 +854,34 @@ attn_context_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __
   float4 acc[KMAX];
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-  int t = tl;
+  // rounds of 4 positions per thread (t = tl + 16 u + 64 round); the loads of the next round are in flight while this
+  // round is accumulated, so the memory latency is paid once per thread instead of once per round
+  float4 cur[4];
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {                                       // the prefetched positions t = tl + 16u
-    const int tu = tl + 16 * u;
-    if (tu < len) {
-#pragma unroll
-      for (int k = 0; k < KMAX; ++k) {
-        if (k < rpa) {
-          const float a = as[k * T + tu];
-          acc[k].x = fmaf(a, pre[u].x, acc[k].x); acc[k].y = fmaf(a, pre[u].y, acc[k].y);
-          acc[k].z = fmaf(a, pre[u].z, acc[k].z); acc[k].w = fmaf(a, pre[u].w, acc[k].w);
-        }
-      }
-    }
-  }
-  t = tl + 64;
-  for (; t + 48 < len; t += 64) {                                     // 4 independent 16-byte loads in flight
-    float4 h[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) h[u] = __ldg(reinterpret_cast<const float4*>(hb + (size_t)(t + 16 * u) * A));
+  for (int u = 0; u < 4; ++u) cur[u] = pre[u];
+  for (int t = tl; t < len; t += 64) {
+    float4 nxt[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
+      const int tn = t + 64 + 16 * u;
+      nxt[u] = tn < len ? __ldg(reinterpret_cast<const float4*>(hb + (size_t)tn * A)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
-      for (int k = 0; k < KMAX; ++k) {
-        if (k < rpa) {
-          const float a = as[k * T + t + 16 * u];
-          acc[k].x = fmaf(a, h[u].x, acc[k].x); acc[k].y = fmaf(a, h[u].y, acc[k].y);
-          acc[k].z = fmaf(a, h[u].z, acc[k].z); acc[k].w = fmaf(a, h[u].w, acc[k].w);
+    for (int u = 0; u < 4; ++u) {
+      const int tu = t + 16 * u;
+      if (tu < len) {
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+          if (k < rpa) {
+            const float a = as[k * T + tu];
+            acc[k].x = fmaf(a, cur[u].x, acc[k].x); acc[k].y = fmaf(a, cur[u].y, acc[k].y);
+            acc[k].z = fmaf(a, cur[u].z, acc[k].z); acc[k].w = fmaf(a, cur[u].w, acc[k].w);
+          }
         }
       }
     }
-  }
-  for (; t < len; t += 16) {
-    const float4 h = __ldg(reinterpret_cast<const float4*>(hb + (size_t)t * A));
 #pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-      if (k < rpa) {
-        const float a = as[k * T + t];
-        acc[k].x = fmaf(a, h.x, acc[k].x); acc[k].y = fmaf(a, h.y, acc[k].y);
-        acc[k].z = fmaf(a, h.z, acc[k].z); acc[k].w = fmaf(a, h.w, acc[k].w);
-      }
-    }
+    for (int u = 0; u < 4; ++u) cur[u] = nxt[u];
   }
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) {
