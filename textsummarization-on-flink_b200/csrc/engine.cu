@@ -41,6 +41,8 @@ Engine::~Engine() {
     if (p) cudaFreeHost(p);
   for (auto& e : ev_) if (e) cudaEventDestroy(e);
   for (auto& e : pev_) if (e) cudaEventDestroy(e);
+  if (st2_) cudaStreamDestroy(st2_);
+  for (auto& e : fev_) if (e) cudaEventDestroy(e);
   if (st_) cudaStreamDestroy(st_);
 }
 
@@ -193,6 +195,8 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   R_ = Bcap_ * d_.K;
   *code = PGEN_ERR_CUDA;
   CK(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&st2_, cudaStreamNonBlocking));
+  for (auto& e : fev_) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (auto& e : ev_) CK(cudaEventCreate(&e));
 
   *code = PGEN_ERR_IO;
@@ -428,7 +432,11 @@ int Engine::step_launch(int B, int o, int ps) {
     nl += launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[n], w_.v, w_.w_c, e_, st_);
     nl += launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[n], state_[n], st_);
     if (profile_) cudaEventRecord(pev_[5 * ps + 1], st_);
-    if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, st_);   // :166-167
+    // p_gen and the exact logits of the article's words are side branches (stream st2_, a parallel branch of the
+    // captured graph): they run beside the out projection and the tensor-core pass and join before the final kernel
+    const bool fork = d_.pointer_gen && vocab_tc_ && !profile_;
+    if (fork) { cudaEventRecord(fev_[0], st_); cudaStreamWaitEvent(st2_, fev_[0], 0); }
+    if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, fork ? st2_ : st_);   // :166-167
     // output = [h; ctx] . AttnOutputProjection + b                                (:173)
     g = GemmArgs(); g.A0 = state_[n] + A + H; g.lda0 = SW; g.k0 = H; g.A1 = state_[n]; g.lda1 = SW; g.k1 = A;
     g.B = w_.out_MT; g.ldb = H + A; g.bias = w_.out_b; g.C = out_; g.ldc = H; g.M = R; g.N = H; g.skinny = 1;
@@ -446,9 +454,12 @@ int Engine::step_launch(int B, int o, int ps) {
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
       if (profile_) cudaEventRecord(pev_[5 * ps + 2], st_);
+      if (fork) { cudaEventRecord(fev_[1], st_); cudaStreamWaitEvent(st2_, fev_[1], 0); }      // out_ is complete
+      if (fork) { nl += vtc_.launch_rescore(ma, B, st2_); cudaEventRecord(fev_[2], st2_); }   // exact fp32 logits of the article's words
       nl += vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, nullptr, st_);
       if (profile_) cudaEventRecord(pev_[5 * ps + 3], st_);
-      nl += vtc_.launch_rescore(ma, B, st_);                 // exact fp32 logits of the article's words
+      if (fork) cudaStreamWaitEvent(st_, fev_[2], 0);
+      else nl += vtc_.launch_rescore(ma, B, st_);
       nl += vtc_.launch_final(ma, st_);                      // candidates re-scored in fp32, copy mass, top-2K   (model.py:146-183, 284-285)
       if (profile_) cudaEventRecord(pev_[5 * ps + 4], st_);
     } else {

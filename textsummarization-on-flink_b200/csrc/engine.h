@@ -86,6 +86,8 @@ class Engine {
   std::vector<cudaEvent_t> pev_;   // 4 events per step when profiling: attn begin, attn end/vocab begin... 
   int pev_used_ = 0;
   cudaStream_t st_ = nullptr;
+  cudaStream_t st2_ = nullptr;       // side branch of a decode step (p_gen, article-word logits)
+  cudaEvent_t fev_[3] = {nullptr, nullptr, nullptr};
   cudaEvent_t ev_[7] = {};
   DeviceWeights w_{};
   std::vector<void*> allocs_;
