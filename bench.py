@@ -51,8 +51,9 @@ def config_dict(n_gpus: int) -> dict:
             "articles_per_step_per_gpu": ARTICLES_PER_STEP, "slots_in_flight": "library default (--slots=4) unless PGEN_BENCH_EXTRA overrides", "beam_size": BEAM, "max_enc_steps": T_ENC,
             "max_dec_steps": S_DEC, "vocab_size": V,
             "sharding": "articles sharded by rank, one GPU per rank, no collective on the data path (x%d)" % n_gpus,
-            "l2": "each step streams > 400 MB of per-batch tensors (zx 210 MB, enc states/features 105 MB, logits "
-                  "51 MB per decode step) -- larger than the 126 MB L2, no explicit flush"}
+            "l2": "no explicit flush: every decode step of every batch in flight streams its own 105 MB of encoder "
+                  "states/features plus the 51 MB projection (and 32 MB of exact rows), and a batch's encoder reads "
+                  "210 MB of the per-word table -- four batches in flight cycle > 600 MB through the 126 MB L2"}
 
 
 def peaks() -> dict:
@@ -183,8 +184,8 @@ def run_reference(args, rank: int, world: int):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cpu-articles", type=int, default=8, help="size of the bounded CPU-baseline sample")
     args = ap.parse_args()
@@ -326,16 +327,16 @@ def main():
                  "achieved": attn_bytes_total / (ps["ms_attention"] * 1e-3) / 1e9 if ps["ms_attention"] > 0 else None,
                  "peak": pk["hbm_gbs"], "unit": "GB/s", "ms_per_launch": ms_attn,
                  # dram__bytes_read.sum + dram__bytes_write.sum of one attn_energy + attn_context launch pair from the
-                 # ncu --set full capture summarised in profiles/r1_final_summary.md (batch with mean length 372:
+                 # ncu --set full capture summarised in profiles/r1b_summary.md (batch with mean length 372:
                  # 96.9 MB algorithmic): bytes per launch pair
-                 "traffic": 96.63e6, "algorithmic_bytes_per_launch": attn_bytes_total / max(1.0, n_prof)}
+                 "traffic": 96.60e6, "algorithmic_bytes_per_launch": attn_bytes_total / max(1.0, n_prof)}
     if roof_attn["achieved"]:
         roof_attn["frac"] = roof_attn["achieved"] / pk["hbm_gbs"]
     flops = 2.0 * R * H * V
     roof_vocab = {"bound": "tensor", "kernel": "vocab projection GEMM (per step)",
                   "achieved": flops / (ms_vocab * 1e-3) / 1e12 if ms_vocab > 0 else None,
                   "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "ms_per_launch": ms_vocab,
-                  "traffic": 51.80e6, "note": "tf32 operands (kind::tf32); peak is the measured bf16 figure, the tf32 "
+                  "traffic": 51.91e6, "note": "tf32 operands (kind::tf32); peak is the measured bf16 figure, the tf32 "
                                                "tensor peak is half of it; traffic = dram bytes of one vocab_tc_kernel launch"}
     if roof_vocab["achieved"]:
         roof_vocab["frac"] = roof_vocab["achieved"] / pk["bf16_tflops_sustained"]
