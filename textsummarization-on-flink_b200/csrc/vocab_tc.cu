@@ -545,6 +545,7 @@ vocab_final_kernel(MergeArgs a) {
     }
     for (int i = threadIdx.x; i <= nu; i += SEL_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
   }
+  if (threadIdx.x < SEL_WARPS * K2) ck[threadIdx.x] = 0ull;      // lists of step 4b: 0 = no entry
   if (threadIdx.x < K2) {                           // defaults, overwritten by the winners in step 4
     a.topk_ids[(size_t)r * K2 + threadIdx.x] = 0;
     a.topk_logp[(size_t)r * K2 + threadIdx.x] = -INFINITY;
@@ -666,43 +667,45 @@ vocab_final_kernel(MergeArgs a) {
     }
   }
   __syncthreads();
-  // ---- 4b: per-warp top-2K over a contiguous sixteenth of the keys (descending lists), then warp 0 merges the lists.
-  // Keys are unique ((value, ~id), ids distinct); equal values are rare, so the second redux runs only then.
+  // ---- 4b: top-2K by counting: every warp ranks the keys of a contiguous sixteenth among themselves (keys are
+  // unique: (value, ~id) with distinct ids) and lists its 2K best in descending order; then every list entry is
+  // ranked against the other lists by binary search and the 2K best overall are written out.
   {
     const int cw = (nf + SEL_WARPS - 1) / SEL_WARPS, c0 = warp * cw, c1 = min(nf, c0 + cw);
-    for (int round = 0; round < K2; ++round) {
-      unsigned long long best = 0ull; int bp = -1;
-      for (int c = c0 + lane; c < c1; c += 32) { const unsigned long long k = fin[c]; if (k > best) { best = k; bp = c; } }
-      const uint32_t hi = __reduce_max_sync(0xffffffffu, (uint32_t)(best >> 32));
-      uint32_t ball = __ballot_sync(0xffffffffu, best != 0ull && (uint32_t)(best >> 32) == hi);
-      if (__popc(ball) > 1) {
-        const uint32_t lo = __reduce_max_sync(0xffffffffu, ((ball >> lane) & 1u) ? (uint32_t)best : 0u);
-        ball = __ballot_sync(0xffffffffu, ((ball >> lane) & 1u) && (uint32_t)best == lo);
+    for (int cb = c0 + lane; cb < c1; cb += 64) {               // a lane ranks two of its keys per pass
+      const unsigned long long k0 = fin[cb], k1 = cb + 32 < c1 ? fin[cb + 32] : 0ull;
+      int r0 = 0, r1 = 0;
+      for (int c = c0; c < c1; ++c) {
+        const unsigned long long o = fin[c];
+        r0 += o > k0 ? 1 : 0; r1 += o > k1 ? 1 : 0;
       }
-      if (ball == 0u) { if (lane == 0) ck[warp * K2 + round] = 0ull; }
-      else if (lane == __ffs(ball) - 1) { ck[warp * K2 + round] = best; fin[bp] = 0ull; }
-      __syncwarp();
+      if (k0 && r0 < K2) ck[warp * K2 + r0] = k0;
+      if (k1 && r1 < K2) ck[warp * K2 + r1] = k1;
     }
   }
   __syncthreads();
-  if (warp == 0) {
-    int head = 0;
-    unsigned long long cur = lane < SEL_WARPS ? ck[lane * K2] : 0ull;
-    for (int round = 0; round < K2; ++round) {
-      const uint32_t hi = __reduce_max_sync(0xffffffffu, (uint32_t)(cur >> 32));
-      uint32_t ball = __ballot_sync(0xffffffffu, cur != 0ull && (uint32_t)(cur >> 32) == hi);
-      if (__popc(ball) > 1) {
-        const uint32_t lo = __reduce_max_sync(0xffffffffu, ((ball >> lane) & 1u) ? (uint32_t)cur : 0u);
-        ball = __ballot_sync(0xffffffffu, ((ball >> lane) & 1u) && (uint32_t)cur == lo);
+  if (threadIdx.x < SEL_WARPS * K2) {
+    const int w = threadIdx.x / K2, i = threadIdx.x - w * K2;
+    const unsigned long long mine = ck[threadIdx.x];
+    if (mine) {
+      int rank = i;
+      for (int w0 = 0; w0 < SEL_WARPS; w0 += 4) {
+        int cnt[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int st = 16; st > 0; st >>= 1) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int wq = w0 + q, idx = cnt[q] + st - 1;
+            if (wq != w && idx < K2 && ck[wq * K2 + idx] > mine) cnt[q] += st;
+          }
+        }
+        rank += cnt[0] + cnt[1] + cnt[2] + cnt[3];
       }
-      if (ball == 0u) break;                        // fewer than 2K entries: the defaults stay
-      if (lane == __ffs(ball) - 1) {
-        const uint32_t o = (uint32_t)(cur >> 32);
+      if (rank < K2) {
+        const uint32_t o = (uint32_t)(mine >> 32);
         const float v = __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu));
-        a.topk_ids[(size_t)r * K2 + round] = (int)(0xffffffffu - (uint32_t)cur);
-        a.topk_logp[(size_t)r * K2 + round] = logf(v);           // model.py:285
-        ++head;
-        cur = head < K2 ? ck[lane * K2 + head] : 0ull;
+        a.topk_ids[(size_t)r * K2 + rank] = (int)(0xffffffffu - (uint32_t)mine);
+        a.topk_logp[(size_t)r * K2 + rank] = logf(v);            // model.py:285
       }
     }
   }
