@@ -298,11 +298,34 @@ int launch_enc_lstm_step(const Dims& d, int B, int s, const int* lens, const flo
 // shared memory through DSMEM; one cluster barrier per time step.  c stays in registers.
 // --------------------------------------------------------------------------------------
 namespace cgx = cooperative_groups;
+// packed fp32 pairs (FFMA2 / FMUL2 / FADD2): each half is an ordinary IEEE fp32 operation
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ unsigned long long fma2_(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned long long mul2_(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ unsigned long long add2_(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
 constexpr int PE_H = 256, PE_THREADS = 512;
 template <int AG> struct PeCfg {                      // AG articles per cluster
   static constexpr int AGP = (AG + 3) & ~3;           // row pitch of the h buffers (float4 loads)
-  static constexpr size_t SMEM = (size_t)(PE_H * 128 + 2 * PE_H * AGP + 8 * AG * 128) * sizeof(float) + 64;
-  static constexpr uint32_t H_BYTES = PE_H * AG * sizeof(float);   // one full h(s) of the group
+  static constexpr size_t SMEM = (size_t)(PE_H * 128 + 2 * PE_H * AGP + 8 * AG * 128 + 2 * 32 * AGP) * sizeof(float) + 64;
+  static constexpr uint32_t H_BYTES = PE_H * AGP * sizeof(float);  // one full h(s) of the group (padded rows)
 };
 
 __device__ __forceinline__ uint32_t pe_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -346,7 +369,8 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
   float* Ws = sm;                                  // [256 k][128 local cols]
   float* hs = Ws + PE_H * 128;                     // [2][256 k][AGP articles]
   float* red = hs + 2 * PE_H * AGP;                // [8 kq][AG articles][128 cols]
-  uint64_t* hbar = reinterpret_cast<uint64_t*>(red + 8 * AG * 128);   // [2] "h buffer b is complete"
+  float* hstage = red + 8 * AG * 128;              // [2][32 units][AGP] this CTA's new h, source of the bulk copies
+  uint64_t* hbar = reinterpret_cast<uint64_t*>(hstage + 2 * 32 * AGP);   // [2] "h buffer b is complete"
   cgx::cluster_group cluster = cgx::this_cluster();
   const int c = (int)cluster.block_rank();         // which 32 hidden units
   const int dir = blockIdx.y, b0 = blockIdx.z * AG;
@@ -360,6 +384,7 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
     Ws[i] = khd[(size_t)k * H4 + g * PE_H + 32 * c + ul];
   }
   for (int i = tid; i < 2 * PE_H * AGP; i += PE_THREADS) hs[i] = 0.f;
+  for (int i = tid; i < 2 * 32 * AGP; i += PE_THREADS) hstage[i] = 0.f;
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(pe_smem_u32(&hbar[b])));
@@ -377,13 +402,10 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
   const int flen = (gate_thread && fb < B) ? lens[fb] : 0;
   float c_reg = 0.f, h_reg = 0.f;
   int id_cur = (ids && flen > 0) ? __ldg(ids + (size_t)fb * T + (dir == 0 ? 0 : flen - 1)) : 0;
-  // remote addresses of "my" h element and of the two barriers in each CTA of the cluster
-  uint32_t r_h[8], r_bar[8];
-#pragma unroll
-  for (int rk = 0; rk < 8; ++rk) {
-    r_h[rk] = pe_mapa(pe_smem_u32(hs + (32 * c + ful) * AGP + (gate_thread ? fa : 0)), rk);
-    r_bar[rk] = pe_mapa(pe_smem_u32(&hbar[0]), rk);
-  }
+  // thread rk < 8 sends this CTA's 32 x AGP block of new h to CTA rk of the cluster with ONE bulk copy per step
+  // (cp.async.bulk shared::cta -> shared::cluster), which also signals that CTA's mbarrier with the bytes written
+  const uint32_t r_dst = pe_mapa(pe_smem_u32(hs + 32 * c * AGP), tid & 7);
+  const uint32_t r_bar = pe_mapa(pe_smem_u32(&hbar[0]), tid & 7);
   cluster.sync();
 
   for (int s = 0; s < grp_max; ++s) {
@@ -406,25 +428,26 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pe_smem_u32(&hbar[cur])), "r"(H_BYTES) : "memory");
     }
     // partial h . Kh over this thread's k range
-    float acc0[AGP], acc1[AGP];
+    // packed fp32 pairs over two articles: acc0p[q] = (article 2q, article 2q+1) of column cp, acc1p of column cp + 64
+    unsigned long long acc0p[AGP / 2], acc1p[AGP / 2];
 #pragma unroll
-    for (int a = 0; a < AGP; ++a) { acc0[a] = 0.f; acc1[a] = 0.f; }
+    for (int a = 0; a < AGP / 2; ++a) { acc0p[a] = 0ull; acc1p[a] = 0ull; }
     const float* hcur = hs + cur * PE_H * AGP;
 #pragma unroll 4
     for (int kk = 0; kk < 32; ++kk) {
       const int k = kq * 32 + kk;
       const float w0 = Ws[k * 128 + cp], w1 = Ws[k * 128 + cp + 64];
+      const unsigned long long w0p = pk2(w0, w0), w1p = pk2(w1, w1);
 #pragma unroll
       for (int q = 0; q < AGP / 4; ++q) {
-        const float4 h4 = *reinterpret_cast<const float4*>(hcur + k * AGP + 4 * q);
-        acc0[4 * q + 0] = fmaf(h4.x, w0, acc0[4 * q + 0]); acc1[4 * q + 0] = fmaf(h4.x, w1, acc1[4 * q + 0]);
-        acc0[4 * q + 1] = fmaf(h4.y, w0, acc0[4 * q + 1]); acc1[4 * q + 1] = fmaf(h4.y, w1, acc1[4 * q + 1]);
-        if (4 * q + 2 < AG) {
-          acc0[4 * q + 2] = fmaf(h4.z, w0, acc0[4 * q + 2]); acc1[4 * q + 2] = fmaf(h4.z, w1, acc1[4 * q + 2]);
-          acc0[4 * q + 3] = fmaf(h4.w, w0, acc0[4 * q + 3]); acc1[4 * q + 3] = fmaf(h4.w, w1, acc1[4 * q + 3]);
-        }
+        const ulonglong2 h4 = *reinterpret_cast<const ulonglong2*>(hcur + k * AGP + 4 * q);
+        acc0p[2 * q] = fma2_(h4.x, w0p, acc0p[2 * q]); acc1p[2 * q] = fma2_(h4.x, w1p, acc1p[2 * q]);
+        if (4 * q + 2 < AG) { acc0p[2 * q + 1] = fma2_(h4.y, w0p, acc0p[2 * q + 1]); acc1p[2 * q + 1] = fma2_(h4.y, w1p, acc1p[2 * q + 1]); }
       }
     }
+    float acc0[AGP], acc1[AGP];
+#pragma unroll
+    for (int a = 0; a < AGP / 2; ++a) { upk2(acc0p[a], acc0[2 * a], acc0[2 * a + 1]); upk2(acc1p[a], acc1[2 * a], acc1[2 * a + 1]); }
     // The partial sums of step s overwrite those of step s-1: every thread that read them has since issued its
     // st.async, and nobody gets here before ALL of those have landed (the wait above).
 #pragma unroll
@@ -447,12 +470,20 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
         h_reg = hn;
         enc_states[((size_t)fb * T + t) * (2 * PE_H) + dir * PE_H + 32 * c + ful] = hn;   // model.py:93
       }
-      // new h (or the frozen one past the article's end) into buffer cur^1 of every CTA of the cluster; each
-      // store adds its 4 bytes to that CTA's barrier for the buffer
+      // new h (or the frozen one past the article's end) into this step's staging buffer
       if (s + 1 < grp_max) {
+        hstage[(cur ^ 1) * 32 * AGP + ful * AGP + fa] = hn;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> async-proxy reads
+      }
+    }
+    if (s + 1 < grp_max && tid < 32 * AG) {
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * AG) : "memory");          // the gate warps only
+      if (tid < 8) {
+        // The staging buffer written two steps ago is free: every CTA has since passed a wait that needed that copy.
+        const uint32_t src = pe_smem_u32(hstage + (cur ^ 1) * 32 * AGP);
         const uint32_t boff = (uint32_t)(cur ^ 1) * (uint32_t)(PE_H * AGP * sizeof(float)), bar_off = (uint32_t)(cur ^ 1) * 8u;
-#pragma unroll
-        for (int rk = 0; rk < 8; ++rk) pe_st_async(r_h[rk] + boff, hn, r_bar[rk] + bar_off);
+        asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(r_dst + boff), "r"(src), "n"(32 * AGP * 4), "r"(r_bar + bar_off) : "memory");
       }
     }
   }
@@ -504,8 +535,7 @@ int launch_enc_lstm_persistent(const Dims& d, int B, const int* lens, const floa
   const int forced = force ? atoi(force) : 0;
   if (forced == 8 || (!forced && (B + 7) / 8 <= per_dir)) return pe_launch<8>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
   if (forced == 10 || (!forced && (B + 9) / 10 <= per_dir)) return pe_launch<10>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
-  if (forced == 12 || (!forced && (B + 11) / 12 <= per_dir)) return pe_launch<12>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
-  return pe_launch<16>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);
+  return pe_launch<12>(d, B, lens, zx, ids, kh, h_fin, c_fin, enc_states, st);     // larger batches: more than one wave
 }
 
 // ======================================================================================
@@ -666,28 +696,6 @@ attn_energy_kernel(Dims d, int rpa_arg, const int* __restrict__ lens, const int*
 // the same encoder feature for two beam rows of the article, so the arithmetic of a row is exactly that of the scalar
 // kernel above at half the issue slots.  Lane l owns elements l, l + 32, l + 64, l + 96 of every 128-element chunk
 // (they share the reciprocal); the decoder features sit in shared memory as [a][row], one 128-bit read per element.
-__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
-  unsigned long long r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ unsigned long long fma2_(unsigned long long a, unsigned long long b, unsigned long long c) {
-  unsigned long long d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-__device__ __forceinline__ unsigned long long mul2_(unsigned long long a, unsigned long long b) {
-  unsigned long long d;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-__device__ __forceinline__ unsigned long long add2_(unsigned long long a, unsigned long long b) {
-  unsigned long long d;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-
 template <int KMAX, int ACH>                       // A = 128 ACH attention features
 __global__ void __launch_bounds__(256, 5)
 attn_energy_pair_kernel(Dims d, const int* __restrict__ lens, const int* __restrict__ active,
