@@ -280,3 +280,34 @@ def test_word_table_and_graph_replay_do_not_change_results(model_dir):
     for got in outs[1:]:
         for x, y in zip(outs[0], got):
             assert np.array_equal(x, y)
+
+
+def test_features_on_tensor_cores_match_fp32(model_dir):
+    """W_h.h_i by the 3xTF32 tcgen05 GEMM against the fp32 SIMT GEMM on the same encoder states, and against a float64
+    product of those states.  The split operands are exact to 2^-22, but the tensor core's fp32 accumulator truncates, so
+    over K = 512 the result is ~1e-5 absolute from the exact product on O(1) values (the fp32 FMA chain: ~1e-6); the
+    bound below is what the decode parity (log-probs within 1e-3) is run with."""
+    from textsummarization_on_flink_b200 import weights_io
+    flags = synth.hyperparams_string(model_dir, max_dec_steps=1, min_dec_steps=0, extra="--articles_per_batch=16")
+    W = weights_io.load_weights(model_dir["weights"])
+    Wh = W["seq2seq/decoder/attention_decoder/W_h"].reshape(512, 512).astype(np.float64)
+    arts = synth.make_article_ids(16, seed=41)
+    got = {}
+    with native.Decoder(flags) as dec:
+        packed = native.pack_articles(arts, dec.max_enc_steps)
+        n, T, A = len(arts), dec.max_enc_steps, 512
+        for mode in ("tc", "simt"):
+            dec.set_option("features=" + mode)
+            dec.stage_upload(*packed)
+            dec.stage_run()
+            dec.stage_sync()
+            got[mode] = dec.debug_fetch("enc_feat", n * T * A).reshape(n, T, A)
+        es = dec.debug_fetch("enc_states", n * T * A).reshape(n, T, A)
+    err = {}
+    for b, (a, _, _) in enumerate(arts):
+        L = len(a)
+        exact = es[b, :L].astype(np.float64) @ Wh
+        for mode in got:
+            err[mode] = max(err.get(mode, 0.0), float(np.abs(got[mode][b, :L] - exact).max()))
+        np.testing.assert_allclose(got["tc"][b, :L], got["simt"][b, :L], atol=2e-5, rtol=1e-4)
+    assert err["simt"] <= 5e-6 and err["tc"] <= 2e-5, err

@@ -260,6 +260,20 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
         }
       }
     }
+    if (A % 256 == 0) {
+      // W_h . h_i on the tensor cores with fp32 accuracy (3xTF32): hi/lo parts of the weights once per model, of the
+      // encoder states once per batch
+      const size_t A2 = A * A, n_es = B * T * A;
+      if (share) { wh_hi_ = share->wh_hi_; wh_lo_ = share->wh_lo_; }
+      else {
+        DALLOC(wh_hi_, float, A2); DALLOC(wh_lo_, float, A2);
+        launch_split_tf32(w_.WhT, wh_hi_, wh_lo_, A2, st_);
+      }
+      DALLOC(es_hi_, float, n_es); DALLOC(es_lo_, float, n_es);
+      std::string why = g3_.init(es_hi_, es_lo_, (int)(B * T), wh_hi_, wh_lo_, (int)A, (int)A, n_sms_);
+      feat_tc_ = g3_.ready;
+      (void)why;
+    }
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
     else vtc_why_ = "vocabulary smaller than one 128-word tile";
     vocab_tc_ = vtc_.ready;
@@ -277,6 +291,7 @@ std::string Engine::set_option(const std::string& kv) {
   if (k == "graph") { use_graph_ = v != "0"; return ""; }
   if (k == "graph_steps") { graph_steps_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "check_every") { check_every_ = std::max(0, atoi(v.c_str())); return ""; }
+  if (k == "features") { feat_tc_ = (v != "simt") && g3_.ready; return ""; }
   if (k == "encoder") { enc_persistent_ = (v != "steps"); return ""; }
   if (k == "vocab") {
     if (v == "simt") { vocab_tc_ = false; return ""; }
@@ -396,10 +411,15 @@ void Engine::encoder() {
     nl += launch_gemm_nt(g, st_);
   }
   {                                                    // attention_decoder.py:67, once per article
-    GemmArgs g;
-    g.A0 = enc_states_; g.lda0 = A; g.k0 = A; g.B = w_.WhT; g.ldb = A;
-    g.C = enc_feat_; g.ldc = A; g.M = B * T; g.N = A;
-    nl += launch_gemm_nt(g, st_);
+    if (feat_tc_) {
+      nl += launch_split_tf32(enc_states_, es_hi_, es_lo_, (size_t)B * T * A, st_);
+      nl += g3_.launch(B * T, enc_feat_, A, st_);
+    } else {
+      GemmArgs g;
+      g.A0 = enc_states_; g.lda0 = A; g.k0 = A; g.B = w_.WhT; g.ldb = A;
+      g.C = enc_feat_; g.ldc = A; g.M = B * T; g.N = A;
+      nl += launch_gemm_nt(g, st_);
+    }
   }
 }
 

@@ -99,6 +99,9 @@ class Engine {
   double* h_out_avg_ = nullptr;
   // device batch slot
   int *ids_, *ext_, *lens_, *noov_, *uniq_, *ucnt_, *pstart_, *plist_;
+  float *wh_hi_ = nullptr, *wh_lo_ = nullptr, *es_hi_ = nullptr, *es_lo_ = nullptr;   // 3xTF32 operands of W_h . h_i
+  GemmTC3 g3_;
+  bool feat_tc_ = false;
   float* zx_tab_ = nullptr;          // [2][V][4H] input projection of every word (shared by the handle's engines)
   float *zx_, *enc_states_, *enc_feat_, *h_enc_[2], *c_enc_;
   float *state_[2], *attn_[2], *cov_[2], *xin_, *hprev_, *cprev_, *z_, *dfeat_, *e_, *out_, *pgen_, *logits_,

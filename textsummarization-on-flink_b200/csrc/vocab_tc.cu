@@ -123,6 +123,11 @@ __device__ __forceinline__ float ex2_ftz(float x) {           // one MUFU.EX2, n
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+__device__ __forceinline__ float tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
 // packed fp32 pairs (FFMA2 / FADD2): two results per issue slot -- the epilogue is issue-bound
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
   uint64_t r;
@@ -335,6 +340,147 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// C[M, N] = A[M, K] . B[N, K]^T on the tensor cores with split operands ("3xTF32"): every fp32 operand is split into
+// hi = tf32(x) and lo = tf32(x - hi); a.b ~ a_lo.b_hi + a_hi.b_lo + a_hi.b_hi (the lo.lo term is 2^-22 relative), every
+// product exact; the tensor core's fp32 accumulator truncates, which leaves ~1e-5 absolute on O(1) sums over K = 512
+// (measured in tests/test_gpu_parity.py::test_features_on_tensor_cores_match_fp32; an fp32 FMA chain gives ~1e-6).  Same CTA-pair structure as the vocabulary kernel (cta_group::2, 256 x 256 x 8
+// MMAs, each CTA stages its 128 rows of A and 128 rows of B), but both operands stream: a stage holds
+// [A_hi | A_lo | B_hi | B_lo] of one 32-wide k-block, 64 KB.  Work item = (256-row block, 256-column block).
+// Used for the once-per-article W_h.h_i features (attention_decoder.py:67).
+// ---------------------------------------------------------------------------------------------
+constexpr int G3_STAGES = 3;
+constexpr int G3_STAGE_BYTES = 4 * TILE_BYTES;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
+gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
+                const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl,
+                int M, int N, int KB, int n_mblk, int n_nblk, float* __restrict__ C, int ldc) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)G3_STAGES * G3_STAGE_BYTES);
+  uint64_t* full = bars;                  // [STAGES] leader's: both CTAs' tiles of the stage have landed
+  uint64_t* empty = bars + G3_STAGES;     // [STAGES] each CTA's: the MMAs reading the stage have retired
+  uint64_t* t_full = bars + 2 * G3_STAGES;   // [2] each CTA's
+  uint64_t* t_empty = t_full + 2;            // [2] leader's
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t crank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int n_items = n_mblk * n_nblk;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < G3_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&t_full[a], 1); mbar_init(&t_empty[a], 2 * (EPI_THREADS / 32)); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int item = pair; item < n_items; item += n_pairs) {
+        const int mrow = (item / n_nblk) * 2 * BM + (int)crank * BM, nrow = (item % n_nblk) * BN + (int)crank * BNH;
+        for (int kb = 0; kb < KB; ++kb, ++it) {
+          const int s = it % G3_STAGES;
+          mbar_wait(&empty[s], ((it / G3_STAGES) & 1) ^ 1);
+          if (crank == 0) mbar_expect_tx(&full[s], 2u * G3_STAGE_BYTES);
+          const uint32_t fl = mapa_rank(&full[s], 0);
+          unsigned char* st = smem + (size_t)s * G3_STAGE_BYTES;
+          tma_load_2d_pair(st, &tmAh, fl, kb * BK, mrow);
+          tma_load_2d_pair(st + TILE_BYTES, &tmAl, fl, kb * BK, mrow);
+          tma_load_2d_pair(st + 2 * TILE_BYTES, &tmBh, fl, kb * BK, nrow);
+          tma_load_2d_pair(st + 3 * TILE_BYTES, &tmBl, fl, kb * BK, nrow);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && crank == 0) {
+      uint32_t it = 0, tcount = 0;
+      for (int item = pair; item < n_items; item += n_pairs, ++tcount) {
+        const int acc = tcount & 1;
+        mbar_wait(&t_empty[acc], ((tcount >> 1) & 1) ^ 1);
+        tc_fence_after();
+        for (int kb = 0; kb < KB; ++kb, ++it) {
+          const int s = it % G3_STAGES;
+          mbar_wait(&full[s], (it / G3_STAGES) & 1);
+          tc_fence_after();
+          const uint32_t sb = smem_u32(smem + (size_t)s * G3_STAGE_BYTES);
+          const uint64_t ah = smem_desc_sw128(sb), al = smem_desc_sw128(sb + TILE_BYTES);
+          const uint64_t bh = smem_desc_sw128(sb + 2 * TILE_BYTES), bl = smem_desc_sw128(sb + 3 * TILE_BYTES);
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4) {                      // small terms first, then the leading product
+            const uint64_t o = (uint64_t)(k4 * 2);
+            tc_mma_tf32_pair(tmem_base + acc * BN, al + o, bh + o, kIdesc, (kb | k4) != 0);
+            tc_mma_tf32_pair(tmem_base + acc * BN, ah + o, bl + o, kIdesc, 1);
+            tc_mma_tf32_pair(tmem_base + acc * BN, ah + o, bh + o, kIdesc, 1);
+          }
+          tc_commit_pair(&empty[s]);
+        }
+        tc_commit_pair(&t_full[acc]);
+      }
+    }
+  } else {
+    // epilogue: thread == row, two warps per TMEM lane quarter, each writing 128 of the tile's 256 columns
+    const int ew = warp - 2, q = warp & 3, half = ew >> 2;
+    const uint32_t t_empty_l0 = mapa_rank(&t_empty[0], 0), t_empty_l1 = mapa_rank(&t_empty[1], 0);
+    uint32_t tcount = 0;
+    for (int item = pair; item < n_items; item += n_pairs, ++tcount) {
+      const int acc = tcount & 1;
+      const int row = (item / n_nblk) * 2 * BM + (int)crank * BM + q * 32 + lane;
+      const int col0 = (item % n_nblk) * BN + half * 128;
+      mbar_wait(&t_full[acc], (tcount >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * 128);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t raw[32];
+        tmem_ld32(tbase + 32 * c, raw);
+        tmem_ld_wait();
+        if (row < M) {
+          float4* dst = reinterpret_cast<float4*>(C + (size_t)row * ldc + col0 + 32 * c);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            dst[j] = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
+                                 __uint_as_float(raw[4 * j + 3]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(acc ? t_empty_l1 : t_empty_l0);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+  }
+}
+
+// hi = tf32(x), lo = tf32(x - hi): x = hi + lo up to 2^-22 relative
+__global__ void split_tf32_kernel(const float* __restrict__ in, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  const float4 x = *reinterpret_cast<const float4*>(in + i);
+  float4 h, l;
+  h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
+  l.x = tf32_rna(x.x - h.x); l.y = tf32_rna(x.y - h.y); l.z = tf32_rna(x.z - h.z); l.w = tf32_rna(x.w - h.w);
+  *reinterpret_cast<float4*>(hi + i) = h;
+  *reinterpret_cast<float4*>(lo + i) = l;
+}
+
 __global__ void round_tf32_kernel(const float* __restrict__ in, float* __restrict__ out, size_t n) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -440,11 +586,6 @@ vocab_rescore_kernel(MergeArgs a) {
 // ---------------------------------------------------------------------------------------------
 constexpr int SEL_THREADS = 512, SEL_WARPS = SEL_THREADS / 32;
 
-__device__ __forceinline__ float tf32_rna(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return __uint_as_float(r);
-}
 
 
 // Order-preserving map float -> uint32 (larger float <=> larger key).
@@ -799,6 +940,42 @@ int VocabTC::launch_final(const MergeArgs& a, cudaStream_t st) const {
     set[dev & 63] = smem;
   }
   vocab_final_kernel<<<a.R, SEL_THREADS, smem, st>>>(a);
+  return 1;
+}
+
+// ---- 3xTF32 GEMM
+std::string GemmTC3::init(const float* a_hi, const float* a_lo, int M_, const float* b_hi, const float* b_lo, int N_, int K_,
+                          int n_sms) {
+  M = M_; N = N_; K = K_; sms = n_sms;
+  if (K % BK != 0 || N % BN != 0) return "3xTF32 GEMM needs K % 32 == 0 and N % 256 == 0";
+  void* fnp = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fnp, cudaEnableDefault, &q) != cudaSuccess || !fnp)
+    return "cuTensorMapEncodeTiled is not available from the driver";
+  EncodeTiledFn fn = (EncodeTiledFn)fnp;
+  std::string err = make_map(fn, &tmAh, a_hi, M, K);
+  if (err.empty()) err = make_map(fn, &tmAl, a_lo, M, K);
+  if (err.empty()) err = make_map(fn, &tmBh, b_hi, N, K);
+  if (err.empty()) err = make_map(fn, &tmBl, b_lo, N, K);
+  if (!err.empty()) return err;
+  const int smem = G3_STAGES * G3_STAGE_BYTES + 1024 + 256;
+  if (cudaFuncSetAttribute(gemm_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+    return "cudaFuncSetAttribute(gemm_tc3_kernel) failed";
+  ready = true;
+  return "";
+}
+
+int GemmTC3::launch(int rows, float* C, int ldc, cudaStream_t st) const {
+  const int n_mblk = (rows + 2 * BM - 1) / (2 * BM), n_nblk = N / BN;
+  const int pairs = std::max(1, std::min(sms / 2, n_mblk * n_nblk));
+  gemm_tc3_kernel<<<2 * pairs, NTHREADS, G3_STAGES * G3_STAGE_BYTES + 1024 + 256, st>>>(tmAh, tmAl, tmBh, tmBl, rows, N, K / BK,
+                                                                                    n_mblk, n_nblk, C, ldc);
+  return 1;
+}
+
+int launch_split_tf32(const float* in, float* hi, float* lo, size_t n, cudaStream_t st) {
+  if (n == 0) return 0;
+  split_tf32_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, st>>>(in, hi, lo, n);
   return 1;
 }
 

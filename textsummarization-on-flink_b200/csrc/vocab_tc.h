@@ -43,6 +43,21 @@ class VocabTC {
   int V = 0, H = 0, K2 = 0, KB = 0, n_tiles = 0, sms = 148;
 };
 
+// C[rows, N] = A[rows, K] . B[N, K]^T on the tensor cores with split operands (3xTF32, ~1e-5 absolute on O(1) sums);
+// the operands are given as their
+// tf32 hi / lo parts (launch_split_tf32), at fixed device addresses baked into the TMA descriptors.
+class GemmTC3 {
+ public:
+  std::string init(const float* a_hi, const float* a_lo, int M, const float* b_hi, const float* b_lo, int N, int K, int n_sms);
+  int launch(int rows, float* C, int ldc, cudaStream_t st) const;
+  bool ready = false;
+
+ private:
+  CUtensorMap tmAh, tmAl, tmBh, tmBl;
+  int M = 0, N = 0, K = 0, sms = 148;
+};
+
 int launch_round_tf32(const float* in, float* out, size_t n, cudaStream_t st);
+int launch_split_tf32(const float* in, float* hi, float* lo, size_t n, cudaStream_t st);   // n % 4 == 0
 
 }  // namespace pgn
