@@ -7,7 +7,7 @@ import pytest
 
 import pgen_oracle as O
 from conftest import small_flags
-from textsummarization_on_flink_b200 import pipeline
+from textsummarization_on_flink_b200 import pipeline, synth
 
 
 def create_model(hyper):
@@ -76,3 +76,18 @@ def test_model_inference_rows(small_cfg, small_model_dir):
     # output schema is honoured
     out3 = list(create_model(flags).setInferenceOutputCols(["uuid", "summary"]).setInferenceOutputTypes([pipeline.STRING] * 2).transform(rows))
     assert [list(r) for r in out3] == [["uuid", "summary"]] * 8 and [r["summary"] for r in out3] == [r["summary"] for r in out]
+
+
+@pytest.mark.gpu
+def test_two_subtasks_on_two_devices_in_one_process(model_dir):
+    """worker_num = 2 with one GPU per subtask inside ONE process (two handles on two devices): full-size model, so
+    every per-device kernel attribute and descriptor is exercised on both devices.  Needs two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    flags = synth.hyperparams_string(model_dir, extra="--articles_per_batch=4").split(" ")
+    arts = synth.make_article_ids(8, seed=17)
+    rows = [{"uuid": "u%d" % i, "article": synth.ids_to_article(e, 50000, salt=i), "reference": "r"} for i, (_, e, _) in enumerate(arts)]
+    one = list(create_model(flags).transform(rows, devices=[0]))
+    two = list(create_model(flags).setWorkerNum(2).transform(rows, devices=[0, 1]))
+    assert two == one

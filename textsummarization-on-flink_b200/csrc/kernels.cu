@@ -14,6 +14,9 @@
 
 namespace pgn {
 
+// Function attributes are per device: a process may hold handles on several GPUs (one per operator subtask).
+static inline int cur_dev() { int dev = 0; cudaGetDevice(&dev); return dev & 63; }
+
 // ======================================================================================
 // Generic fp32 GEMM  C = act([A0|A1] . B^T + bias)
 // ======================================================================================
@@ -803,8 +806,9 @@ int launch_attn_energy(const Dims& d, int B, int rpa, const int* lens, const int
     else attn_energy_kernel<8, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   } else {
     const size_t smem = (size_t)(16 * d.A + 2 * d.A) * sizeof(float);
-    static bool set = false;
-    if (!set) { cudaFuncSetAttribute(attn_energy_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); set = true; }
+    static bool set[64] = {false};
+    const int dev = cur_dev();
+    if (!set[dev]) { cudaFuncSetAttribute(attn_energy_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); set[dev] = true; }
     attn_energy_kernel<16, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   }
   return 1;
@@ -914,10 +918,11 @@ template <int KMAX>
 static void launch_ctx_t(const Dims& d, int B, int rpa, const int* lens, const int* active,
                          const float* enc_states, const float* e, float* attn, float* state, cudaStream_t st) {
   const size_t smem = (size_t)(KMAX * d.T + 8 * KMAX * CTX_COLS) * sizeof(float);
-  static bool set = false;
-  if (!set && smem > 48 * 1024) {
+  static bool set[64] = {false};
+  const int dev = cur_dev();
+  if (!set[dev] && smem > 48 * 1024) {
     cudaFuncSetAttribute(attn_context_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    set = true;
+    set[dev] = true;
   }
   dim3 grid(d.A / CTX_COLS, B);
   attn_context_kernel<KMAX><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_states, e, attn, state);
@@ -1105,10 +1110,11 @@ final_topk_kernel(Dims d, FinalArgs a) {
 template <int K2MAX>
 static void launch_final_t(const Dims& d, int B, const FinalArgs& a, cudaStream_t st) {
   const size_t smem = (size_t)((d.V + 31) / 32) * 4 + (size_t)256 * K2MAX * 8 + 8 * 12 + 16;
-  static size_t set = 0;
-  if (smem > 48 * 1024 && smem > set) {
+  static size_t set[64] = {0};
+  const int dev = cur_dev();
+  if (smem > 48 * 1024 && smem > set[dev]) {
     cudaFuncSetAttribute(final_topk_kernel<K2MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    set = smem;
+    set[dev] = smem;
   }
   final_topk_kernel<K2MAX><<<B * d.K, 256, smem, st>>>(d, a);
 }
