@@ -185,7 +185,14 @@ PGEN_API int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap
  * out_dev [rows, H] -> logits_dev [rows, V]; use_tc != 0 runs the tcgen05 tf32 kernel (scores carry tf32
  * rounding), 0 the fp32 SIMT kernel. */
 PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* logits_dev, int use_tc);
-/* Test hook: choose kernel variants at run time (e.g. "vocab=simt", "vocab=tc", "profile=1"). */
+/* Run-time switches (tests, profiling, A/B measurements), "key=value":
+ *   vocab=tc|simt        tcgen05 tf32 vocabulary pass + exact re-scoring, or the all-fp32 dense path
+ *   features=tc|simt     W_h.h_i by the 3xTF32 tcgen05 GEMM, or the fp32 SIMT GEMM
+ *   encoder=persistent|steps   one cluster kernel for the whole recurrence, or one launch per time step
+ *   graph=1|0, graph_steps=N   replay N (even) decode steps per CUDA graph, or launch every kernel
+ *   check_every=N        poll the device every N steps after min_dec_steps and stop early when every article is done
+ *   profile=1|0          per-step CUDA events for pgen_stats (plain launches)
+ * No counterpart in the reference. */
 PGEN_API int pgen_set_option(pgen_t* h, const char* key_value);
 
 #ifdef __cplusplus
