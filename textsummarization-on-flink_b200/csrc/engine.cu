@@ -405,7 +405,7 @@ void Engine::encoder() {
     GemmArgs g;
     g.A0 = c_enc_; g.lda0 = H; g.k0 = H; g.A1 = c_enc_ + (size_t)B * H; g.lda1 = H; g.k1 = H;
     g.B = w_.red_wcT; g.ldb = A; g.bias = w_.red_bc; g.act = 1;
-    g.C = state_[0] + A; g.ldc = K * d_.SW; g.M = B; g.N = H;
+    g.C = state_[0] + A; g.ldc = K * d_.SW; g.M = B; g.N = H; g.skinny = 1;    // few rows, long K: split-K tile kernel
     nl += launch_gemm_nt(g, st_);
     g.A0 = hfin; g.A1 = hfin + (size_t)B * H; g.B = w_.red_whT; g.bias = w_.red_bh; g.C = state_[0] + A + H;
     nl += launch_gemm_nt(g, st_);
@@ -540,7 +540,7 @@ void Engine::decoder() {
   {  // attention_decoder.py:138-140: context of the initial state (row b*K only; all K hyps are identical)
     GemmArgs g;
     g.A0 = state_[0] + A; g.lda0 = K * SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
-    g.C = dfeat_; g.ldc = K * A; g.M = B; g.N = A;
+    g.C = dfeat_; g.ldc = K * A; g.M = B; g.N = A; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
     nl += launch_attn_energy(d_, B, 1, lens_, bb_.active, enc_feat_, dfeat_, cov_[0], w_.v, w_.w_c, e_, st_);
     nl += launch_attn_context(d_, B, 1, lens_, bb_.active, enc_states_, e_, attn_[0], state_[0], st_);
