@@ -556,6 +556,40 @@ gather_step_kernel(Dims d, StepBufs b) {
   const float* so = b.state_old + (size_t)rp * d.SW;
   float* xin = b.xin + (size_t)r * (d.E + d.A);
   const float* er = b.emb + (size_t)tok * d.E;
+  const int len = b.lens[art];
+  if (((d.E | d.A | d.H | d.T | d.SW) & 3) == 0) {
+    // Everything is a multiple of 4 floats: the row is a list of 128-bit copies, and a thread requests ALL of its
+    // chunks before it stores the first (one memory round trip instead of one per loop iteration).
+    const int nE = d.E / 4, nA = d.A / 4, nH = d.H / 4, nT = d.use_cov ? (len + 3) / 4 : 0;
+    const int total = nE + nA + 2 * nH + nT;
+    const float4* co = reinterpret_cast<const float4*>(b.cov_old + (size_t)rp * d.T);
+    const float4* ao = reinterpret_cast<const float4*>(b.attn_old + (size_t)rp * d.T);
+    constexpr int MAXC = 6;                                          // 128 threads x 6 chunks x 4 floats per pass
+    for (int base = 0; base < total; base += 128 * MAXC) {
+      float4 v[MAXC], w[MAXC];
+#pragma unroll
+      for (int q = 0; q < MAXC; ++q) {
+        const int i = base + q * 128 + threadIdx.x;
+        w[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < nE) v[q] = __ldg(reinterpret_cast<const float4*>(er) + i);
+        else if (i < nE + nA + 2 * nH) v[q] = *(reinterpret_cast<const float4*>(so) + (i - nE));   // ctx | c | h are contiguous
+        else if (i < total) { v[q] = co[i - nE - nA - 2 * nH]; w[q] = ao[i - nE - nA - 2 * nH]; }
+      }
+#pragma unroll
+      for (int q = 0; q < MAXC; ++q) {
+        const int i = base + q * 128 + threadIdx.x;
+        if (i < nE + nA) reinterpret_cast<float4*>(xin)[i] = v[q];                                  // model.py:214 | previous context
+        else if (i < nE + nA + nH) reinterpret_cast<float4*>(b.cprev + (size_t)r * d.H)[i - nE - nA] = v[q];
+        else if (i < nE + nA + 2 * nH) reinterpret_cast<float4*>(b.hprev + (size_t)r * d.H)[i - nE - nA - nH] = v[q];
+        else if (i < total) {                                                                      // attention_decoder.py:114
+          const int t4 = i - nE - nA - 2 * nH;
+          reinterpret_cast<float4*>(b.cov_new + (size_t)r * d.T)[t4] =
+              make_float4(v[q].x + w[q].x, v[q].y + w[q].y, v[q].z + w[q].z, v[q].w + w[q].w);
+        }
+      }
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < d.E; i += 128) xin[i] = er[i];       // model.py:214
   for (int i = threadIdx.x; i < d.A; i += 128) xin[d.E + i] = so[i]; // previous context
   for (int i = threadIdx.x; i < d.H; i += 128) {
@@ -563,7 +597,6 @@ gather_step_kernel(Dims d, StepBufs b) {
     b.hprev[(size_t)r * d.H + i] = so[d.A + d.H + i];
   }
   if (d.use_cov) {                                                   // attention_decoder.py:114
-    const int len = b.lens[art];
     const float* co = b.cov_old + (size_t)rp * d.T;
     const float* ao = b.attn_old + (size_t)rp * d.T;
     float* cn = b.cov_new + (size_t)r * d.T;
