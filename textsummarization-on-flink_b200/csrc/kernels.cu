@@ -979,7 +979,23 @@ pgen_kernel(int SW, int K, int R, const float* __restrict__ state, const float* 
   if (r >= R || !active[r / K]) return;
   const float* s = state + (size_t)r * SW;
   float acc = 0.f;
-  for (int i = lane; i < SW; i += 32) acc = fmaf(s[i], w[i], acc);
+  if ((SW & 3) == 0 && SW <= 12 * 128) {            // 128-bit loads, all of a lane's chunks requested before the first FMA
+    float4 sv[12], wv[12];
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+      const int i = lane + 32 * q;
+      const bool in = 4 * i < SW;
+      sv[q] = in ? *(reinterpret_cast<const float4*>(s) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      wv[q] = in ? __ldg(reinterpret_cast<const float4*>(w) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+      acc = fmaf(sv[q].x, wv[q].x, acc); acc = fmaf(sv[q].y, wv[q].y, acc);
+      acc = fmaf(sv[q].z, wv[q].z, acc); acc = fmaf(sv[q].w, wv[q].w, acc);
+    }
+  } else {
+    for (int i = lane; i < SW; i += 32) acc = fmaf(s[i], w[i], acc);
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
   if (lane == 0) pgen[r] = sigmoidf_(acc + bias[0]);
@@ -1170,6 +1186,8 @@ beam_step_kernel(Dims d, const int* __restrict__ topk_ids, const float* __restri
   __shared__ double keys[BEAM_MAXC];
   __shared__ double sums[BEAM_MAXC];
   __shared__ int order[BEAM_MAXC];
+  __shared__ int toks[BEAM_MAXC];
+  __shared__ float lps[BEAM_MAXC];
   __shared__ int n_new_s;
   const int art = blockIdx.x;
   if (!b.active[art]) return;
@@ -1180,6 +1198,8 @@ beam_step_kernel(Dims d, const int* __restrict__ topk_ids, const float* __restri
   for (int c = threadIdx.x; c < nc; c += 128) {
     const int i = c / K2;
     const float lp = topk_logp[(size_t)(art * K + i) * K2 + (c - i * K2)];
+    lps[c] = lp;
+    toks[c] = topk_ids[(size_t)(art * K + i) * K2 + (c - i * K2)];      // staged: the serial walk below reads shared memory only
     const double s = b.beam_sum[art * K + i] + (double)lp;              // Hypothesis.log_prob (:72-74), float64
     sums[c] = s;
     keys[c] = s / (double)(step + 2);                                   // avg_log_prob (:77-79), [START] counted
@@ -1197,8 +1217,8 @@ beam_step_kernel(Dims d, const int* __restrict__ topk_ids, const float* __restri
     for (int rk = 0; rk < nc; ++rk) {                                   // :145-154
       const int c = order[rk];
       const int i = c / K2;
-      const int tok = topk_ids[(size_t)(art * K + i) * K2 + (c - i * K2)];
-      const float lp = topk_logp[(size_t)(art * K + i) * K2 + (c - i * K2)];
+      const int tok = toks[c];
+      const float lp = lps[c];
       if (tok == kStop) {
         if (step >= d.min_dec_steps) {
           const int q = art * K + n_res;
