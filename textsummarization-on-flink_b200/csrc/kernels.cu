@@ -1,4 +1,5 @@
-// sm_100a kernels of the pointer-generator decode path (first, all-fp32 SIMT generation).
+// sm_100a kernels of the pointer-generator decode path: fp32 GEMMs, the persistent cluster BiLSTM, attention, p_gen,
+// beam bookkeeping and the all-fp32 vocabulary path (the tcgen05 kernels live in vocab_tc.cu).
 // File:line citations are relative to /root/reference/src/main/python/pointer-generator/.
 //
 // Row convention: decoder row r = b*K + k (article b, beam slot k).  Every per-element reduction

@@ -1,4 +1,6 @@
 // Micro-benchmark of the per-step decoder GEMMs (not part of the product): nvcc -O3 -gencode arch=compute_100a,code=sm_100a
+// NOTE: back-to-back stream launches are quantised to ~2 us ticks on this platform (tick_bench.cu): compare variants
+// inside a CUDA graph or with ncu, not with this loop alone.
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
