@@ -901,6 +901,10 @@ void VocabTC::plan(int R, int* n_mpairs, int* n_ranges) const {
   int nr = (sms / 2) / *n_mpairs;
   if (nr < 1) nr = 1;
   if (nr > n_tiles) nr = n_tiles;
+  // the slowest pair sets the time: with ceil(n_tiles / nr) tiles on the busiest pair, use only as many pairs as
+  // that needs (196 tiles: 66 pairs x 3 instead of 74 pairs x 2..3) and leave the other SMs to concurrent batches
+  const int per = (n_tiles + nr - 1) / nr;
+  nr = (n_tiles + per - 1) / per;
   *n_ranges = nr;
 }
 
