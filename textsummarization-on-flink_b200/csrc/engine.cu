@@ -288,6 +288,13 @@ std::string Engine::set_option(const std::string& kv) {
   const size_t eq = kv.find('=');
   if (eq == std::string::npos) return "option must be key=value";
   const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
+  // captured step graphs bake the kernel variants in: drop them, they are re-captured on the next batch
+  if (!graphs_.empty()) {
+    CK(cudaSetDevice(device_));
+    CK(cudaStreamSynchronize(st_));
+    for (auto& g : graphs_) cudaGraphExecDestroy(g.second);
+    graphs_.clear();
+  }
   if (k == "graph") { use_graph_ = v != "0"; return ""; }
   if (k == "graph_steps") { graph_steps_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "check_every") { check_every_ = std::max(0, atoi(v.c_str())); return ""; }
