@@ -665,26 +665,45 @@ vocab_final_kernel(MergeArgs a) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- 0: everything this row needs, one round of loads
-  const float sgv = (int)threadIdx.x < nsg ? a.smax[(size_t)r * a.sstride + threadIdx.x] : -FLT_MAX;
-  for (int h = threadIdx.x; h < H; h += SEL_THREADS) {
+  // (every load of a thread is requested before its first store: one memory round trip, not one per array)
+  const int tx = threadIdx.x;
+  const float sgv = tx < nsg ? a.smax[(size_t)r * a.sstride + tx] : -FLT_MAX;
+  const float v_out = tx < H ? a.out[(size_t)r * H + tx] : 0.f;
+  const float v_pm = tx < NP ? a.part_m[(size_t)tx * R + r] : 0.f, v_ps = tx < NP ? a.part_s[(size_t)tx * R + r] : 0.f;
+  float v_att = 0.f, v_arl = 0.f;
+  int v_pls = 0, v_uid = 0, v_pss = 0;
+  if (nu > 0) {
+    if (tx < len) { v_att = a.attn[(size_t)r * T + tx]; v_pls = a.pos_list[(size_t)art * T + tx]; }
+    if (tx < nu) { v_arl = a.artl[(size_t)r * T + tx]; v_uid = a.uniq_ids[(size_t)art * T + tx]; }
+    if (tx <= nu) v_pss = a.pos_start[(size_t)art * (T + 1) + tx];
+  }
+  if (tx < H) { outs[tx] = v_out; outt[tx] = tf32_rna(v_out); }
+  if (tx < NP) { pm[tx] = v_pm; ps[tx] = v_ps; }
+  if (nu > 0) {
+    if (tx < len) { att[tx] = v_att; pls[tx] = v_pls; }
+    if (tx < nu) { arl[tx] = v_arl; uids[tx] = v_uid; }
+    if (tx <= nu) pss[tx] = v_pss;
+  }
+  // sizes beyond one element per thread (max_enc_steps > 511, more than 512 parts)
+  for (int h = tx + SEL_THREADS; h < H; h += SEL_THREADS) {
     const float o = a.out[(size_t)r * H + h];
     outs[h] = o;
     outt[h] = tf32_rna(o);
   }
-  for (int pt = threadIdx.x; pt < NP; pt += SEL_THREADS) {
+  for (int pt = tx + SEL_THREADS; pt < NP; pt += SEL_THREADS) {
     pm[pt] = a.part_m[(size_t)pt * R + r];
     ps[pt] = a.part_s[(size_t)pt * R + r];
   }
   if (nu > 0) {
-    for (int t = threadIdx.x; t < len; t += SEL_THREADS) {
+    for (int t = tx + SEL_THREADS; t < len; t += SEL_THREADS) {
       att[t] = a.attn[(size_t)r * T + t];
       pls[t] = a.pos_list[(size_t)art * T + t];
     }
-    for (int u = threadIdx.x; u < nu; u += SEL_THREADS) {
+    for (int u = tx + SEL_THREADS; u < nu; u += SEL_THREADS) {
       arl[u] = a.artl[(size_t)r * T + u];
       uids[u] = a.uniq_ids[(size_t)art * T + u];
     }
-    for (int i = threadIdx.x; i <= nu; i += SEL_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
+    for (int i = tx + SEL_THREADS; i <= nu; i += SEL_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
   }
   if (threadIdx.x < SEL_WARPS * K2) ck[threadIdx.x] = 0ull;      // lists of step 4b: 0 = no entry
   if (threadIdx.x < K2) {                           // defaults, overwritten by the winners in step 4
