@@ -192,6 +192,8 @@ PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, 
  *   graph=1|0, graph_steps=N   replay N (even) decode steps per CUDA graph, or launch every kernel
  *   check_every=N        poll the device every N steps after min_dec_steps and stop early when every article is done
  *   profile=1|0          per-step CUDA events for pgen_stats (plain launches)
+ *   measure=N            replay the attention pair and the tensor-core pass of the last decoded batch N times each
+ *                        from a graph between two events; sums land in ms_attention / ms_vocab, prof_steps = N
  * No counterpart in the reference. */
 PGEN_API int pgen_set_option(pgen_t* h, const char* key_value);
 

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <cstdlib>
 #include <fstream>
 
@@ -284,6 +285,53 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   return "";
 }
 
+// Kernel-only timing for the roofline: the attention pair and the tensor-core pass of the last decoded batch, each
+// replayed `reps` times from a graph (both are idempotent on the buffers the batch left behind) between two CUDA
+// events on this engine's stream -- no launch gaps, caches as warm as in the step loop.  Results land in the profile
+// fields of the stats (sums over `reps` launches, prof_steps = reps).  Re-initialises the beam state: call it after
+// the batch's results have been taken.
+std::string Engine::measure(int reps) {
+  std::string err = sync();
+  if (!err.empty()) return err;
+  const int B = nB_, K = d_.K, R = B * K;
+  if (B <= 0) return "";
+  launch_init_beam(d_, B, lens_, bb_, st_);                    // every article active again
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  auto timed = [&](const std::function<void()>& body, double* total_ms) -> std::string {
+    body();                                                    // lazy function attributes outside the capture
+    cudaGraph_t g = nullptr; cudaGraphExec_t ge = nullptr;
+    if (cudaStreamBeginCapture(st_, cudaStreamCaptureModeRelaxed) != cudaSuccess) return "measure: capture failed";
+    for (int i = 0; i < reps; ++i) body();
+    if (cudaStreamEndCapture(st_, &g) != cudaSuccess || !g || cudaGraphInstantiate(&ge, g, 0) != cudaSuccess) {
+      if (g) cudaGraphDestroy(g);
+      return "measure: graph instantiation failed";
+    }
+    cudaGraphDestroy(g);
+    cudaGraphLaunch(ge, st_);                                  // warm-up replay
+    cudaEventRecord(e0, st_);
+    cudaGraphLaunch(ge, st_);
+    cudaEventRecord(e1, st_);
+    cudaStreamSynchronize(st_);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaGraphExecDestroy(ge);
+    *total_ms = ms;
+    return "";
+  };
+  double ms_att = 0, ms_voc = 0;
+  err = timed([&] {
+    launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[0], w_.v, w_.w_c, e_, st_);
+    launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[0], state_[0], st_);
+  }, &ms_att);
+  if (err.empty() && vocab_tc_)
+    err = timed([&] { vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, nullptr, st_); }, &ms_voc);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (!err.empty()) return err;
+  stats.ms_attention = ms_att; stats.ms_vocab = ms_voc; stats.ms_beam = 0; stats.prof_steps = (uint64_t)reps;
+  return check("measure");
+}
+
 std::string Engine::set_option(const std::string& kv) {
   const size_t eq = kv.find('=');
   if (eq == std::string::npos) return "option must be key=value";
@@ -309,6 +357,7 @@ std::string Engine::set_option(const std::string& kv) {
     }
     return "vocab must be simt or tc";
   }
+  if (k == "measure") return ran_ ? measure(std::max(1, atoi(v.c_str()))) : std::string();
   if (k == "profile") {
     profile_ = atoi(v.c_str()) != 0;
     if (profile_ && pev_.empty()) {

@@ -67,6 +67,7 @@ class Engine {
   int graph_chunk_ = 0, graph_nodes_ = 0;
   bool graph_failed_ = false;
   std::map<int, cudaGraphExec_t> graphs_;     // by articles in the batch
+  std::string measure(int reps);
   int step_launch(int B, int o, int ps);
   cudaGraphExec_t step_graph(int B, int chunk, bool capture);
   int check_every_ = 0;              // > 0: poll the device every N steps (after min_dec_steps) to stop early;
