@@ -67,6 +67,10 @@ typedef struct {
   double ms_attention, ms_vocab;   /* summed over the steps of the last batch run with option profile=1 */
   double ms_select;                /* ... same for what follows the vocabulary GEMM: re-scoring, merge, top-2K */
   double prof_steps;               /* number of steps those two sums cover */
+  /* tf.nn.top_k (model.py:284) is exact; the tensor-core pass picks candidates from tf32 scores.  Every decoder row
+   * is checked against an error bound after its exact re-scoring: rows that needed extra candidate groups, and rows
+   * that had to score the whole vocabulary in fp32 (flat or tied distributions).  Either way the row's top-2K is exact. */
+  uint64_t selection_widened, selection_fallbacks;
 } pgen_stats_t;
 
 /* Replaces main_on_flink/inference_on_flink/default_setup (run_summarization.py:402-426,
@@ -155,7 +159,10 @@ PGEN_API int pgen_submit_example(pgen_t* h, const void* example, size_t len);
  *   lens [n_articles] (int32)   dfeat [n_articles*beam_size, 2H] = W_s s_t + b_attn
  *   cov [n_articles*beam_size, max_enc_steps] (ignored when coverage=0)
  *   attn [n_articles*beam_size, max_enc_steps]   ctx [n_articles*beam_size, 2H]      (outputs)
- * The energies scratch (one float per row and encoder position) is cudaMalloc'ed for the call.
+ * attn[r, t] is written for every t < max_enc_steps: positions at or past lens[b] hold exactly 0, like the
+ * reference's masked distribution (attention_decoder.py:99); articles with lens[b] == 0 are left untouched.
+ * With hidden_dim 256 and beam_size 4 or 8 this is the step loop's one-launch kernel (csrc/attn_fused.cu), otherwise
+ * the energy + context kernel pair.  The scratch (energies, per-segment partials) is cudaMalloc'ed for the call.
  * Synchronous: returns after the kernels have finished. */
 PGEN_API int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float* enc_states,
                    const int32_t* lens, const float* dfeat, const float* cov, float* attn, float* ctx);
@@ -191,6 +198,8 @@ PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, 
  *   encoder=persistent|steps   one cluster kernel for the whole recurrence, or one launch per time step
  *   graph=1|0, graph_steps=N   replay N (even) decode steps per CUDA graph, or launch every kernel
  *   check_every=N        poll the device every N steps after min_dec_steps and stop early when every article is done
+ *   vocab_guard=auto|widen|dense|off   exactness guard of the tensor-core candidate selection: auto (default), or force
+ *                        the widened / dense re-scoring on every row (tests), or switch the check off (A-B timing)
  *   profile=1|0          per-step CUDA events for pgen_stats (plain launches)
  *   measure=N            replay the attention pair and the tensor-core pass of the last decoded batch N times each
  *                        from a graph between two events; sums land in ms_attention / ms_vocab, prof_steps = N

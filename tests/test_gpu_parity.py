@@ -38,9 +38,12 @@ def _has_near_tie(trace, upto):
     return False
 
 
-def check_against_oracle(dec, W, hps, arts, max_near_tie_frac=0.1):
+def check_against_oracle(dec, W, hps, arts, max_near_tie_frac=0.1, decode=None):
+    """Every article against the oracle.  Identical tokens and log-probs within RTOL -- or, at a documented near-tie,
+    identical tokens and log-probs up to the step where the oracle's own candidates are within NEAR_TIE of each
+    other; such articles are counted and bounded.  `decode`: alternative way of getting (tok, len, logp, avg)."""
     ids, ext, lens, noov = native.pack_articles(arts, dec.max_enc_steps)
-    tok, ln, lp, avg = dec.decode_ids(ids, ext, lens, noov)
+    tok, ln, lp, avg = decode(ids, ext, lens, noov) if decode else dec.decode_ids(ids, ext, lens, noov)
     ref = _oracle_decode(W, hps, arts)
     near = 0
     for b, (rt, rl, ravg, tr) in enumerate(ref):
@@ -49,6 +52,10 @@ def check_against_oracle(dec, W, hps, arts, max_near_tie_frac=0.1):
             first = next((i for i, (x, y) in enumerate(zip(got, rt)) if x != y), min(len(got), len(rt)))
             assert _has_near_tie(tr, min(first, len(tr) - 1)), \
                 "article %d: tokens differ at %d with no near-tie\n got %s\n ref %s" % (b, first, got, rt)
+            # the common prefix still has to carry the oracle's log-probs (the swap may have happened at an earlier
+            # step than the one where the winning hypothesis shows it: allow the step before the difference)
+            upto = max(0, first - 1)
+            np.testing.assert_allclose(lp[b, :upto], rl[:upto], rtol=RTOL, atol=ATOL, err_msg="article %d prefix" % b)
             near += 1
             continue
         assert ln[b] == len(rt)
@@ -211,24 +218,31 @@ def test_config4_beam8_200_oovs(model_dir):
 
 def test_w0_reference_scale_weights_logprobs(tmp_path_factory):
     """W0 = the reference's own initialisers (trunc-normal 1e-4, LSTM U(-0.02, 0.02)): the 50k-way distribution is
-    almost flat, so token identity is rounding-dominated (SURVEY.md hard parts) -- compare what is well defined:
-    the log-prob of the FIRST emitted token (a copy of an article word) and the avg log-prob, within 1e-3."""
+    almost flat (logits within ~1e-3 of each other), so nearly every beam step holds candidates closer than NEAR_TIE
+    and WHICH of them wins is rounding (SURVEY.md hard parts).  Same accounting as everywhere else: tokens identical, or
+    identical up to a step with a near-tie in the oracle's own candidates, log-probs within 1e-3 on the common
+    prefix; the first emitted token and the average log-prob are well defined and must always agree."""
     root = str(tmp_path_factory.mktemp("pgen_w0"))
     paths = synth.make_model_dir(root, "W0")
     from textsummarization_on_flink_b200 import weights_io
     W = weights_io.load_weights(paths["weights"])
-    flags = synth.hyperparams_string(paths, max_dec_steps=40, min_dec_steps=10, extra="--articles_per_batch=4")
+    flags = synth.hyperparams_string(paths, max_dec_steps=40, min_dec_steps=10, extra="--articles_per_batch=8")
     hps = O.parse_hyperparams(flags)
-    arts = synth.make_article_ids(3, seed=91)
+    arts = synth.make_article_ids(6, seed=91)
     with native.Decoder(flags) as dec:
-        tok, ln, lp, avg = dec.decode_ids(*native.pack_articles(arts, dec.max_enc_steps))
+        got = {}
+
+        def decode(*packed):
+            got["out"] = dec.decode_ids(*packed)
+            return got["out"]
+
+        check_against_oracle(dec, W, hps, arts, max_near_tie_frac=1.0, decode=decode)
+        tok, ln, lp, avg = got["out"]
     for b, (a, e, k) in enumerate(arts):
         rt, rl, ravg = O.decode_ids(W, hps, a, e, k, mode="dedup")
         assert ln[b] == len(rt)
         assert abs(lp[b, 0] - rl[0]) <= RTOL * abs(rl[0]) + ATOL
         assert abs(avg[b] - ravg) <= RTOL * abs(ravg) + 1e-4
-        same = sum(int(x == y) for x, y in zip(tok[b, :ln[b]].tolist(), rt))
-        assert same >= 0.5 * len(rt)             # not asserted to be identical: flat distributions are near-ties
 
 
 def test_edge_rows_through_submit(small_cfg, small_model_dir):

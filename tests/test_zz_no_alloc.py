@@ -4,8 +4,9 @@ Some hosts of this library may not allocate device memory at all: the process' G
 another allocator or capped by a fixed budget, or the calling loop cannot take the device-wide stall of
 cudaMalloc/cudaFree.  For them the library keeps the attention scratch in a fixed 1 MiB device array.
 This test drives both entry points through the C ABI on the same device buffers and requires the same
-answers, twice in a row with different shapes so that whatever the first call leaves in the shared
-array is seen (and must be harmless) by the second; it also checks that an over-sized request is refused.
+answers -- and the oracle's (attention_decoder.py:79-129) -- twice in a row with different shapes so that
+whatever the first call leaves in the shared array is seen (and must be harmless) by the second; it also
+checks that an over-sized request is refused.
 
 Collected last on purpose (file name): a run that stops at the first failure has by then run every
 other test.  It needs nothing from the other tests and also passes alone in a fresh process."""
@@ -13,6 +14,7 @@ import numpy as np
 import pytest
 
 from conftest import small_flags
+from test_gpu_kernels import oracle_attention_from_features
 from textsummarization_on_flink_b200 import native
 
 pytestmark = pytest.mark.gpu
@@ -53,6 +55,13 @@ def test_static_scratch_attention_matches_allocating_entry_point(small_cfg, smal
                                            err_msg="call %d article %d" % (call, b))
                 np.testing.assert_allclose(got_attn[rows, :L].sum(axis=1), 1.0, atol=1e-5)
             np.testing.assert_allclose(got_ctx, ref_ctx, atol=ATOL, rtol=RTOL, err_msg="call %d" % call)
+            # and against the oracle, on every entry: positions past an article's end hold exactly 0
+            # (the poison written into the output buffers must be gone)
+            ora_attn, ora_ctx = oracle_attention_from_features(small_cfg["W"], host, K, True)
+            np.testing.assert_allclose(got_attn, ora_attn, atol=ATOL, rtol=RTOL, err_msg="call %d vs oracle" % call)
+            np.testing.assert_allclose(got_ctx, ora_ctx, atol=ATOL, rtol=RTOL, err_msg="call %d vs oracle" % call)
+            for b in range(n):
+                assert not got_attn[b * K:(b + 1) * K, int(host["lens"][b]):].any()
 
 
 def test_static_scratch_rejects_requests_beyond_its_array(small_cfg, small_model_dir):

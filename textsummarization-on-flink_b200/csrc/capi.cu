@@ -219,6 +219,7 @@ int pgen_stats(pgen_t* h, pgen_stats_t* out) {
     const EngineStats& x = e->stats;
     s.batches += x.batches; s.decode_steps += x.decode_steps; s.article_steps += x.article_steps;
     s.early_stops += x.early_stops; s.kernel_launches += x.kernel_launches;
+    s.selection_widened += x.selection_widened; s.selection_fallbacks += x.selection_fallbacks;
   }
   const EngineStats& last = h->eng().stats;          // timings: the slot the stage API addresses
   out->rows_in = h->rows_in; out->rows_out = h->rows_out; out->batches = s.batches;
@@ -228,6 +229,7 @@ int pgen_stats(pgen_t* h, pgen_stats_t* out) {
   out->ms_decoder = last.ms_decoder; out->ms_d2h = last.ms_d2h;
   out->ms_attention = last.ms_attention; out->ms_vocab = last.ms_vocab; out->ms_select = last.ms_beam;
   out->prof_steps = (double)last.prof_steps;
+  out->selection_widened = s.selection_widened; out->selection_fallbacks = s.selection_fallbacks;
   return PGEN_OK;
 }
 

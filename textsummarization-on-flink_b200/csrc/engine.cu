@@ -2,6 +2,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <functional>
 #include <cstdlib>
@@ -38,7 +39,7 @@ Engine::~Engine() {
   for (void* p : allocs_) cudaFree(p);
   for (void* p : {(void*)h_ids_, (void*)h_ext_, (void*)h_lens_, (void*)h_noov_, (void*)h_uniq_, (void*)h_ucnt_,
                   (void*)h_pstart_, (void*)h_plist_, (void*)h_nactive_, (void*)h_out_tok_, (void*)h_out_len_,
-                  (void*)h_out_lp_, (void*)h_out_avg_, (void*)h_steps_, (void*)h_rescnt_})
+                  (void*)h_out_lp_, (void*)h_out_avg_, (void*)h_steps_, (void*)h_rescnt_, (void*)h_selstats_})
     if (p) cudaFreeHost(p);
   for (auto& e : ev_) if (e) cudaEventDestroy(e);
   for (auto& e : pev_) if (e) cudaEventDestroy(e);
@@ -161,6 +162,14 @@ std::string Engine::load_weights(const std::string& path) {
   NEED(D + "AttnOutputProjection/Linear/Matrix", (size_t)(H + A) * H); UPT(&w_.out_MT, H + A, H);
   NEED(D + "AttnOutputProjection/Linear/Bias", (size_t)H); UP(&w_.out_b, (size_t)H);
   NEED(P + "output_projection/w", (size_t)H * V); UPT(&w_.proj_wT, H, V);
+  {                                                  // largest column norm: error bound of the tf32 logits (vocab_tc.cu)
+    std::vector<double> sq((size_t)V, 0.0);
+    for (int h = 0; h < H; ++h)
+      for (int v = 0; v < V; ++v) { const double x = p[(size_t)h * V + v]; sq[v] += x * x; }
+    double mx = 0.0;
+    for (int v = 0; v < V; ++v) mx = std::max(mx, sq[v]);
+    w_.proj_wnorm_max = (float)(std::sqrt(mx) * (1.0 + 1e-6));
+  }
   NEED(P + "output_projection/v", (size_t)V); UP(&w_.proj_v, (size_t)V);
 #undef NEED
 #undef UP
@@ -214,7 +223,8 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   HOSTALLOC(h_ids_, B * T); HOSTALLOC(h_ext_, B * T); HOSTALLOC(h_lens_, B); HOSTALLOC(h_noov_, B);
   HOSTALLOC(h_uniq_, B * T); HOSTALLOC(h_ucnt_, B); HOSTALLOC(h_pstart_, B * (T + 1)); HOSTALLOC(h_plist_, B * T);
   HOSTALLOC(h_nactive_, 1); HOSTALLOC(h_out_tok_, B * S); HOSTALLOC(h_out_len_, B); HOSTALLOC(h_out_lp_, B * S);
-  HOSTALLOC(h_out_avg_, B); HOSTALLOC(h_steps_, B); HOSTALLOC(h_rescnt_, B);
+  HOSTALLOC(h_out_avg_, B); HOSTALLOC(h_steps_, B); HOSTALLOC(h_rescnt_, B); HOSTALLOC(h_selstats_, 2);
+  h_selstats_[0] = h_selstats_[1] = 0;
 #undef HOSTALLOC
 #define DALLOC(p, type, n) do { p = dalloc<type>(n); if (!p) return std::string("cudaMalloc failed for " #p); } while (0)
   DALLOC(ids_, int, B * T); DALLOC(ext_, int, B * T); DALLOC(lens_, int, B); DALLOC(noov_, int, B);
@@ -246,6 +256,13 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     sstride_ = (int)((((V + 255) / 256) * 2 + 31) & ~(size_t)31);
     DALLOC(smax_, float, (size_t)sstride_ * Rpad);
     DALLOC(artl_, float, R * T);
+    DALLOC(sel_stats_, int, 2);
+    if (attn_fused_supported(d_)) {
+      DALLOC(att_pctx_, float, attn_fused_pctx_floats(d_, (int)B)); DALLOC(att_segstat_, float, attn_fused_segstat_floats(d_, (int)B));
+      DALLOC(att_cnt_, int, B);
+      attn_fused_ = attn_fused_prepare(d_) == cudaSuccess;
+      if (!attn_fused_) cudaGetLastError();
+    }
     if (!share) launch_round_tf32(w_.proj_wT, proj_wT_tf32_, V * H, st_);
     if (H == 256 && hp.encoder_table) {
       // The encoder's input projection depends on the token only: x.Kx + b of every vocabulary word, once per model
@@ -320,10 +337,7 @@ std::string Engine::measure(int reps) {
     return "";
   };
   double ms_att = 0, ms_voc = 0;
-  err = timed([&] {
-    launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[0], w_.v, w_.w_c, e_, st_);
-    launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[0], state_[0], st_);
-  }, &ms_att);
+  err = timed([&] { attention(B, cov_[0], attn_[0], state_[0]); }, &ms_att);
   if (err.empty() && vocab_tc_)
     err = timed([&] { vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, nullptr, st_); }, &ms_voc);
   cudaEventDestroy(e0); cudaEventDestroy(e1);
@@ -348,6 +362,15 @@ std::string Engine::set_option(const std::string& kv) {
   if (k == "check_every") { check_every_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "features") { feat_tc_ = (v != "simt") && g3_.ready; return ""; }
   if (k == "encoder") { enc_persistent_ = (v != "steps"); return ""; }
+  if (k == "attention") {
+    if (v == "split") { attn_fused_ = false; return ""; }
+    if (v == "fused") {
+      if (!att_cnt_) return "one-launch attention needs hidden_dim 256 and beam_size 4 or 8";
+      attn_fused_ = true;
+      return "";
+    }
+    return "attention must be fused or split";
+  }
   if (k == "vocab") {
     if (v == "simt") { vocab_tc_ = false; return ""; }
     if (v == "tc") {
@@ -356,6 +379,11 @@ std::string Engine::set_option(const std::string& kv) {
       return "";
     }
     return "vocab must be simt or tc";
+  }
+  if (k == "vocab_guard") {
+    if (v == "auto") vocab_guard_ = 0; else if (v == "widen") vocab_guard_ = 1; else if (v == "dense") vocab_guard_ = 2;
+    else if (v == "off") vocab_guard_ = 3; else return "vocab_guard must be auto, widen, dense or off";
+    return "";
   }
   if (k == "measure") return ran_ ? measure(std::max(1, atoi(v.c_str()))) : std::string();
   if (k == "profile") {
@@ -479,6 +507,15 @@ void Engine::encoder() {
   }
 }
 
+// The attention pass of a decode step over all K rows of every live article (attention_decoder.py:156-158).
+int Engine::attention(int B, const float* cov, float* attn, float* state) {
+  if (attn_fused_)
+    return launch_attn_fused(d_, B, lens_, bb_.active, enc_feat_, enc_states_, dfeat_, cov, w_.v, w_.w_c, e_, att_pctx_,
+                             att_segstat_, att_cnt_, attn, state, d_.SW, n_sms_, st_);
+  int nl = launch_attn_energy(d_, B, d_.K, lens_, bb_.active, enc_feat_, dfeat_, cov, w_.v, w_.w_c, e_, st_);
+  return nl + launch_attn_context(d_, B, d_.K, lens_, bb_.active, enc_states_, e_, attn, state, st_);
+}
+
 // One decode step (beam_search.py:109-156) for buffer parity o (old) -> n (new).  Nothing in it depends on the step
 // number on the host side (beam_step reads it from steps_done), so a captured step can be replayed.
 int Engine::step_launch(int B, int o, int ps) {
@@ -505,8 +542,7 @@ int Engine::step_launch(int B, int o, int ps) {
     g.C = dfeat_; g.ldc = A; g.M = R; g.N = A; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
     if (profile_) cudaEventRecord(pev_[5 * ps + 0], st_);
-    nl += launch_attn_energy(d_, B, K, lens_, bb_.active, enc_feat_, dfeat_, cov_[n], w_.v, w_.w_c, e_, st_);
-    nl += launch_attn_context(d_, B, K, lens_, bb_.active, enc_states_, e_, attn_[n], state_[n], st_);
+    nl += attention(B, cov_[n], attn_[n], state_[n]);
     if (profile_) cudaEventRecord(pev_[5 * ps + 1], st_);
     // p_gen and the exact logits of the article's words are side branches (stream st2_, a parallel branch of the
     // captured graph): they run beside the out projection and the tensor-core pass and join before the final kernel
@@ -529,6 +565,7 @@ int Engine::step_launch(int B, int o, int ps) {
       ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active; ma.lens = lens_;
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
       ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
+      ma.wnorm_max = w_.proj_wnorm_max; ma.guard = vocab_guard_; ma.sel_stats = sel_stats_;
       if (profile_) cudaEventRecord(pev_[5 * ps + 2], st_);
       if (fork) { cudaEventRecord(fev_[1], st_); cudaStreamWaitEvent(st2_, fev_[1], 0); }      // out_ is complete
       if (fork) { nl += vtc_.launch_rescore(ma, B, st2_); cudaEventRecord(fev_[2], st2_); }   // exact fp32 logits of the article's words
@@ -592,6 +629,7 @@ void Engine::decoder() {
   const int B = nB_, T = d_.T, H = d_.H, A = d_.A, K = d_.K, R = B * K, SW = d_.SW;
   uint64_t& nl = stats.kernel_launches;
   nl += launch_init_beam(d_, B, lens_, bb_, st_);
+  if (att_cnt_) cudaMemsetAsync(att_cnt_, 0, (size_t)B * sizeof(int), st_);   // segment counters of the one-launch attention
   if (d_.use_cov) cudaMemsetAsync(cov_[0], 0, (size_t)R * T * sizeof(float), st_);   // beam_search.py:105
   {  // attention_decoder.py:138-140: context of the initial state (row b*K only; all K hyps are identical)
     GemmArgs g;
@@ -655,6 +693,7 @@ std::string Engine::run() {
     CK(cudaMemcpyAsync(h_out_avg_, out_avg_, n * 8, cudaMemcpyDeviceToHost, st_));
     CK(cudaMemcpyAsync(h_steps_, bb_.steps_done, n * 4, cudaMemcpyDeviceToHost, st_));
     CK(cudaMemcpyAsync(h_rescnt_, bb_.res_count, n * 4, cudaMemcpyDeviceToHost, st_));
+    CK(cudaMemcpyAsync(h_selstats_, sel_stats_, 2 * 4, cudaMemcpyDeviceToHost, st_));
   }
   CK(cudaEventRecord(ev_[6], st_));
   std::string err = check("decode launch");
@@ -703,6 +742,8 @@ std::string Engine::download(int32_t* out_tokens, int32_t* out_lens, float* out_
       stats.article_steps += h_steps_[b];
       if (h_rescnt_[b] >= d_.K) ++stats.early_stops;
     }
+    stats.selection_widened = (uint64_t)h_selstats_[0];
+    stats.selection_fallbacks = (uint64_t)h_selstats_[1];
     counted_ = true;
   }
   if (out_tokens) memcpy(out_tokens, h_out_tok_, n * S * 4);
@@ -735,16 +776,25 @@ std::string Engine::attention_op(int n, const float* enc_feat, const float* enc_
   if (n <= 0) return "";
   CK(cudaSetDevice(device_));
   const size_t rows = (size_t)n * d_.K;
+  const bool fused = attn_fused_ && att_cnt_;
+  // scratch of the call: energies, "article is live" flags, and for the one-launch kernel its per-segment partials
+  const size_t n_pctx = fused ? attn_fused_pctx_floats(d_, n) : 0, n_seg = fused ? attn_fused_segstat_floats(d_, n) : 0;
   float* e = nullptr;
   int* act = nullptr;
-  CK(cudaMalloc((void**)&e, rows * d_.T * sizeof(float)));
-  if (cudaMalloc((void**)&act, (size_t)n * sizeof(int)) != cudaSuccess) { cudaFree(e); return "cudaMalloc failed"; }
-  std::vector<int> ones((size_t)n, 1);
-  cudaMemcpyAsync(act, ones.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, st_);
+  CK(cudaMalloc((void**)&e, (rows * d_.T + n_pctx + n_seg) * sizeof(float)));
+  if (cudaMalloc((void**)&act, (size_t)2 * n * sizeof(int)) != cudaSuccess) { cudaFree(e); return "cudaMalloc failed"; }
+  std::vector<int> ones((size_t)2 * n, 1);
+  std::fill(ones.begin() + n, ones.end(), 0);                     // [n] live flags, [n] segment counters
+  cudaMemcpyAsync(act, ones.data(), (size_t)2 * n * sizeof(int), cudaMemcpyHostToDevice, st_);
   Dims d = d_;
   d.SW = d.A;                      // ctx rows are dense [rows, A] here
-  stats.kernel_launches += launch_attn_energy(d, n, d.K, lens, act, enc_feat, dfeat, cov, w_.v, w_.w_c, e, st_);
-  stats.kernel_launches += launch_attn_context(d, n, d.K, lens, act, enc_states, e, attn, ctx, st_);
+  if (fused) {
+    stats.kernel_launches += launch_attn_fused(d, n, lens, act, enc_feat, enc_states, dfeat, cov, w_.v, w_.w_c, e,
+                                               e + rows * d_.T, e + rows * d_.T + n_pctx, act + n, attn, ctx, d.A, n_sms_, st_);
+  } else {
+    stats.kernel_launches += launch_attn_energy(d, n, d.K, lens, act, enc_feat, dfeat, cov, w_.v, w_.w_c, e, st_);
+    stats.kernel_launches += launch_attn_context(d, n, d.K, lens, act, enc_states, e, attn, ctx, st_);
+  }
   cudaError_t err = cudaStreamSynchronize(st_);
   cudaFree(e);
   cudaFree(act);

@@ -18,6 +18,7 @@ struct DeviceWeights {
   float *red_wcT, *red_whT, *red_bc, *red_bh;
   float *WhT, *v, *w_c, *att_MT, *att_b, *x_MT, *x_b, *dec_kT, *dec_b, *pg_w, *pg_b, *out_MT, *out_b;
   float *proj_wT, *proj_v;
+  float proj_wnorm_max = 0.f;      // max over the vocabulary of the L2 norm of a word's projection column
 };
 
 struct EngineStats {
@@ -25,6 +26,7 @@ struct EngineStats {
   double ms_h2d = 0, ms_encoder = 0, ms_decoder = 0, ms_d2h = 0;
   double ms_attention = 0, ms_vocab = 0, ms_beam = 0;   // summed over the steps of the last profiled batch
   uint64_t prof_steps = 0;
+  uint64_t selection_widened = 0, selection_fallbacks = 0;   // rows whose tf32 candidate set failed the exactness guard
 };
 
 class Engine {
@@ -73,7 +75,14 @@ class Engine {
   int check_every_ = 0;              // > 0: poll the device every N steps (after min_dec_steps) to stop early;
                                      // 0: never block the host -- run() is fully asynchronous
   bool profile_ = false;
+  int vocab_guard_ = 0;              // MergeArgs::guard
+  int* sel_stats_ = nullptr;         // device [2], cumulative
+  int32_t* h_selstats_ = nullptr;    // pinned copy, refreshed with every batch's results
   bool enc_persistent_ = true;
+  bool attn_fused_ = false;          // one-launch attention (attn_fused.cu) instead of the energy + context pair
+  float *att_pctx_ = nullptr, *att_segstat_ = nullptr;
+  int* att_cnt_ = nullptr;
+  int attention(int B, const float* cov, float* attn, float* state);   // the step's attention pass on dfeat_
   bool vocab_tc_ = false;          // tensor-core vocabulary path in use (falls back to the SIMT kernels when
                                    // the dims are outside what vocab_tc.cu covers)
   VocabTC vtc_;

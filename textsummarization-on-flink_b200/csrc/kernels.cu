@@ -894,6 +894,8 @@ attn_context_kernel(Dims d, int rpa, const int* __restrict__ lens, const int* __
       as[k * T + t] = x;
       if (blockIdx.x == 0) attn[(size_t)(art * d.K + k) * T + t] = x;
     }
+    if (blockIdx.x == 0)                                              // the masked distribution is exactly 0 past the article (:99)
+      for (int t = len + lane; t < T; t += 32) attn[(size_t)(art * d.K + k) * T + t] = 0.f;
   }
   __syncthreads();
   // context = sum_t attn[t] * h_t   (:126-127)

@@ -585,14 +585,15 @@ vocab_rescore_kernel(MergeArgs a) {
 // Candidate groups of one decoder row + exact re-scoring of their words.  One block per row.
 // ---------------------------------------------------------------------------------------------
 constexpr int SEL_THREADS = 512, SEL_WARPS = SEL_THREADS / 32;
+constexpr int QCAP = 64;            // groups a row may add to its candidate set when the guard trips (more: dense scan)
+static_assert(QCAP * GW == SEL_THREADS, "the dense scan handles one word per thread and chunk");
 
-
-
-// Order-preserving map float -> uint32 (larger float <=> larger key).
+// Order-preserving map float -> uint32 (larger float <=> larger key) and its inverse.
 __device__ __forceinline__ uint32_t f2ord(float x) {
   const uint32_t b = __float_as_uint(x);
   return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
 }
+__device__ __forceinline__ float ord2f(uint32_t o) { return __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu)); }
 
 // One warp extracts the `rounds` largest of the 32 keys its lanes hold (0 = nothing) into list[0..rounds), sorted
 // descending, with ids[] alongside: one redux.max + one ballot per round, no shuffles.
@@ -608,12 +609,14 @@ __device__ __forceinline__ void warp_top_rounds(uint32_t key, int id, int rounds
   }
 }
 // Warp 0 merges n_lists (<= 32) descending lists of `len` keys into the `rounds` largest overall: lane l walks list l.
+// *last_key receives the key of the last round (0: fewer than `rounds` keys exist).
 __device__ __forceinline__ void warp_merge_heads(const uint32_t* lists, const int* ids, int n_lists, int len, int rounds,
-                                                 int* out, int lane) {
+                                                 int* out, uint32_t* last_key, int lane) {
   int head = 0;
   uint32_t cur = lane < n_lists ? lists[lane * len] : 0u;
+  uint32_t m = 0u;
   for (int round = 0; round < rounds; ++round) {
-    const uint32_t m = __reduce_max_sync(0xffffffffu, cur);
+    m = __reduce_max_sync(0xffffffffu, cur);
     const uint32_t ball = __ballot_sync(0xffffffffu, cur == m);
     if (lane == __ffs(ball) - 1) {
       out[round] = m ? ids[lane * len + head] : -1;
@@ -621,47 +624,116 @@ __device__ __forceinline__ void warp_merge_heads(const uint32_t* lists, const in
       cur = (m && head < len) ? lists[lane * len + head] : 0u;
     }
   }
+  if (lane == 0) *last_key = m;
+}
+
+// Exact fp32 logit (and the tf32-emulated one the tensor core summed) of the 8 words of each of the n_groups groups
+// listed in glist -> cx / ca / cid [base, base + 8 n_groups).  Warp per word, 4 words in flight per warp.
+__device__ __forceinline__ void rescore_groups(const MergeArgs& a, const int* glist, int n_groups, int base,
+                                               const float* outs, const float* outt, float* cx, float* ca, int* cid,
+                                               int warp, int lane) {
+  const int nw = n_groups * GW, H = a.H, V = a.V;
+  for (int it0 = warp * 4; it0 < nw; it0 += SEL_WARPS * 4) {
+    float4 w4[4][2];
+    int ids[4];
+    float bb[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int it = it0 + u;
+      const int grp = it < nw ? glist[it / GW] : -1;
+      const int id = grp >= 0 ? grp * GW + (it % GW) : -1;
+      ids[u] = (id >= 0 && id < V) ? id : -1;
+      bb[u] = ids[u] >= 0 ? __ldg(a.bias + ids[u]) : 0.f;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int h = lane * 4 + hh * 128;
+        w4[u][hh] = (ids[u] >= 0 && h < H) ? __ldg(reinterpret_cast<const float4*>(a.wT + (size_t)ids[u] * H + h))
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    float acc[8];                                   // (word u, exact) at 2u, (word u, tf32-emulated) at 2u + 1
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float ex = 0.f, em = 0.f;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int h = lane * 4 + hh * 128;
+        if (h < H) {
+          const float4 o4 = *reinterpret_cast<const float4*>(outs + h);
+          const float4 t4 = *reinterpret_cast<const float4*>(outt + h);
+          const float4 w = w4[u][hh];
+          ex = fmaf(w.x, o4.x, ex); ex = fmaf(w.y, o4.y, ex); ex = fmaf(w.z, o4.z, ex); ex = fmaf(w.w, o4.w, ex);
+          em = fmaf(tf32_rna(w.x), t4.x, em); em = fmaf(tf32_rna(w.y), t4.y, em);
+          em = fmaf(tf32_rna(w.z), t4.z, em); em = fmaf(tf32_rna(w.w), t4.w, em);
+        }
+      }
+      acc[2 * u] = ex; acc[2 * u + 1] = em;
+    }
+    const float tot = warp_multi_reduce<8>(acc, lane);          // lane l holds value l / 4
+    const int vi = lane >> 2, u = vi >> 1, it = it0 + u;
+    int id = ids[0]; float b = bb[0];
+    if (u == 1) { id = ids[1]; b = bb[1]; } else if (u == 2) { id = ids[2]; b = bb[2]; } else if (u == 3) { id = ids[3]; b = bb[3]; }
+    if ((lane & 3) == 0 && it < nw) {
+      if (vi & 1) ca[base + it] = id >= 0 ? tot + b : -FLT_MAX;
+      else { cx[base + it] = id >= 0 ? tot + b : -FLT_MAX; cid[base + it] = id; }
+    }
+  }
 }
 
 // One block per beam row, after the tensor-core pass:
 //   1. the 2K+8 best groups of 8 words by group maximum (tf32 logits), hierarchically and without shuffles: first
-//      the 2K+8 best 128-word supergroups (one key per thread, redux.max + ballot rounds per warp, warp 0 merges
-//      the warps' sorted lists), then the same over the 16 groups of each selected supergroup -- the best groups
-//      necessarily lie inside the best supergroups;
+//      the best 128-word supergroups (one key per thread, redux.max + ballot rounds per warp, warp 0 merges the
+//      warps' sorted lists), then the same over the 16 groups of each selected supergroup -- the best groups
+//      necessarily lie inside the best supergroups.  One more round than needed yields the maximum of the best
+//      group that was NOT selected;
 //   2. exact fp32 logit (and the tf32-emulated one, to take the tensor-core value back out of the sum of
 //      exponentials) of the 8 words of every selected group;
 //   3. softmax denominator from the per-part (max, sum exp2) of the tensor-core pass, corrected by step 2;
 //   4. final distribution on candidates + the article's words (model.py:146-183), top-2K with tf.nn.top_k's tie
-//      rule (larger value, then lower id) -> topk_ids / topk_logp (model.py:284-285).
+//      rule (larger value, then lower id) -> topk_ids / topk_logp (model.py:284-285);
+//   5. guard: tf.nn.top_k is exact over V + n_oov (model.py:284), the candidate set came from tf32 maxima.  A word
+//      outside the selected groups has a tf32 logit <= u (the best unselected maximum) and therefore an exact logit
+//      <= u + eps with eps = 1.1e-3 |out| max_w |w_w| (both operands rounded to 11 significant bits: 2^-10 sum |o w|
+//      <= 2^-10 |o| |w|, plus the accumulator's rounding).  If p_gen softmax(u + eps) is below the 2K-th value
+//      found, no such word can be in the top 2K and the row is exact as it stands.  Otherwise every unselected
+//      group whose maximum could reach that value is re-scored too (at most QCAP of them: "widened") and steps 3-4
+//      are repeated; if there are more than QCAP (a flat or tied row), every word of the vocabulary is scored in
+//      fp32 by this block ("dense").  Both cases are counted in sel_stats.
+enum { GUARD_AUTO = 0, GUARD_WIDEN = 1, GUARD_DENSE = 2, GUARD_OFF = 3 };
+
 __global__ void __launch_bounds__(SEL_THREADS)
 vocab_final_kernel(MergeArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int r = blockIdx.x, art = r / a.K;
   if (!a.active[art]) return;
   const int V = a.V, H = a.H, G = a.G, T = a.T, NP = a.n_parts, R = a.R, NC = a.NC, K2 = a.K2;
+  const int G1 = G + 1, NCT = NC + QCAP * GW;
   const int nsg = (V + 127) >> 7;                   // supergroups of 128 words (16 groups)
+  const int ngroups = (V + GW - 1) / GW;
   const int nu = a.pointer_gen ? a.uniq_cnt[art] : 0;
   const int len = a.lens[art];
-  const int nf = NC + nu;
-  unsigned long long* fin = reinterpret_cast<unsigned long long*>(sm);        // [NC + T] (value, ~id) keys
-  unsigned long long* ck = fin + (NC + T);          // [16 warps][K2] per-warp winners of the final top-2K
+  unsigned long long* fin = reinterpret_cast<unsigned long long*>(sm);        // [NCT + T] (value, ~id) keys
+  unsigned long long* ck = fin + ((NCT + T + 1) & ~1);   // [16 warps][K2] per-warp winners of the final top-2K
   float* outs = reinterpret_cast<float*>(ck + SEL_WARPS * K2);                // [H] decoder output, exact
   float* outt = outs + H;                           // [H] the tf32-rounded copy the tensor core multiplied
-  uint32_t* wk = reinterpret_cast<uint32_t*>(outt + H);                       // [16 warps][G] selection lists: keys
-  int* wi = reinterpret_cast<int*>(wk + SEL_WARPS * G);                       // [16 warps][G]                  ids
-  float* pm = reinterpret_cast<float*>(wi + SEL_WARPS * G);                   // [NP] part maxima
+  uint32_t* wk = reinterpret_cast<uint32_t*>(outt + H);                       // [16 warps][G + 1] selection lists: keys
+  int* wi = reinterpret_cast<int*>(wk + SEL_WARPS * G1);                      // [16 warps][G + 1]                  ids
+  float* pm = reinterpret_cast<float*>(wi + SEL_WARPS * G1);                  // [NP] part maxima
   float* ps = pm + NP;                              // [NP] part sums
   float* att = ps + NP;                             // [T] attention of this row
   float* arl = att + T;                             // [T] exact logits of the article's words
-  float* cx = arl + T;                              // [NC] exact logits of the candidates
-  float* ca = cx + NC;                              // [NC] tf32-emulated logits of the candidates
-  int* cid = reinterpret_cast<int*>(ca + NC);       // [NC] candidate word ids
-  int* pss = cid + NC;                              // [T + 1] pos_start
+  float* cx = arl + T;                              // [NCT] exact logits of the candidates
+  float* ca = cx + NCT;                             // [NCT] tf32-emulated logits of the candidates
+  int* cid = reinterpret_cast<int*>(ca + NCT);      // [NCT] candidate word ids
+  int* pss = cid + NCT;                             // [T + 1] pos_start
   int* pls = pss + (T + 1);                         // [T] pos_list
   int* uids = pls + T;                              // [T] uniq_ids
-  int* sels = uids + T;                             // [G] selected supergroups
-  int* sel = sels + G;                              // [G] selected groups
-  float* MS = reinterpret_cast<float*>(sel + G);    // [2] M (natural log domain), S
+  int* sels = uids + T;                             // [G + 1] selected supergroups (+ the best one left out)
+  int* sel = sels + G1;                             // [G + 1] selected groups (+ the best one left out)
+  int* near = sel + G1;                             // [QCAP] groups added by the guard
+  float* MS = reinterpret_cast<float*>(near + QCAP);   // [2] M (natural log domain), S
+  float* gf = MS + 2;                               // [2] 2K-th final value of the last pass, |out|
+  uint32_t* gi = reinterpret_cast<uint32_t*>(gf + 2);  // [4] best unselected supergroup key, group key, counters
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- 0: everything this row needs, one round of loads
@@ -705,16 +777,15 @@ vocab_final_kernel(MergeArgs a) {
     }
     for (int i = tx + SEL_THREADS; i <= nu; i += SEL_THREADS) pss[i] = a.pos_start[(size_t)art * (T + 1) + i];
   }
-  if (threadIdx.x < SEL_WARPS * K2) ck[threadIdx.x] = 0ull;      // lists of step 4b: 0 = no entry
   if (threadIdx.x < K2) {                           // defaults, overwritten by the winners in step 4
     a.topk_ids[(size_t)r * K2 + threadIdx.x] = 0;
     a.topk_logp[(size_t)r * K2 + threadIdx.x] = -INFINITY;
   }
-  // ---- 1a: the G best supergroups: per-warp lists, then warp 0 merges them; meanwhile the last warp combines
-  // the per-part softmax statistics of the tensor-core pass
-  warp_top_rounds(sgv > -FLT_MAX ? f2ord(sgv) : 0u, threadIdx.x, G, wk + warp * G, wi + warp * G, lane);
+  // ---- 1a: the G (+1) best supergroups: per-warp lists, then warp 0 merges them; meanwhile the last warp combines
+  // the per-part softmax statistics of the tensor-core pass and the one before it takes the norm of the output
+  warp_top_rounds(sgv > -FLT_MAX ? f2ord(sgv) : 0u, threadIdx.x, G1, wk + warp * G1, wi + warp * G1, lane);
   __syncthreads();
-  if (warp == 0) warp_merge_heads(wk, wi, SEL_WARPS, G, G, sels, lane);
+  if (warp == 0) warp_merge_heads(wk, wi, SEL_WARPS, G1, G1, sels, &gi[0], lane);
   if (warp == SEL_WARPS - 1) {
     float M2 = -FLT_MAX;
     for (int pt = lane; pt < NP; pt += 32) M2 = fmaxf(M2, pm[pt]);
@@ -726,87 +797,57 @@ vocab_final_kernel(MergeArgs a) {
     for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
     if (lane == 0) { MS[0] = M2 * kLn2; MS[1] = S; }
   }
+  if (warp == SEL_WARPS - 2) {
+    float q = 0.f;
+    for (int h = lane; h < H; h += 32) q = fmaf(outs[h], outs[h], q);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    if (lane == 0) gf[1] = sqrtf(q);
+  }
   __syncthreads();
-  // ---- 1b: the G best groups among the 16 G groups of those supergroups (thread = group, 64 contiguous bytes of
-  // the row's group maxima per supergroup)
+  // ---- 1b: the G (+1) best groups among the 16 G groups of the G best supergroups (thread = group, 64 contiguous
+  // bytes of the row's group maxima per supergroup)
   {
     const int n2 = G * 16, nw2 = (n2 + 31) >> 5;    // <= 512 threads, <= 16 warps
     if (warp < nw2) {
       const int sg = (int)threadIdx.x < n2 ? sels[threadIdx.x >> 4] : -1;
       const int grp = sg >= 0 ? sg * 16 + (int)(threadIdx.x & 15) : -1;
-      const float gv = grp >= 0 ? reinterpret_cast<const float*>(a.gmax + (size_t)r * a.gstride)[grp] : -FLT_MAX;
-      warp_top_rounds(gv > -FLT_MAX ? f2ord(gv) : 0u, grp, G, wk + warp * G, wi + warp * G, lane);
+      const float gv = (grp >= 0 && grp < ngroups) ? reinterpret_cast<const float*>(a.gmax + (size_t)r * a.gstride)[grp] : -FLT_MAX;
+      warp_top_rounds(gv > -FLT_MAX ? f2ord(gv) : 0u, grp, G1, wk + warp * G1, wi + warp * G1, lane);
     }
     __syncthreads();
-    if (warp == 0) warp_merge_heads(wk, wi, nw2, G, G, sel, lane);
+    if (warp == 0) warp_merge_heads(wk, wi, nw2, G1, G1, sel, &gi[1], lane);
   }
   __syncthreads();
-  // ---- 2: exact fp32 logit and tf32-emulated logit of every word of the selected groups: warp per word, 4 in flight
-  const int nw = G * GW;
-  for (int it0 = warp * 4; it0 < nw; it0 += SEL_WARPS * 4) {
-    float4 w4[4][2];
-    int ids[4];
-    float bb[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int it = it0 + u;
-      const int grp = it < nw ? sel[it / GW] : -1;
-      const int id = grp >= 0 ? grp * GW + (it % GW) : -1;
-      ids[u] = (id >= 0 && id < V) ? id : -1;
-      bb[u] = ids[u] >= 0 ? __ldg(a.bias + ids[u]) : 0.f;
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        const int h = lane * 4 + hh * 128;
-        w4[u][hh] = (ids[u] >= 0 && h < H) ? __ldg(reinterpret_cast<const float4*>(a.wT + (size_t)ids[u] * H + h))
-                                           : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-    }
-    float acc[8];                                   // (word u, exact) at 2u, (word u, tf32-emulated) at 2u + 1
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      float ex = 0.f, em = 0.f;
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        const int h = lane * 4 + hh * 128;
-        if (h < H) {
-          const float4 o4 = *reinterpret_cast<const float4*>(outs + h);
-          const float4 t4 = *reinterpret_cast<const float4*>(outt + h);
-          const float4 w = w4[u][hh];
-          ex = fmaf(w.x, o4.x, ex); ex = fmaf(w.y, o4.y, ex); ex = fmaf(w.z, o4.z, ex); ex = fmaf(w.w, o4.w, ex);
-          em = fmaf(tf32_rna(w.x), t4.x, em); em = fmaf(tf32_rna(w.y), t4.y, em);
-          em = fmaf(tf32_rna(w.z), t4.z, em); em = fmaf(tf32_rna(w.w), t4.w, em);
-        }
-      }
-      acc[2 * u] = ex; acc[2 * u + 1] = em;
-    }
-    const float tot = warp_multi_reduce<8>(acc, lane);          // lane l holds value l / 4
-    const int vi = lane >> 2, u = vi >> 1, it = it0 + u;
-    int id = ids[0]; float b = bb[0];
-    if (u == 1) { id = ids[1]; b = bb[1]; } else if (u == 2) { id = ids[2]; b = bb[2]; } else if (u == 3) { id = ids[3]; b = bb[3]; }
-    if ((lane & 3) == 0 && it < nw) {
-      if (vi & 1) ca[it] = id >= 0 ? tot + b : -FLT_MAX;
-      else { cx[it] = id >= 0 ? tot + b : -FLT_MAX; cid[it] = id; }
-    }
-  }
+  // ---- 2: exact fp32 logit and tf32-emulated logit of every word of the selected groups
+  rescore_groups(a, sel, G, 0, outs, outt, cx, ca, cid, warp, lane);
   __syncthreads();
-  // ---- 3: swap the tensor-core value of every re-scored word for its exact value inside the sum
-  if (warp == 0) {
-    const float M = MS[0];
-    float S = 0.f;
-    for (int c = lane; c < NC; c += 32)
-      if (cid[c] >= 0) S += expf(cx[c] - M) - expf(ca[c] - M);
+
+  const float M = MS[0];
+  const float pg = a.pointer_gen ? a.pgen[r] : 1.f;
+  // error bound of a tensor-core logit against the fp32 one (natural-log units), see 5. above
+  const float eps = 1.1e-3f * gf[1] * a.wnorm_max + 4e-6f * (fabsf(M) + 1.f);
+  int ncand = NC, s_done = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    // ---- 3: swap the tensor-core value of every (newly) re-scored word for its exact value inside the sum
+    if (warp == 0) {
+      float S = 0.f;
+      for (int c = s_done + lane; c < ncand; c += 32)
+        if (cid[c] >= 0) S += expf(cx[c] - M) - expf(ca[c] - M);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
-    if (lane == 0) MS[1] += S;
-  }
-  __syncthreads();
-  // ---- 4a: final distribution on the candidate set (model.py:158-181) as (value, ~id) keys
-  {
-    const float M = MS[0], S = MS[1];
-    const float pg = a.pointer_gen ? a.pgen[r] : 1.f;
+      for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+      if (lane == 0) MS[1] += S;
+    }
+    s_done = ncand;
+    if (threadIdx.x < SEL_WARPS * K2) ck[threadIdx.x] = 0ull;    // lists of step 4b: 0 = no entry
+    if (threadIdx.x == 0) gf[0] = -1.f;
+    __syncthreads();
+    // ---- 4a: final distribution on the candidate set (model.py:158-181) as (value, ~id) keys
+    const int nf = ncand + nu;
+    const float S = MS[1];
     for (int c = threadIdx.x; c < nf; c += SEL_THREADS) {
       float val = -FLT_MAX; int id = -1;
-      if (c < NC) {
+      if (c < ncand) {
         id = cid[c];
         if (id >= 0) {
           int lo = 0, hi2 = nu;                                 // article words are handled below with their copy mass
@@ -815,7 +856,7 @@ vocab_final_kernel(MergeArgs a) {
           else val = a.pointer_gen ? pg * (expf(cx[c] - M) / S) : expf(cx[c] - M) / S;
         }
       } else {
-        const int u = c - NC;
+        const int u = c - ncand;
         id = uids[u];
         const float omp = 1.0f - pg;
         float copy = 0.f;
@@ -825,51 +866,173 @@ vocab_final_kernel(MergeArgs a) {
       }
       fin[c] = id >= 0 ? ((unsigned long long)f2ord(val) << 32) | (0xffffffffu - (uint32_t)id) : 0ull;
     }
-  }
-  __syncthreads();
-  // ---- 4b: top-2K by counting: every warp ranks the keys of a contiguous sixteenth among themselves (keys are
-  // unique: (value, ~id) with distinct ids) and lists its 2K best in descending order; then every list entry is
-  // ranked against the other lists by binary search and the 2K best overall are written out.
-  {
-    const int cw = (nf + SEL_WARPS - 1) / SEL_WARPS, c0 = warp * cw, c1 = min(nf, c0 + cw);
-    for (int cb = c0 + lane; cb < c1; cb += 64) {               // a lane ranks two of its keys per pass
-      const unsigned long long k0 = fin[cb], k1 = cb + 32 < c1 ? fin[cb + 32] : 0ull;
-      int r0 = 0, r1 = 0;
-      for (int c = c0; c < c1; ++c) {
-        const unsigned long long o = fin[c];
-        r0 += o > k0 ? 1 : 0; r1 += o > k1 ? 1 : 0;
+    __syncthreads();
+    // ---- 4b: top-2K by counting: every warp ranks the keys of a contiguous sixteenth among themselves (keys are
+    // unique: (value, ~id) with distinct ids) and lists its 2K best in descending order; then every list entry is
+    // ranked against the other lists by binary search and the 2K best overall are written out.
+    {
+      const int cw = (nf + SEL_WARPS - 1) / SEL_WARPS, c0 = warp * cw, c1 = min(nf, c0 + cw);
+      for (int cb = c0 + lane; cb < c1; cb += 64) {               // a lane ranks two of its keys per pass
+        const unsigned long long k0 = fin[cb], k1 = cb + 32 < c1 ? fin[cb + 32] : 0ull;
+        int r0 = 0, r1 = 0;
+        for (int c = c0; c < c1; ++c) {
+          const unsigned long long o = fin[c];
+          r0 += o > k0 ? 1 : 0; r1 += o > k1 ? 1 : 0;
+        }
+        if (k0 && r0 < K2) ck[warp * K2 + r0] = k0;
+        if (k1 && r1 < K2) ck[warp * K2 + r1] = k1;
       }
-      if (k0 && r0 < K2) ck[warp * K2 + r0] = k0;
-      if (k1 && r1 < K2) ck[warp * K2 + r1] = k1;
     }
-  }
-  __syncthreads();
-  if (threadIdx.x < SEL_WARPS * K2) {
-    const int w = threadIdx.x / K2, i = threadIdx.x - w * K2;
-    const unsigned long long mine = ck[threadIdx.x];
-    if (mine) {
-      int rank = i;
-      for (int w0 = 0; w0 < SEL_WARPS; w0 += 4) {
-        int cnt[4] = {0, 0, 0, 0};
+    __syncthreads();
+    if (threadIdx.x < SEL_WARPS * K2) {
+      const int w = threadIdx.x / K2, i = threadIdx.x - w * K2;
+      const unsigned long long mine = ck[threadIdx.x];
+      if (mine) {
+        int rank = i;
+        for (int w0 = 0; w0 < SEL_WARPS; w0 += 4) {
+          int cnt[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int st = 16; st > 0; st >>= 1) {
+          for (int st = 16; st > 0; st >>= 1) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int wq = w0 + q, idx = cnt[q] + st - 1;
-            if (wq != w && idx < K2 && ck[wq * K2 + idx] > mine) cnt[q] += st;
+            for (int q = 0; q < 4; ++q) {
+              const int wq = w0 + q, idx = cnt[q] + st - 1;
+              if (wq != w && idx < K2 && ck[wq * K2 + idx] > mine) cnt[q] += st;
+            }
+          }
+          rank += cnt[0] + cnt[1] + cnt[2] + cnt[3];
+        }
+        if (rank < K2) {
+          const float v = ord2f((uint32_t)(mine >> 32));
+          a.topk_ids[(size_t)r * K2 + rank] = (int)(0xffffffffu - (uint32_t)mine);
+          a.topk_logp[(size_t)r * K2 + rank] = logf(v);            // model.py:285
+          if (rank == K2 - 1) gf[0] = v;
+        }
+      }
+    }
+    if (pass == 1 || a.guard == GUARD_OFF) break;
+    __syncthreads();
+    // ---- 5: guard (every quantity below is block-uniform)
+    const uint32_t uk = gi[0] > gi[1] ? gi[0] : gi[1];            // best maximum among the groups left out (0: none)
+    const float pstar = gf[0];                                    // -1: fewer than 2K entries so far
+    if (uk == 0u && a.guard != GUARD_DENSE) break;                // every group of the row was a candidate
+    bool ok = false;
+    if (uk != 0u) ok = pstar > pg * (expf(ord2f(uk) * kLn2 + eps - M) / S);
+    if (ok && a.guard == GUARD_AUTO) break;
+    // smallest exact logit an outside word needs to reach the 2K-th value (with slack for the rounding of log / exp)
+    float theta = -FLT_MAX;
+    if (pstar > 0.f && pg > 0.f) theta = M + logf(pstar * S / pg) - 1e-5f;
+    if (a.guard == GUARD_WIDEN) theta -= 0.25f;                   // test mode: re-score well below the threshold too
+    bool dense = a.guard == GUARD_DENSE;
+    int n_near = 0;
+    if (!dense) {
+      if (threadIdx.x == 0) gi[2] = 0u;
+      __syncthreads();
+      const float* grow = reinterpret_cast<const float*>(a.gmax + (size_t)r * a.gstride);
+      for (int g = threadIdx.x; g < ngroups; g += SEL_THREADS) {
+        const float gv = grow[g];
+        if (gv > -FLT_MAX && gv * kLn2 + eps >= theta) {
+          bool in = false;
+          for (int q = 0; q < G; ++q) in |= sel[q] == g;
+          if (!in) {
+            const uint32_t idx = atomicAdd(&gi[2], 1u);
+            if (idx < (uint32_t)QCAP) near[idx] = g;
           }
         }
-        rank += cnt[0] + cnt[1] + cnt[2] + cnt[3];
       }
-      if (rank < K2) {
-        const uint32_t o = (uint32_t)(mine >> 32);
-        const float v = __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu));
-        a.topk_ids[(size_t)r * K2 + rank] = (int)(0xffffffffu - (uint32_t)mine);
-        a.topk_logp[(size_t)r * K2 + rank] = logf(v);            // model.py:285
+      __syncthreads();
+      n_near = (int)gi[2];
+      if (n_near > QCAP) dense = true;
+      else if (n_near == 0) break;
+      else {                                                      // ascending group order: the arithmetic below must not
+        const int mine = (int)threadIdx.x < n_near ? near[threadIdx.x] : 0;   // depend on who won the atomics
+        int rank = 0;
+        if ((int)threadIdx.x < n_near) for (int j = 0; j < n_near; ++j) rank += near[j] < mine ? 1 : 0;
+        __syncthreads();
+        if ((int)threadIdx.x < n_near) near[rank] = mine;
+        __syncthreads();
       }
+    }
+    if (!dense) {
+      rescore_groups(a, near, n_near, NC, outs, outt, cx, ca, cid, warp, lane);
+      ncand = NC + n_near * GW;
+      if (threadIdx.x == 0 && a.sel_stats) atomicAdd(a.sel_stats, 1);
+      __syncthreads();
+      continue;
+    }
+    // ---- dense: exact fp32 logit of every word of the vocabulary, QCAP groups (= one word per thread) at a time.
+    // Keeps the sum of exponentials (exact for every word) and the 2K best words that do not occur in the article
+    // (those are ranked with their copy mass from arl); survivors of a chunk are merged into the list by counting.
+    {
+      unsigned long long* carry = ck;                             // [2][K2], descending, 0 = empty
+      unsigned long long* surv = fin;                             // [<= 512]
+      if (threadIdx.x < 2 * K2) carry[threadIdx.x] = 0ull;
+      float s_part = 0.f;
+      int cb = 0;
+      for (int g0 = 0; g0 < ngroups; g0 += QCAP) {
+        const int ng = min(QCAP, ngroups - g0);
+        if ((int)threadIdx.x < ng) near[threadIdx.x] = g0 + threadIdx.x;
+        if (threadIdx.x == 0) gi[3] = 0u;
+        if ((int)threadIdx.x < K2) carry[(cb ^ 1) * K2 + threadIdx.x] = 0ull;
+        __syncthreads();
+        rescore_groups(a, near, ng, NC, outs, outt, cx, ca, cid, warp, lane);
+        __syncthreads();
+        const unsigned long long thr = carry[cb * K2 + K2 - 1];
+        if ((int)threadIdx.x < ng * GW) {
+          const int id = cid[NC + threadIdx.x];
+          if (id >= 0) {
+            const float l = cx[NC + threadIdx.x];
+            s_part += expf(l - M);
+            int lo = 0, hi2 = nu;
+            while (lo < hi2) { const int mid = (lo + hi2) >> 1; if (uids[mid] < id) lo = mid + 1; else hi2 = mid; }
+            if (!(lo < nu && uids[lo] == id)) {
+              const unsigned long long key = ((unsigned long long)f2ord(l) << 32) | (0xffffffffu - (uint32_t)id);
+              if (key > thr) surv[atomicAdd(&gi[3], 1u)] = key;
+            }
+          }
+        }
+        __syncthreads();
+        const int ns = (int)gi[3];
+        if (ns > 0) {
+          const int tot = K2 + ns;
+          for (int i = threadIdx.x; i < tot; i += SEL_THREADS) {
+            const unsigned long long k = i < K2 ? carry[cb * K2 + i] : surv[i - K2];
+            if (!k) continue;
+            int rank = 0;
+            for (int j = 0; j < K2; ++j) rank += carry[cb * K2 + j] > k ? 1 : 0;
+            for (int j = 0; j < ns; ++j) rank += surv[j] > k ? 1 : 0;
+            if (rank < K2) carry[(cb ^ 1) * K2 + rank] = k;
+          }
+          cb ^= 1;
+        }
+        __syncthreads();
+      }
+      // exact softmax denominator: per-warp sums in lane order, then the 16 warps in order (deterministic)
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s_part += __shfl_xor_sync(0xffffffffu, s_part, o);
+      float* wsum = reinterpret_cast<float*>(wk);
+      if (lane == 0) wsum[warp] = s_part;
+      for (int c = threadIdx.x; c < NCT; c += SEL_THREADS) cid[c] = -1;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        float Sx = 0.f;
+        for (int w = 0; w < SEL_WARPS; ++w) Sx += wsum[w];
+        MS[1] = Sx;
+        if (a.sel_stats) atomicAdd(a.sel_stats + 1, 1);
+      }
+      if ((int)threadIdx.x < K2) {                                // the list becomes the candidate set of the second pass
+        const unsigned long long k = carry[cb * K2 + threadIdx.x];
+        if (k) {
+          cid[threadIdx.x] = (int)(0xffffffffu - (uint32_t)k);
+          cx[threadIdx.x] = ord2f((uint32_t)(k >> 32));
+          ca[threadIdx.x] = cx[threadIdx.x];
+        }
+      }
+      ncand = K2; s_done = K2;                                    // nothing left to swap: S is exact already
+      __syncthreads();
     }
   }
 }
+
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -948,9 +1111,9 @@ int VocabTC::launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const {
 }
 
 size_t VocabTC::final_smem(int T, int n_parts) const {
-  const size_t NC = (size_t)G * GW;
-  return 8 * (NC + T) + 8 * (size_t)SEL_WARPS * K2 + 4 * (2 * (size_t)H + 2 * (size_t)SEL_WARPS * G + 2 * (size_t)n_parts +
-         2 * (size_t)T + 3 * NC + (3 * (size_t)T + 1) + 2 * (size_t)G + 2);
+  const size_t NCT = (size_t)G * GW + (size_t)QCAP * GW, G1 = (size_t)G + 1;
+  return 8 * ((NCT + T + 1) & ~(size_t)1) + 8 * (size_t)SEL_WARPS * K2 + 4 * (2 * (size_t)H + 2 * (size_t)SEL_WARPS * G1 + 2 * (size_t)n_parts +
+         2 * (size_t)T + 3 * NCT + (3 * (size_t)T + 1) + 2 * G1 + QCAP + 2 + 2 + 4) + 16;
 }
 
 int VocabTC::launch_final(const MergeArgs& a, cudaStream_t st) const {

@@ -21,6 +21,9 @@ struct MergeArgs {
   const int* active; const int* lens;
   int* topk_ids; float* topk_logp;               // [R, 2K]
   int K, K2, G, NC, H, V, T, R, n_parts, pointer_gen;
+  float wnorm_max = 0.f;                         // max over the vocabulary of |w_w|_2 (error bound of the tf32 logits)
+  int guard = 0;                                 // 0 auto, 1 always widen, 2 always dense, 3 off (tests / A-B runs)
+  int* sel_stats = nullptr;                      // [2] rows whose candidate set was widened / scored densely
 };
 
 class VocabTC {
