@@ -8,20 +8,26 @@
 // The encoder features F and the encoder states h of an article (2 x T x 2 KB) are each read from HBM exactly once
 // per step and shared by the article's K beam rows.  Work item = (article, segment of 32 encoder positions); the
 // segmentation depends on the article alone, so an article's arithmetic is the same whatever shares the batch.  A
-// persistent grid of one CTA per SM walks the items; every CTA streams the F tile and the h tile of its items through
-// a ring of three 64.5 KB shared-memory buffers filled by cp.async.bulk row copies (rows padded by 16 B so that
-// "lane = position" reads are conflict-free) completing on mbarriers, so that the tiles of the next item are in
-// flight while this one is computed:
+// persistent grid of one CTA per SM takes the items from a ticket counter (a CTA that started late simply takes
+// fewer).  Three kinds of warps per CTA:
 //
-//   E phase  warp = (pair of beam rows, slice of the 512 features), lane = position: packed FFMA2 over the row pair,
-//            tanh(x) = 1 - 2 / (1 + 2^(2 log2e x)) on the special-function unit, four features share one reciprocal
-//            (1.25 MUFU operations per tanh); the slices' partial sums are added in fixed order;
-//   softmax  inside the segment (its own maximum), p = exp(e - m_seg);
-//   C phase  thread = feature: ctx_seg[k][a] = sum_t p[t][k] h[t][a].
+//   producer (1 warp)  draws the tickets, and streams each item's F tile, h tile, decoder features and coverage
+//            into shared memory with cp.async.bulk completing on mbarriers: a ring of three 64 KB tile buffers (one
+//            copy per group of four rows; the groups sit 16 B further apart than their size so that "lane = position"
+//            reads are conflict-free), as far ahead as "consumed" mbarriers allow;
+//   E warps (16)  warp = (pair of beam rows, slice of the 512 features), lane = position: packed FFMA2 over the row
+//            pair, tanh(x) = 1 - 2 / (1 + 2^(2 log2e x)) on the special-function unit, four features share one
+//            reciprocal (1.25 MUFU operations per tanh) -- this is the part that is bound by the special-function
+//            unit, and it runs back to back, item after item;
+//   C warps (8)   meanwhile finish the PREVIOUS item: slices' partial sums added in fixed order, softmax inside
+//            the segment (its own maximum), p = exp(e - m_seg), ctx_seg[k][a] = sum_t p[t][k] h[t][a] with
+//            thread = 2 features, and write (m_seg, sum p, ctx_seg) to a small scratch.
 //
-// Every segment writes (m_seg, sum p, ctx_seg) to a small scratch; the CTA that completes an article's LAST segment
-// (a counter per article, self-resetting) merges the segments in segment order -- M = max m_seg, S = sum s_seg
-// e^(m_seg - M) -- and writes attn (softmax, then the reference's re-normalisation) and the context vector.
+// A second, small kernel (one CTA per article) then merges the segments in segment order -- M = max m_seg,
+// S = sum s_seg e^(m_seg - M) -- and writes attn (softmax, then the reference's re-normalisation) and the context
+// vector.  (Merging inside the first kernel, by the CTA that finished an article's last segment, was measured: with
+// nearly all of the SM's memory configured as shared there is next to no L1, and the merge's ~60 L2 loads per thread
+// took 15k cycles on the C warps, which then held up the tile ring.)
 #include <cuda_runtime.h>
 
 #include <cfloat>
@@ -33,23 +39,33 @@ namespace pgn {
 
 namespace {
 
-constexpr int AF_A = 512, AF_SEG = 32, AF_NT = 512, AF_NW = AF_NT / 32;
-constexpr int AF_ROWF = AF_A + 4;                    // row pitch in floats: 2 KB + 16 B
-constexpr int AF_TILE = AF_SEG * AF_ROWF * 4;        // bytes of one ring buffer
+constexpr int AF_A = 512, AF_SEG = 32;
+constexpr int AF_NE = 512, AF_EW = AF_NE / 32;       // E threads / warps
+constexpr int AF_CW = 8, AF_NCT = AF_CW * 32;        // C warps / threads (thread = 2 features in the C phase)
+constexpr int AF_NT = AF_NE + AF_NCT + 32;           // + one producer warp
+constexpr int AF_GRPF = 4 * AF_A + 4;                // pitch of a group of four rows in floats: 8 KB + 16 B
+constexpr int AF_TILE = (AF_SEG / 4) * AF_GRPF * 4;  // bytes of one ring buffer
 constexpr float kS = 2.885390081777927f;             // 2 log2(e): e^{2x} = 2^{kS x}
+constexpr int AF_MAXSEG = 32;                        // max_enc_steps <= 1024
+constexpr int AF_MAXB = 1024;                        // articles per device batch this kernel takes (more: the kernel pair)
+constexpr int AF_IQ = 4;                             // item slots between the producer and the other warps
 
 template <int K> struct AfCfg {
   static constexpr int NPAIR = K / 2;
-  static constexpr int NSLICE = AF_NW / NPAIR;       // warps (feature slices) per row pair
+  static constexpr int NSLICE = AF_EW / NPAIR;       // warps (feature slices) per row pair
   static constexpr int SLICE = AF_A / NSLICE;        // features per warp
+  static constexpr int NDS = K == 4 ? 2 : 1;         // buffers of decoder features + coverage (shared memory is the limit)
+  static constexpr int DS_FLOATS = K * AF_A;         // one buffer: [NPAIR][512][2], kS * decoder features
   static constexpr int OFF_PART = 3 * AF_TILE;                       // [NSLICE][K][32] partial energies
-  static constexpr int OFF_DS = OFF_PART + NSLICE * K * 32 * 4;      // [NPAIR][512][2] kS * decoder features
-  static constexpr int OFF_VS = OFF_DS + AF_A * K * 4;               // [512] -2 v
+  static constexpr int OFF_DS = OFF_PART + NSLICE * K * 32 * 4;      // [NDS][NPAIR][512][2]
+  static constexpr int OFF_VS = OFF_DS + NDS * DS_FLOATS * 4;        // [512] -2 v
   static constexpr int OFF_WS = OFF_VS + AF_A * 4;                   // [512] kS w_c
-  static constexpr int OFF_P = OFF_WS + AF_A * 4;                    // [32][K] p = exp(e - m_seg)
-  static constexpr int OFF_RED = OFF_P + 32 * K * 4;                 // [AF_NW][K] + [3][K] merge scratch
-  static constexpr int OFF_BAR = OFF_RED + (AF_NW * K + 4 * K) * 4;  // 3 mbarriers + flag
-  static constexpr int SMEM = OFF_BAR + 64;
+  static constexpr int OFF_CV = OFF_WS + AF_A * 4;                   // [NDS][K][32] coverage of the item's positions
+  static constexpr int OFF_P = OFF_CV + NDS * K * 32 * 4;            // [32][K] p = exp(e - m_seg)
+  static constexpr int OFF_BAR = OFF_P + 32 * K * 4;                 // mbarriers
+  static constexpr int OFF_INT = OFF_BAR + 192;                      // item slots
+  static constexpr int OFF_NSG = OFF_INT + 32;          // [B] segments of every live article, [B] positions of its last segment
+  static constexpr int SMEM = OFF_NSG + 2 * AF_MAXB;
 };
 
 __device__ __forceinline__ uint32_t af_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -86,145 +102,181 @@ __device__ __forceinline__ void af_bar_wait(uint64_t* bar, uint32_t parity) {
     if (!ok && ++spins > (1u << 26)) __trap();       // a protocol bug becomes an error, not a hang
   }
 }
+__device__ __forceinline__ void af_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(af_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void af_expect(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(af_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void af_bulk(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(af_u32(dst)), "l"(src), "r"(bytes), "r"(af_u32(bar)) : "memory");
+}
 
 struct AfArgs {
   const int* lens; const int* active;
   const float* enc_feat; const float* enc_states;    // [B, T, 512]
-  const float* dfeat;                                // [B*K, 512]
+  const float* dpack;                                // [B, K/2, 512, 2] = kS * decoder features, beam rows interleaved in pairs
   const float* cov;                                  // [B*K, T] (nullptr: no coverage term)
   const float* v; const float* w_c;                  // [512]
   float* e;                                          // [B*K, T] energies (scratch)
   float* pctx;                                       // [B, NSEG, K, 512] per-segment context partials (scratch)
   float* segstat;                                    // [B, NSEG, K, 2] per-segment (max, sum) (scratch)
-  int* counters;                                     // [B] segments completed; zero before the launch, zero after it
-  float* attn;                                       // [B*K, T]
-  float* ctx; int ctx_ld;                            // context vector of row r at ctx + r * ctx_ld
+  int* ticket;                                       // work counter: zero before the launch, zero after it
   int B, T, nseg_max;
 };
 
-// Warp 0 issues the row copies of one tile (rows [t0, t0 + n) of `src`, 2 KB each) into a ring buffer.
-__device__ __forceinline__ void af_issue_tile(float* buf, uint64_t* bar, const float* src, int n, int lane) {
-  if (lane == 0) {
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // the buffer's last readers used ordinary loads
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(af_u32(bar)), "r"((uint32_t)n * AF_A * 4u) : "memory");
-  }
-  __syncwarp();
-  if (lane < n)
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(af_u32(buf + lane * AF_ROWF)), "l"(src + (size_t)lane * AF_A), "n"(AF_A * 4), "r"(af_u32(bar)) : "memory");
-}
+// Position p of a segment lives in row group p >> 2 (four 2 KB rows, contiguous in HBM -> ONE bulk copy per group) and
+// the groups are 16 B further apart than their size, so that the eight lanes of a quarter warp -- which hold positions of
+// eight different groups, see af_pos() -- read eight different 16-byte bank groups.
+__device__ __forceinline__ int af_off(int p) { return (p >> 2) * AF_GRPF + (p & 3) * AF_A; }      // in floats
+__device__ __forceinline__ int af_pos(int lane) { return (lane & 7) * 4 + (lane >> 3); }           // E phase: lane -> position
+
+__device__ __forceinline__ void af_sync_e() { asm volatile("bar.sync 1, %0;" ::"n"(AF_NE) : "memory"); }    // E warps only
+__device__ __forceinline__ void af_sync_c() { asm volatile("bar.sync 2, %0;" ::"n"(AF_NCT) : "memory"); }   // C warps only
 
 template <int K>
 __global__ void __launch_bounds__(AF_NT, 1)
 attn_fused_kernel(AfArgs a) {
   using C = AfCfg<K>;
+  constexpr int NDS = C::NDS;
   extern __shared__ __align__(128) unsigned char smraw[];
   float* tiles = reinterpret_cast<float*>(smraw);
   float* part = reinterpret_cast<float*>(smraw + C::OFF_PART);
   float* ds = reinterpret_cast<float*>(smraw + C::OFF_DS);
   float* vs = reinterpret_cast<float*>(smraw + C::OFF_VS);
   float* ws = reinterpret_cast<float*>(smraw + C::OFF_WS);
+  float* cvs = reinterpret_cast<float*>(smraw + C::OFF_CV);
   float* psm = reinterpret_cast<float*>(smraw + C::OFF_P);
-  float* red = reinterpret_cast<float*>(smraw + C::OFF_RED);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smraw + C::OFF_BAR);
-  int* flag = reinterpret_cast<int*>(bars + 3);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smraw + C::OFF_BAR);    // [3] tile landed (transaction bytes)
+  uint64_t* empty = full + 3;                                          // [3] tile consumed
+  uint64_t* itembar = empty + 3;                                       // [AF_IQ] item slot written
+  uint64_t* dsfull = itembar + AF_IQ;                                  // [2] decoder features + coverage landed
+  uint64_t* dsfree = dsfull + 2;                                       // [2] ... consumed
+  uint64_t* efull = dsfree + 2;                                        // partial energies of an item written
+  uint64_t* efree = efull + 1;                                         // ... consumed
+  volatile int* items = reinterpret_cast<int*>(smraw + C::OFF_INT);    // [AF_IQ] the CTA's j-th item (-1: no more)
+  unsigned char* nsg = smraw + C::OFF_NSG;
+  unsigned char* lastn = nsg + AF_MAXB;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int T = a.T, NSEG = a.nseg_max;
   const int n_items = a.B * NSEG;
 
-  // the items of this CTA: i = blockIdx.x, + gridDim.x, ... restricted to live articles' existing segments
-  auto valid = [&](int i) -> bool {
-    const int art = i / NSEG, seg = i - art * NSEG;
-    return a.active[art] && seg * AF_SEG < a.lens[art];
-  };
-  auto next_item = [&](int i) -> int {
-    i += gridDim.x;
-    while (i < n_items && !valid(i)) i += gridDim.x;
-    return i;
-  };
-  int it0 = (int)blockIdx.x;
-  while (it0 < n_items && !valid(it0)) it0 += gridDim.x;
-  if (it0 >= n_items) return;
-  int it1 = next_item(it0);
-
+  // Segments of every live article (0: finished or empty) and the length of its last segment, in shared memory: with
+  // this much of the SM's memory configured as shared there is next to no L1 left, and walking the item list must
+  // not cost an L2 round trip per look-up.
+  for (int b = tid; b < a.B; b += AF_NT) {
+    const int len = a.lens[b];
+    nsg[b] = (a.active[b] && len > 0) ? (unsigned char)((len + AF_SEG - 1) / AF_SEG) : 0;
+    lastn[b] = (unsigned char)(len > 0 ? ((len - 1) & (AF_SEG - 1)) + 1 : 0);
+  }
   if (tid == 0) {
-    for (int b = 0; b < 3; ++b) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(af_u32(&bars[b])));
+    for (int b = 0; b < 16; ++b) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(af_u32(&full[b])));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   for (int i = tid; i < AF_A; i += AF_NT) { vs[i] = -2.0f * a.v[i]; ws[i] = a.cov ? kS * a.w_c[i] : 0.f; }
+  if (!a.cov) for (int i = tid; i < NDS * K * 32; i += AF_NT) cvs[i] = 0.f;
   __syncthreads();
-  float vsum = 0.f;                                  // sum_a v_a: e = sum v - 2 sum v / (1 + e^{2x})
-  for (int i = lane; i < AF_A; i += 32) vsum += vs[i];
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) vsum += __shfl_xor_sync(0xffffffffu, vsum, o);
-  vsum *= -0.5f;
-
   auto item_geom = [&](int i, int& art, int& seg, int& n) {
     art = i / NSEG; seg = i - art * NSEG;
-    n = min(AF_SEG, a.lens[art] - seg * AF_SEG);
+    n = seg == (int)nsg[art] - 1 ? (int)lastn[art] : AF_SEG;
   };
-  // tile loads are numbered: load 2j = F tile of the CTA's j-th item, 2j + 1 = its h tile; load n uses buffer n % 3
-  uint32_t n_load = 0;                               // next load to issue (warp 0)
-  auto issue = [&](int i, bool states) {
-    int art, seg, n;
-    item_geom(i, art, seg, n);
-    const float* src = (states ? a.enc_states : a.enc_feat) + ((size_t)art * T + (size_t)seg * AF_SEG) * AF_A;
-    const uint32_t b = n_load % 3;
-    af_issue_tile(tiles + (size_t)b * (AF_TILE / 4), &bars[b], src, n, lane);
-    ++n_load;
+  // the j-th item of this CTA, as handed over by the producer (-1: no more)
+  auto get_item = [&](uint32_t j) -> int {
+    af_bar_wait(&itembar[j % AF_IQ], (j / AF_IQ) & 1);
+    return items[j % AF_IQ];
   };
-  if (warp == 0) {
-    issue(it0, false);
-    issue(it0, true);
-    if (it1 < n_items) issue(it1, false);
-  }
-  // per-warp roles
-  const int pair = warp % C::NPAIR, slice = warp / C::NPAIR;
-  // decoder features and coverage of the first item
-  float dreg[K];
-  float cv0 = 0.f, cv1 = 0.f;
-  {
-    int art, seg, n;
-    item_geom(it0, art, seg, n);
-#pragma unroll
-    for (int k = 0; k < K; ++k) dreg[k] = a.dfeat[(size_t)(art * K + k) * AF_A + tid];
-    if (a.cov && lane < n) {
-      cv0 = a.cov[(size_t)(art * K + 2 * pair) * T + seg * AF_SEG + lane];
-      cv1 = a.cov[(size_t)(art * K + 2 * pair + 1) * T + seg * AF_SEG + lane];
-    }
-  }
-  const unsigned long long kS2 = af_pk2(kS, kS), one2 = af_pk2(1.0f, 1.0f);
-  uint32_t j = 0;                                    // index of the current item in this CTA's sequence
-  for (int it = it0; it < n_items; it = it1, it1 = next_item(it1), ++j) {
-    int art, seg, n;
-    item_geom(it, art, seg, n);
-    const int t0 = seg * AF_SEG;
-    // ds of this item (the E phase of the previous item is over: see the barrier at the end of the loop body)
-#pragma unroll
-    for (int p = 0; p < C::NPAIR; ++p)
-      *reinterpret_cast<float2*>(ds + ((size_t)p * AF_A + tid) * 2) = make_float2(kS * dreg[2 * p], kS * dreg[2 * p + 1]);
-    const unsigned long long cv2 = af_pk2(cv0, cv1);
-    // prefetch the next item's decoder features and coverage into registers
-    if (it1 < n_items) {
-      int art1, seg1, n1;
-      item_geom(it1, art1, seg1, n1);
-#pragma unroll
-      for (int k = 0; k < K; ++k) dreg[k] = a.dfeat[(size_t)(art1 * K + k) * AF_A + tid];
-      cv0 = cv1 = 0.f;
-      if (a.cov && lane < n1) {
-        cv0 = a.cov[(size_t)(art1 * K + 2 * pair) * T + seg1 * AF_SEG + lane];
-        cv1 = a.cov[(size_t)(art1 * K + 2 * pair + 1) * T + seg1 * AF_SEG + lane];
+
+  // Tile loads are numbered: load 2j = F tile of the CTA's j-th item, 2j + 1 = its h tile; load n uses buffer n % 3.
+  if (warp == AF_EW + AF_CW) {
+    // ===== producer warp =====
+    // Draws the CTA's items from the ticket counter (ticket = article * NSEG + segment; tickets of finished articles
+    // or of segments past an article's end are skipped), hands them to the other warps through `items`, and streams
+    // their data as far ahead as the buffers allow.
+    int* ticket = a.ticket;
+    auto draw = [&]() -> int {                                         // lane 0 only
+      for (;;) {
+        const int t = atomicAdd(ticket, 1);
+        if (t >= n_items) {
+          // every CTA draws exactly one ticket past the end; the last of them leaves the counter at zero
+          if (t == n_items + (int)gridDim.x - 1) *ticket = 0;
+          return -1;
+        }
+        const int art = t / NSEG;
+        if (t - art * NSEG < (int)nsg[art]) return t;
       }
+    };
+    auto hand_over = [&](uint32_t j, int it) {                         // lane 0 only
+      items[j % AF_IQ] = it;
+      af_arrive(&itembar[j % AF_IQ]);
+    };
+    auto issue_tile = [&](uint32_t nl, int it, bool states) {
+      int art, seg, n;
+      item_geom(it, art, seg, n);
+      const uint32_t b = nl % 3;
+      const float* src = (states ? a.enc_states : a.enc_feat) + ((size_t)art * T + (size_t)seg * AF_SEG) * AF_A;
+      float* buf = tiles + (size_t)b * (AF_TILE / 4);
+      if (lane == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // the buffer's last readers used ordinary loads
+        af_expect(&full[b], (uint32_t)n * AF_A * 4u);
+      }
+      __syncwarp();
+      const int rows = min(4, n - 4 * lane);                           // lane g copies row group g
+      if (rows > 0) af_bulk(buf + lane * AF_GRPF, src + (size_t)lane * 4 * AF_A, (uint32_t)rows * AF_A * 4u, &full[b]);
+    };
+    auto issue_ds = [&](uint32_t j, int it) {                          // decoder features (one copy) + coverage (K copies)
+      int art, seg, n;
+      item_geom(it, art, seg, n);
+      const uint32_t b = j % NDS;
+      af_bar_wait(&dsfree[b], ((j / NDS) & 1) ^ 1);
+      const uint32_t cvb = a.cov ? (uint32_t)((n + 3) & ~3) * 4u : 0u;
+      if (lane == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        af_expect(&dsfull[b], (uint32_t)C::DS_FLOATS * 4u + (uint32_t)K * cvb);
+        af_bulk(ds + (size_t)b * C::DS_FLOATS, a.dpack + (size_t)art * C::DS_FLOATS, (uint32_t)C::DS_FLOATS * 4u, &dsfull[b]);
+      }
+      __syncwarp();
+      if (a.cov && lane < K)
+        af_bulk(cvs + ((size_t)b * K + lane) * 32, a.cov + (size_t)(art * K + lane) * T + seg * AF_SEG, cvb, &dsfull[b]);
+    };
+    uint32_t nl = 0, j = 0;                                            // next load, item being loaded
+    int cur = 0;
+    if (lane == 0) { cur = draw(); hand_over(0, cur); }
+    cur = __shfl_sync(0xffffffffu, cur, 0);
+    while (cur >= 0) {
+      int nxt = 0;
+      for (int states = 0; states < 2; ++states, ++nl) {
+        af_bar_wait(&empty[nl % 3], ((nl / 3) & 1) ^ 1);               // the buffer's previous tile has been consumed
+        issue_tile(nl, cur, states != 0);
+        if (states == 0) {
+          issue_ds(j, cur);
+          if (lane == 0) { nxt = draw(); hand_over(j + 1, nxt); }      // the next item, while this one's data flies
+          nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        }
+      }
+      cur = nxt;
+      ++j;
     }
-    __syncthreads();                                 // ds complete
-    // ---------------- E phase ----------------
-    {
-      const uint32_t ld = 2 * j, b = ld % 3;
-      af_bar_wait(&bars[b], (ld / 3) & 1);
-      const float* Frow = tiles + (size_t)b * (AF_TILE / 4) + lane * AF_ROWF + slice * C::SLICE;
+    return;
+  }
+
+  if (warp < AF_EW) {
+    // ===== E warps: partial energies of item after item =====
+    const int pair = warp % C::NPAIR, slice = warp / C::NPAIR;
+    const int mypos = af_pos(lane);
+    const unsigned long long kS2 = af_pk2(kS, kS), one2 = af_pk2(1.0f, 1.0f);
+    for (uint32_t j = 0;; ++j) {
+      const int it = get_item(j);
+      if (it < 0) break;
+      const uint32_t db = j % NDS, ld = 2 * j, b = ld % 3;
+      af_bar_wait(&dsfull[db], (j / NDS) & 1);
+      af_bar_wait(&full[b], (ld / 3) & 1);
+      const float* cvp = cvs + ((size_t)db * K + 2 * pair) * 32 + mypos;
+      const unsigned long long cv2 = af_pk2(cvp[0], cvp[32]);
+      const float* Frow = tiles + (size_t)b * (AF_TILE / 4) + af_off(mypos) + slice * C::SLICE;
       const float4* vs4 = reinterpret_cast<const float4*>(vs + slice * C::SLICE);
       const float4* ws4 = reinterpret_cast<const float4*>(ws + slice * C::SLICE);
-      const float4* ds4 = reinterpret_cast<const float4*>(ds + ((size_t)pair * AF_A + slice * C::SLICE) * 2);
+      const float4* ds4 = reinterpret_cast<const float4*>(ds + (size_t)db * C::DS_FLOATS + ((size_t)pair * AF_A + slice * C::SLICE) * 2);
       unsigned long long acc2 = 0ull;
 #pragma unroll 2
       for (int c = 0; c < C::SLICE / 4; ++c) {
@@ -255,15 +307,34 @@ attn_fused_kernel(AfArgs a) {
       }
       float s0, s1;
       af_upk2(acc2, s0, s1);
-      part[(slice * K + 2 * pair) * 32 + lane] = s0;
-      part[(slice * K + 2 * pair + 1) * 32 + lane] = s1;
+      if (j > 0) af_bar_wait(efree, (j - 1) & 1);    // the C warps have read the previous item's partial sums
+      part[(slice * K + 2 * pair) * 32 + mypos] = s0;
+      part[(slice * K + 2 * pair + 1) * 32 + mypos] = s1;
+      af_sync_e();                                   // every E warp is done with the F tile, the features and `part` is complete
+      if (tid == 0) { af_arrive(&empty[b]); af_arrive(&dsfree[db]); af_arrive(efull); }
     }
-    __syncthreads();                                 // partial energies complete; the F buffer is free
-    // the freed buffer takes the h tile of the next item
-    if (warp == 0 && it1 < n_items) issue(it1, true);
-    // ---------------- energies, softmax inside the segment ----------------
-    if (warp < K) {
-      const int k = warp;
+    return;
+  }
+
+  // ===== C warps: softmax inside the segment, context partial =====
+  const int ctid = tid - AF_NE, cw = warp - AF_EW;
+  float vsum = 0.f;                                  // sum_a v_a: e = sum v - 2 sum v / (1 + e^{2x})
+  for (int i = lane; i < AF_A; i += 32) vsum += vs[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) vsum += __shfl_xor_sync(0xffffffffu, vsum, o);
+  vsum *= -0.5f;
+  for (uint32_t j = 0;; ++j) {
+    const int it = get_item(j);
+    if (it < 0) break;
+    int art, seg, n;
+    item_geom(it, art, seg, n);
+    const int t0 = seg * AF_SEG;
+    // ---------------- energies, softmax inside the segment (lane = position) ----------------
+    af_bar_wait(efull, j & 1);
+#pragma unroll
+    for (int kk = 0; kk < K; kk += AF_CW) {
+      const int k = kk + cw;
+      if (k >= K) break;                             // (beam 4: the upper four C warps have no row)
       float e = vsum;
 #pragma unroll
       for (int s = 0; s < C::NSLICE; ++s) e += part[(s * K + k) * 32 + lane];       // fixed order
@@ -282,116 +353,147 @@ attn_fused_kernel(AfArgs a) {
         st[0] = m; st[1] = s;
       }
     }
-    __syncthreads();                                 // p complete
-    // ---------------- C phase ----------------
+    af_sync_c();                                     // p complete, `part` read
+    if (ctid == 0) af_arrive(efree);
+    // ---------------- context partial: thread = 2 features, packed over row pairs ----------------
     {
       const uint32_t ld = 2 * j + 1, b = ld % 3;
-      af_bar_wait(&bars[b], (ld / 3) & 1);
-      const float* Hc = tiles + (size_t)b * (AF_TILE / 4) + tid;
-      float acc[K];
+      af_bar_wait(&full[b], (ld / 3) & 1);
+      const float* Hc = tiles + (size_t)b * (AF_TILE / 4) + 2 * ctid;
+      unsigned long long acc2[C::NPAIR][2];
 #pragma unroll
-      for (int k = 0; k < K; ++k) acc[k] = 0.f;
-#pragma unroll 4
+      for (int p = 0; p < C::NPAIR; ++p) { acc2[p][0] = 0ull; acc2[p][1] = 0ull; }
+#pragma unroll 8
       for (int t = 0; t < n; ++t) {
-        const float h = Hc[t * AF_ROWF];
+        const float2 h = *reinterpret_cast<const float2*>(Hc + af_off(t));
 #pragma unroll
-        for (int k4 = 0; k4 < K; k4 += 4) {
-          const float4 p4 = *reinterpret_cast<const float4*>(psm + t * K + k4);
-          acc[k4] = fmaf(p4.x, h, acc[k4]); acc[k4 + 1] = fmaf(p4.y, h, acc[k4 + 1]);
-          acc[k4 + 2] = fmaf(p4.z, h, acc[k4 + 2]); acc[k4 + 3] = fmaf(p4.w, h, acc[k4 + 3]);
+        for (int p2 = 0; p2 < C::NPAIR; p2 += 2) {
+          const ulonglong2 pp = *reinterpret_cast<const ulonglong2*>(psm + t * K + 2 * p2);   // rows (2 p2, +1), (2 p2 + 2, +3)
+          acc2[p2][0] = af_fma2(pp.x, af_pk2(h.x, h.x), acc2[p2][0]);
+          acc2[p2][1] = af_fma2(pp.x, af_pk2(h.y, h.y), acc2[p2][1]);
+          acc2[p2 + 1][0] = af_fma2(pp.y, af_pk2(h.x, h.x), acc2[p2 + 1][0]);
+          acc2[p2 + 1][1] = af_fma2(pp.y, af_pk2(h.y, h.y), acc2[p2 + 1][1]);
         }
       }
-      float* pc = a.pctx + (size_t)(art * NSEG + seg) * K * AF_A + tid;
+      float* pc = a.pctx + (size_t)(art * NSEG + seg) * K * AF_A + 2 * ctid;
 #pragma unroll
-      for (int k = 0; k < K; ++k) pc[k * AF_A] = acc[k];
-    }
-    // publish the segment; the CTA that completes the article's last segment merges
-    __threadfence();
-    __syncthreads();                                 // the h buffer and psm are free; every partial is written
-    if (warp == 0) {
-      // the freed buffer takes the F tile of the item after next
-      const int it2 = it1 < n_items ? next_item(it1) : n_items;
-      if (it2 < n_items) issue(it2, false);
-    }
-    const int nseg = (a.lens[art] + AF_SEG - 1) / AF_SEG;
-    if (tid == 0) *flag = (atomicAdd(a.counters + art, 1) == nseg - 1) ? 1 : 0;
-    __syncthreads();
-    if (*flag) {
-      __threadfence();
-      const int len = a.lens[art];
-      float* Mk = red + AF_NW * K;                   // [K] M, [K] S, [K] s2
-      float* Sk = Mk + K;
-      float* S2 = Sk + K;
-      if (warp < K) {                                // segment statistics -> M, S of the row (segment order)
-        const int k = warp;
-        float m = -FLT_MAX;
-        for (int s = lane; s < nseg; s += 32) m = fmaxf(m, __ldcg(a.segstat + ((size_t)(art * NSEG + s) * K + k) * 2));
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        float S = 0.f;
-        if (lane == 0)
-          for (int s = 0; s < nseg; ++s) {
-            const float* st = a.segstat + ((size_t)(art * NSEG + s) * K + k) * 2;
-            S += __ldcg(st + 1) * expf(__ldcg(st) - m);
-          }
-        if (lane == 0) { Mk[k] = m; Sk[k] = S; }
+      for (int p = 0; p < C::NPAIR; ++p) {
+        float lo0, hi0, lo1, hi1;
+        af_upk2(acc2[p][0], lo0, hi0);
+        af_upk2(acc2[p][1], lo1, hi1);
+        *reinterpret_cast<float2*>(pc + (2 * p) * AF_A) = make_float2(lo0, lo1);
+        *reinterpret_cast<float2*>(pc + (2 * p + 1) * AF_A) = make_float2(hi0, hi1);
       }
-      __syncthreads();
-      // softmax over the article's positions (:98), its sum for the re-normalisation (:100-101)
-      float sum[K];
-#pragma unroll
-      for (int k = 0; k < K; ++k) sum[k] = 0.f;
-      for (int t = tid; t < len; t += AF_NT) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-          const size_t o = (size_t)(art * K + k) * T + t;
-          const float x = expf(__ldcg(a.e + o) - Mk[k]) / Sk[k];
-          a.attn[o] = x;
-          sum[k] += x;
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sum[k] += __shfl_xor_sync(0xffffffffu, sum[k], o);
-        if (lane == 0) red[warp * K + k] = sum[k];
-      }
-      __syncthreads();
-      if (tid < K) {
-        float s2 = 0.f;
-        for (int w = 0; w < AF_NW; ++w) s2 += red[w * K + tid];
-        S2[tid] = s2;
-      }
-      __syncthreads();
-      for (int t = tid; t < len; t += AF_NT) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-          const size_t o = (size_t)(art * K + k) * T + t;
-          a.attn[o] = a.attn[o] / S2[k];             // written by this thread above
-        }
-      }
-      for (int t = len + tid; t < T; t += AF_NT) {   // the masked distribution is exactly 0 past the article (:99)
-#pragma unroll
-        for (int k = 0; k < K; ++k) a.attn[(size_t)(art * K + k) * T + t] = 0.f;
-      }
-      // context = sum_seg e^(m_seg - M) ctx_seg / S, re-normalised like attn
-      float cacc[K];
-#pragma unroll
-      for (int k = 0; k < K; ++k) cacc[k] = 0.f;
-      for (int s = 0; s < nseg; ++s) {
-        const float* pc = a.pctx + (size_t)(art * NSEG + s) * K * AF_A + tid;
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-          const float w = expf(__ldcg(a.segstat + ((size_t)(art * NSEG + s) * K + k) * 2) - Mk[k]);
-          cacc[k] = fmaf(w, __ldcg(pc + k * AF_A), cacc[k]);
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < K; ++k) a.ctx[(size_t)(art * K + k) * a.ctx_ld + tid] = cacc[k] / Sk[k] / S2[k];
-      if (tid == 0) a.counters[art] = 0;             // ready for the next launch
-      __syncthreads();                               // red / Mk are reused by a later merge of this CTA
+      af_sync_c();                                   // the h buffer and psm are free
+      if (ctid == 0) af_arrive(&empty[b]);
     }
   }
+}
+
+// Second kernel: one CTA per live article merges its segments (segment order) into attn and the context vector.
+template <int K>
+__global__ void __launch_bounds__(512)
+attn_merge_kernel(const int* __restrict__ lens, const int* __restrict__ active, const float* __restrict__ e,
+                  const float* __restrict__ pctx, const float* __restrict__ segstat, float* __restrict__ attn,
+                  float* __restrict__ ctx, int ctx_ld, int T, int NSEG) {
+  __shared__ float wsm[AF_MAXSEG * K], Mk[K], Sk[K], S2[K], red[16 * K];
+  const int art = blockIdx.x;
+  if (!active[art]) return;
+  const int len = lens[art];
+  if (len <= 0) return;
+  const int nseg = (len + AF_SEG - 1) / AF_SEG;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // everything a thread needs is requested before its first use
+  constexpr int TPT = 2;                             // positions per thread (T <= 1024)
+  float ev[TPT][K];
+#pragma unroll
+  for (int q = 0; q < TPT; ++q) {
+    const int t = tid + q * 512;
+#pragma unroll
+    for (int k = 0; k < K; ++k) ev[q][k] = t < len ? e[(size_t)(art * K + k) * T + t] : 0.f;
+  }
+  float2 st = make_float2(-FLT_MAX, 0.f);
+  if (warp < K && lane < nseg) st = *reinterpret_cast<const float2*>(segstat + ((size_t)(art * NSEG + lane) * K + warp) * 2);
+  if (warp < K) {                                    // segment statistics -> M, S of the row; lane = segment
+    float M = st.x;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+    const float w = lane < nseg ? expf(st.x - M) : 0.f;
+    if (lane < nseg) wsm[lane * K + warp] = w;
+    float S = st.y * w;                              // fixed tree over the segments
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+    if (lane == 0) { Mk[warp] = M; Sk[warp] = S; }
+  }
+  __syncthreads();
+  // softmax over the article's positions (:98) and its sum for the re-normalisation (:100-101)
+  float sum[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) sum[k] = 0.f;
+#pragma unroll
+  for (int q = 0; q < TPT; ++q) {
+    const int t = tid + q * 512;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      ev[q][k] = t < len ? expf(ev[q][k] - Mk[k]) / Sk[k] : 0.f;
+      sum[k] += ev[q][k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum[k] += __shfl_xor_sync(0xffffffffu, sum[k], o);
+    if (lane == 0) red[warp * K + k] = sum[k];
+  }
+  // context = sum_seg e^(m_seg - M) ctx_seg / S (segment order), thread = feature; eight segments' loads in flight
+  float cacc[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) cacc[k] = 0.f;
+  constexpr int SB = 32 / K;
+  for (int s0 = 0; s0 < nseg; s0 += SB) {
+    float pv[SB][K];
+#pragma unroll
+    for (int q = 0; q < SB; ++q) {
+      const float* pc = pctx + (size_t)(art * NSEG + min(s0 + q, nseg - 1)) * K * AF_A + tid;
+#pragma unroll
+      for (int k = 0; k < K; ++k) pv[q][k] = pc[k * AF_A];
+    }
+#pragma unroll
+    for (int q = 0; q < SB; ++q) {
+      if (s0 + q < nseg) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) cacc[k] = fmaf(wsm[(s0 + q) * K + k], pv[q][k], cacc[k]);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid < K) {
+    float s2 = 0.f;
+    for (int w = 0; w < 16; ++w) s2 += red[w * K + tid];
+    S2[tid] = s2;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < TPT; ++q) {
+    const int t = tid + q * 512;
+    if (t < T) {
+#pragma unroll
+      for (int k = 0; k < K; ++k)                    // the masked distribution is exactly 0 past the article (:99)
+        attn[(size_t)(art * K + k) * T + t] = t < len ? ev[q][k] / S2[k] : 0.f;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) ctx[(size_t)(art * K + k) * ctx_ld + tid] = cacc[k] / Sk[k] / S2[k];
+}
+
+// dpack[b][p][a][0..1] = kS * dfeat[(b K + 2p + {0,1}), a]: the layout the E warps read, one bulk copy per item
+__global__ void __launch_bounds__(256)
+attn_pack_dfeat_kernel(int K, int R, const float* __restrict__ dfeat, float* __restrict__ dpack, const int* __restrict__ active) {
+  const int i = blockIdx.x * 256 + threadIdx.x;      // (row pair, feature)
+  if (i >= (R / 2) * AF_A) return;
+  const int rp = i / AF_A, f = i - rp * AF_A;        // rows 2 rp, 2 rp + 1
+  if (active && !active[(2 * rp) / K]) return;
+  reinterpret_cast<float2*>(dpack)[i] = make_float2(kS * dfeat[(size_t)(2 * rp) * AF_A + f], kS * dfeat[(size_t)(2 * rp + 1) * AF_A + f]);
 }
 
 template <int K>
@@ -401,7 +503,10 @@ static cudaError_t af_prepare() {
 
 }  // namespace
 
-bool attn_fused_supported(const Dims& d) { return d.A == AF_A && (d.K == 4 || d.K == 8); }
+bool attn_fused_supported(const Dims& d) {
+  return d.A == AF_A && (d.K == 4 || d.K == 8) && d.T <= AF_SEG * AF_MAXSEG && d.T % 4 == 0;   // (16-byte coverage copies)
+}
+int attn_fused_max_articles() { return AF_MAXB; }
 
 int attn_fused_nseg(const Dims& d) { return (d.T + AF_SEG - 1) / AF_SEG; }
 
@@ -414,19 +519,31 @@ cudaError_t attn_fused_prepare(const Dims& d) {
   return cudaErrorInvalidValue;
 }
 
+int launch_attn_pack_dfeat(const Dims& d, int B, const float* dfeat, float* dpack, const int* active, cudaStream_t st) {
+  const int R = B * d.K, n = (R / 2) * AF_A;
+  if (n <= 0) return 0;
+  attn_pack_dfeat_kernel<<<(n + 255) / 256, 256, 0, st>>>(d.K, R, dfeat, dpack, active);
+  return 1;
+}
+
 int launch_attn_fused(const Dims& d, int B, const int* lens, const int* active, const float* enc_feat,
-                      const float* enc_states, const float* dfeat, const float* cov, const float* v, const float* w_c,
-                      float* e, float* pctx, float* segstat, int* counters, float* attn, float* ctx, int ctx_ld, int n_sms,
+                      const float* enc_states, const float* dpack, const float* cov, const float* v, const float* w_c,
+                      float* e, float* pctx, float* segstat, int* ticket, float* attn, float* ctx, int ctx_ld, int n_sms,
                       cudaStream_t st) {
   AfArgs a;
-  a.lens = lens; a.active = active; a.enc_feat = enc_feat; a.enc_states = enc_states; a.dfeat = dfeat;
+  a.lens = lens; a.active = active; a.enc_feat = enc_feat; a.enc_states = enc_states; a.dpack = dpack;
   a.cov = d.use_cov ? cov : nullptr; a.v = v; a.w_c = w_c; a.e = e; a.pctx = pctx; a.segstat = segstat;
-  a.counters = counters; a.attn = attn; a.ctx = ctx; a.ctx_ld = ctx_ld; a.B = B; a.T = d.T; a.nseg_max = attn_fused_nseg(d);
+  a.ticket = ticket; a.B = B; a.T = d.T; a.nseg_max = attn_fused_nseg(d);
   const int items = B * a.nseg_max;
   const int grid = items < n_sms ? items : n_sms;
-  if (d.K == 4) attn_fused_kernel<4><<<grid, AF_NT, AfCfg<4>::SMEM, st>>>(a);
-  else attn_fused_kernel<8><<<grid, AF_NT, AfCfg<8>::SMEM, st>>>(a);
-  return 1;
+  if (d.K == 4) {
+    attn_fused_kernel<4><<<grid, AF_NT, AfCfg<4>::SMEM, st>>>(a);
+    attn_merge_kernel<4><<<B, 512, 0, st>>>(lens, active, e, pctx, segstat, attn, ctx, ctx_ld, d.T, a.nseg_max);
+  } else {
+    attn_fused_kernel<8><<<grid, AF_NT, AfCfg<8>::SMEM, st>>>(a);
+    attn_merge_kernel<8><<<B, 512, 0, st>>>(lens, active, e, pctx, segstat, attn, ctx, ctx_ld, d.T, a.nseg_max);
+  }
+  return 2;
 }
 
 }  // namespace pgn

@@ -257,9 +257,10 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     DALLOC(smax_, float, (size_t)sstride_ * Rpad);
     DALLOC(artl_, float, R * T);
     DALLOC(sel_stats_, int, 2);
-    if (attn_fused_supported(d_)) {
+    if (attn_fused_supported(d_) && (int)B <= attn_fused_max_articles()) {
       DALLOC(att_pctx_, float, attn_fused_pctx_floats(d_, (int)B)); DALLOC(att_segstat_, float, attn_fused_segstat_floats(d_, (int)B));
-      DALLOC(att_cnt_, int, B);
+      DALLOC(dpack_, float, R * A);
+      DALLOC(att_cnt_, int, B + 1);                                  // per-article segment counters + the ticket counter
       attn_fused_ = attn_fused_prepare(d_) == cudaSuccess;
       if (!attn_fused_) cudaGetLastError();
     }
@@ -509,9 +510,11 @@ void Engine::encoder() {
 
 // The attention pass of a decode step over all K rows of every live article (attention_decoder.py:156-158).
 int Engine::attention(int B, const float* cov, float* attn, float* state) {
-  if (attn_fused_)
-    return launch_attn_fused(d_, B, lens_, bb_.active, enc_feat_, enc_states_, dfeat_, cov, w_.v, w_.w_c, e_, att_pctx_,
-                             att_segstat_, att_cnt_, attn, state, d_.SW, n_sms_, st_);
+  if (attn_fused_) {
+    int nl = launch_attn_pack_dfeat(d_, B, dfeat_, dpack_, bb_.active, st_);
+    return nl + launch_attn_fused(d_, B, lens_, bb_.active, enc_feat_, enc_states_, dpack_, cov, w_.v, w_.w_c, e_, att_pctx_,
+                                  att_segstat_, att_cnt_, attn, state, d_.SW, n_sms_, st_);
+  }
   int nl = launch_attn_energy(d_, B, d_.K, lens_, bb_.active, enc_feat_, dfeat_, cov, w_.v, w_.w_c, e_, st_);
   return nl + launch_attn_context(d_, B, d_.K, lens_, bb_.active, enc_states_, e_, attn, state, st_);
 }
@@ -629,7 +632,7 @@ void Engine::decoder() {
   const int B = nB_, T = d_.T, H = d_.H, A = d_.A, K = d_.K, R = B * K, SW = d_.SW;
   uint64_t& nl = stats.kernel_launches;
   nl += launch_init_beam(d_, B, lens_, bb_, st_);
-  if (att_cnt_) cudaMemsetAsync(att_cnt_, 0, (size_t)B * sizeof(int), st_);   // segment counters of the one-launch attention
+  if (att_cnt_) cudaMemsetAsync(att_cnt_, 0, (size_t)(B + 1) * sizeof(int), st_);   // segment counters of the one-launch attention
   if (d_.use_cov) cudaMemsetAsync(cov_[0], 0, (size_t)R * T * sizeof(float), st_);   // beam_search.py:105
   {  // attention_decoder.py:138-140: context of the initial state (row b*K only; all K hyps are identical)
     GemmArgs g;
@@ -776,20 +779,23 @@ std::string Engine::attention_op(int n, const float* enc_feat, const float* enc_
   if (n <= 0) return "";
   CK(cudaSetDevice(device_));
   const size_t rows = (size_t)n * d_.K;
-  const bool fused = attn_fused_ && att_cnt_;
+  const bool fused = attn_fused_ && att_cnt_ && n <= attn_fused_max_articles();
   // scratch of the call: energies, "article is live" flags, and for the one-launch kernel its per-segment partials
   const size_t n_pctx = fused ? attn_fused_pctx_floats(d_, n) : 0, n_seg = fused ? attn_fused_segstat_floats(d_, n) : 0;
+  const size_t n_pack = fused ? rows * d_.A : 0;
   float* e = nullptr;
   int* act = nullptr;
-  CK(cudaMalloc((void**)&e, (rows * d_.T + n_pctx + n_seg) * sizeof(float)));
-  if (cudaMalloc((void**)&act, (size_t)2 * n * sizeof(int)) != cudaSuccess) { cudaFree(e); return "cudaMalloc failed"; }
-  std::vector<int> ones((size_t)2 * n, 1);
-  std::fill(ones.begin() + n, ones.end(), 0);                     // [n] live flags, [n] segment counters
-  cudaMemcpyAsync(act, ones.data(), (size_t)2 * n * sizeof(int), cudaMemcpyHostToDevice, st_);
+  CK(cudaMalloc((void**)&e, (rows * d_.T + n_pctx + n_seg + n_pack) * sizeof(float)));
+  if (cudaMalloc((void**)&act, ((size_t)2 * n + 1) * sizeof(int)) != cudaSuccess) { cudaFree(e); return "cudaMalloc failed"; }
+  std::vector<int> ones((size_t)2 * n + 1, 1);
+  std::fill(ones.begin() + n, ones.end(), 0);                     // [n] live flags, [n] segment counters, ticket counter
+  cudaMemcpyAsync(act, ones.data(), ((size_t)2 * n + 1) * sizeof(int), cudaMemcpyHostToDevice, st_);
   Dims d = d_;
   d.SW = d.A;                      // ctx rows are dense [rows, A] here
   if (fused) {
-    stats.kernel_launches += launch_attn_fused(d, n, lens, act, enc_feat, enc_states, dfeat, cov, w_.v, w_.w_c, e,
+    float* pack = e + rows * d_.T + n_pctx + n_seg;
+    stats.kernel_launches += launch_attn_pack_dfeat(d, n, dfeat, pack, nullptr, st_);
+    stats.kernel_launches += launch_attn_fused(d, n, lens, act, enc_feat, enc_states, pack, cov, w_.v, w_.w_c, e,
                                                e + rows * d_.T, e + rows * d_.T + n_pctx, act + n, attn, ctx, d.A, n_sms_, st_);
   } else {
     stats.kernel_launches += launch_attn_energy(d, n, d.K, lens, act, enc_feat, dfeat, cov, w_.v, w_.w_c, e, st_);

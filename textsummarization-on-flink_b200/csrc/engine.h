@@ -80,7 +80,7 @@ class Engine {
   int32_t* h_selstats_ = nullptr;    // pinned copy, refreshed with every batch's results
   bool enc_persistent_ = true;
   bool attn_fused_ = false;          // one-launch attention (attn_fused.cu) instead of the energy + context pair
-  float *att_pctx_ = nullptr, *att_segstat_ = nullptr;
+  float *att_pctx_ = nullptr, *att_segstat_ = nullptr, *dpack_ = nullptr;
   int* att_cnt_ = nullptr;
   int attention(int B, const float* cov, float* attn, float* state);   // the step's attention pass on dfeat_
   bool vocab_tc_ = false;          // tensor-core vocabulary path in use (falls back to the SIMT kernels when

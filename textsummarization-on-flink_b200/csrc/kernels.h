@@ -70,17 +70,21 @@ int launch_attn_energy(const Dims& d, int B, int rows_per_article, const int* le
 int launch_attn_context(const Dims& d, int B, int rows_per_article, const int* lens, const int* active,
                         const float* enc_states, const float* e, float* attn, float* state, cudaStream_t st);
 // The same attention pass (all K rows of every live article) in ONE launch, hidden_dim 256 and beam 4 or 8 only
-// (attn_fused.cu): persistent CTAs stream the encoder features and states through shared memory once, per-segment
-// partials in `pctx` / `segstat`, merged by the CTA that finishes an article's last segment (`counters`: [B] ints,
-// zero before the launch and left zero by it).  ctx of row r goes to ctx + r * ctx_ld.
+// (attn_fused.cu): persistent CTAs stream the encoder features and states through shared memory once and leave
+// per-segment partials in `pctx` / `segstat`, which a second small kernel merges per article (`ticket`: one int, zero
+// before the launch and left zero by it).  ctx of row r goes to ctx + r * ctx_ld.
 bool attn_fused_supported(const Dims& d);
+int attn_fused_max_articles();                       // per launch (articles_per_batch must not exceed it)
 int attn_fused_nseg(const Dims& d);
 size_t attn_fused_pctx_floats(const Dims& d, int B);
 size_t attn_fused_segstat_floats(const Dims& d, int B);
 cudaError_t attn_fused_prepare(const Dims& d);       // per device, before the first launch (and before any capture)
+// dpack [B][K/2][512][2] = 2 log2(e) * dfeat with the article's beam rows interleaved in pairs: what the kernel's
+// producer copies into shared memory in one piece (the decoder cell writes this layout directly)
+int launch_attn_pack_dfeat(const Dims& d, int B, const float* dfeat, float* dpack, const int* active, cudaStream_t st);
 int launch_attn_fused(const Dims& d, int B, const int* lens, const int* active, const float* enc_feat,
-                      const float* enc_states, const float* dfeat, const float* cov, const float* v, const float* w_c,
-                      float* e, float* pctx, float* segstat, int* counters, float* attn, float* ctx, int ctx_ld, int n_sms,
+                      const float* enc_states, const float* dpack, const float* cov, const float* v, const float* w_c,
+                      float* e, float* pctx, float* segstat, int* ticket, float* attn, float* ctx, int ctx_ld, int n_sms,
                       cudaStream_t st);
 // p_gen = sigmoid(state[r,:] . pg_w + pg_b)                                     (attention_decoder.py:166-167)
 int launch_pgen(const Dims& d, int R, const float* state, const float* pg_w, const float* pg_b, float* pgen,

@@ -921,7 +921,8 @@ vocab_final_kernel(MergeArgs a) {
     // smallest exact logit an outside word needs to reach the 2K-th value (with slack for the rounding of log / exp)
     float theta = -FLT_MAX;
     if (pstar > 0.f && pg > 0.f) theta = M + logf(pstar * S / pg) - 1e-5f;
-    if (a.guard == GUARD_WIDEN) theta -= 0.25f;                   // test mode: re-score well below the threshold too
+    if (a.guard == GUARD_WIDEN && uk != 0u)                       // test mode: always take in the best group left out
+      theta = fminf(theta, ord2f(uk) * kLn2 - 1e-3f);
     bool dense = a.guard == GUARD_DENSE;
     int n_near = 0;
     if (!dense) {
