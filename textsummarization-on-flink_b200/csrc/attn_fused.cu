@@ -23,7 +23,7 @@
 //            the segment (its own maximum), p = exp(e - m_seg), ctx_seg[k][a] = sum_t p[t][k] h[t][a] with
 //            thread = 2 features, and write (m_seg, sum p, ctx_seg) to a small scratch.
 //
-// A second, small kernel (one CTA per article) then merges the segments in segment order -- M = max m_seg,
+// A second, small kernel (one CTA per beam row) then merges the segments in segment order -- M = max m_seg,
 // S = sum s_seg e^(m_seg - M) -- and writes attn (softmax, then the reference's re-normalisation) and the context
 // vector.  (Merging inside the first kernel, by the CTA that finished an article's last segment, was measured: with
 // nearly all of the SM's memory configured as shared there is next to no L1, and the merge's ~60 L2 loads per thread
@@ -390,100 +390,81 @@ attn_fused_kernel(AfArgs a) {
   }
 }
 
-// Second kernel: one CTA per live article merges its segments (segment order) into attn and the context vector.
-template <int K>
+// Second kernel: one CTA per beam row of every live article merges the article's segments (segment order) into the
+// row's attn and context vector.  Every load of a thread is requested before its first use.
 __global__ void __launch_bounds__(512)
-attn_merge_kernel(const int* __restrict__ lens, const int* __restrict__ active, const float* __restrict__ e,
+attn_merge_kernel(int K, const int* __restrict__ lens, const int* __restrict__ active, const float* __restrict__ e,
                   const float* __restrict__ pctx, const float* __restrict__ segstat, float* __restrict__ attn,
                   float* __restrict__ ctx, int ctx_ld, int T, int NSEG) {
-  __shared__ float wsm[AF_MAXSEG * K], Mk[K], Sk[K], S2[K], red[16 * K];
-  const int art = blockIdx.x;
+  __shared__ float wsm[AF_MAXSEG], MS[3], red[16];
+  const int r = blockIdx.x, art = r / K, k = r - art * K;
   if (!active[art]) return;
   const int len = lens[art];
   if (len <= 0) return;
   const int nseg = (len + AF_SEG - 1) / AF_SEG;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  // everything a thread needs is requested before its first use
   constexpr int TPT = 2;                             // positions per thread (T <= 1024)
-  float ev[TPT][K];
+  float ev[TPT];
 #pragma unroll
   for (int q = 0; q < TPT; ++q) {
     const int t = tid + q * 512;
-#pragma unroll
-    for (int k = 0; k < K; ++k) ev[q][k] = t < len ? e[(size_t)(art * K + k) * T + t] : 0.f;
+    ev[q] = t < len ? e[(size_t)r * T + t] : 0.f;
   }
-  float2 st = make_float2(-FLT_MAX, 0.f);
-  if (warp < K && lane < nseg) st = *reinterpret_cast<const float2*>(segstat + ((size_t)(art * NSEG + lane) * K + warp) * 2);
-  if (warp < K) {                                    // segment statistics -> M, S of the row; lane = segment
+  constexpr int SB = 16;                             // segments of context partials in flight per thread
+  float pv[SB];
+#pragma unroll
+  for (int q = 0; q < SB; ++q) pv[q] = pctx[((size_t)(art * NSEG + min(q, nseg - 1)) * K + k) * AF_A + tid];
+  if (warp == 0) {                                   // segment statistics -> M, S of the row; lane = segment
+    float2 st = make_float2(-FLT_MAX, 0.f);
+    if (lane < nseg) st = *reinterpret_cast<const float2*>(segstat + ((size_t)(art * NSEG + lane) * K + k) * 2);
     float M = st.x;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
     const float w = lane < nseg ? expf(st.x - M) : 0.f;
-    if (lane < nseg) wsm[lane * K + warp] = w;
+    wsm[lane] = w;
     float S = st.y * w;                              // fixed tree over the segments
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
-    if (lane == 0) { Mk[warp] = M; Sk[warp] = S; }
+    if (lane == 0) { MS[0] = M; MS[1] = S; }
   }
   __syncthreads();
+  const float M = MS[0], S = MS[1];
   // softmax over the article's positions (:98) and its sum for the re-normalisation (:100-101)
-  float sum[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) sum[k] = 0.f;
+  float sum = 0.f;
 #pragma unroll
   for (int q = 0; q < TPT; ++q) {
     const int t = tid + q * 512;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      ev[q][k] = t < len ? expf(ev[q][k] - Mk[k]) / Sk[k] : 0.f;
-      sum[k] += ev[q][k];
-    }
+    ev[q] = t < len ? expf(ev[q] - M) / S : 0.f;
+    sum += ev[q];
   }
 #pragma unroll
-  for (int k = 0; k < K; ++k) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum[k] += __shfl_xor_sync(0xffffffffu, sum[k], o);
-    if (lane == 0) red[warp * K + k] = sum[k];
-  }
-  // context = sum_seg e^(m_seg - M) ctx_seg / S (segment order), thread = feature; eight segments' loads in flight
-  float cacc[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) cacc[k] = 0.f;
-  constexpr int SB = 32 / K;
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) red[warp] = sum;
+  // context = sum_seg e^(m_seg - M) ctx_seg / S (segment order), thread = feature
+  float cacc = 0.f;
   for (int s0 = 0; s0 < nseg; s0 += SB) {
-    float pv[SB][K];
 #pragma unroll
-    for (int q = 0; q < SB; ++q) {
-      const float* pc = pctx + (size_t)(art * NSEG + min(s0 + q, nseg - 1)) * K * AF_A + tid;
+    for (int q = 0; q < SB; ++q)
+      if (s0 + q < nseg) cacc = fmaf(wsm[s0 + q], pv[q], cacc);
+    if (s0 + SB < nseg) {
 #pragma unroll
-      for (int k = 0; k < K; ++k) pv[q][k] = pc[k * AF_A];
-    }
-#pragma unroll
-    for (int q = 0; q < SB; ++q) {
-      if (s0 + q < nseg) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) cacc[k] = fmaf(wsm[(s0 + q) * K + k], pv[q][k], cacc[k]);
-      }
+      for (int q = 0; q < SB; ++q) pv[q] = pctx[((size_t)(art * NSEG + min(s0 + SB + q, nseg - 1)) * K + k) * AF_A + tid];
     }
   }
   __syncthreads();
-  if (tid < K) {
+  if (tid == 0) {
     float s2 = 0.f;
-    for (int w = 0; w < 16; ++w) s2 += red[w * K + tid];
-    S2[tid] = s2;
+    for (int w = 0; w < 16; ++w) s2 += red[w];
+    MS[2] = s2;
   }
   __syncthreads();
+  const float s2 = MS[2];
 #pragma unroll
   for (int q = 0; q < TPT; ++q) {
     const int t = tid + q * 512;
-    if (t < T) {
-#pragma unroll
-      for (int k = 0; k < K; ++k)                    // the masked distribution is exactly 0 past the article (:99)
-        attn[(size_t)(art * K + k) * T + t] = t < len ? ev[q][k] / S2[k] : 0.f;
-    }
+    if (t < T) attn[(size_t)r * T + t] = t < len ? ev[q] / s2 : 0.f;   // exactly 0 past the article (:99)
   }
-#pragma unroll
-  for (int k = 0; k < K; ++k) ctx[(size_t)(art * K + k) * ctx_ld + tid] = cacc[k] / Sk[k] / S2[k];
+  ctx[(size_t)r * ctx_ld + tid] = cacc / S / s2;
 }
 
 // dpack[b][p][a][0..1] = kS * dfeat[(b K + 2p + {0,1}), a]: the layout the E warps read, one bulk copy per item
@@ -538,10 +519,10 @@ int launch_attn_fused(const Dims& d, int B, const int* lens, const int* active, 
   const int grid = items < n_sms ? items : n_sms;
   if (d.K == 4) {
     attn_fused_kernel<4><<<grid, AF_NT, AfCfg<4>::SMEM, st>>>(a);
-    attn_merge_kernel<4><<<B, 512, 0, st>>>(lens, active, e, pctx, segstat, attn, ctx, ctx_ld, d.T, a.nseg_max);
+    attn_merge_kernel<<<B * 4, 512, 0, st>>>(4, lens, active, e, pctx, segstat, attn, ctx, ctx_ld, d.T, a.nseg_max);
   } else {
     attn_fused_kernel<8><<<grid, AF_NT, AfCfg<8>::SMEM, st>>>(a);
-    attn_merge_kernel<8><<<B, 512, 0, st>>>(lens, active, e, pctx, segstat, attn, ctx, ctx_ld, d.T, a.nseg_max);
+    attn_merge_kernel<<<B * 8, 512, 0, st>>>(8, lens, active, e, pctx, segstat, attn, ctx, ctx_ld, d.T, a.nseg_max);
   }
   return 2;
 }

@@ -293,6 +293,11 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
       feat_tc_ = g3_.ready;
       (void)why;
     }
+    if (H == 256 && E == 128) {
+      if (share) dcell_.share(share->dcell_);
+      else dcell_.init(d_, w_.x_MT, w_.dec_kT, w_.att_MT, w_.out_MT, [&](size_t nf) { return dalloc<float>(nf); }, st_);
+      dec_fused_ = dcell_.ready;
+    }
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
     else vtc_why_ = "vocabulary smaller than one 128-word tile";
     vocab_tc_ = vtc_.ready;
@@ -363,6 +368,15 @@ std::string Engine::set_option(const std::string& kv) {
   if (k == "check_every") { check_every_ = std::max(0, atoi(v.c_str())); return ""; }
   if (k == "features") { feat_tc_ = (v != "simt") && g3_.ready; return ""; }
   if (k == "encoder") { enc_persistent_ = (v != "steps"); return ""; }
+  if (k == "decoder") {
+    if (v == "split") { dec_fused_ = false; return ""; }
+    if (v == "fused") {
+      if (!dcell_.ready) return "fused decoder cell needs hidden_dim 256 and emb_dim 128";
+      dec_fused_ = true;
+      return "";
+    }
+    return "decoder must be fused or split";
+  }
   if (k == "attention") {
     if (v == "split") { attn_fused_ = false; return ""; }
     if (v == "fused") {
@@ -511,7 +525,8 @@ void Engine::encoder() {
 // The attention pass of a decode step over all K rows of every live article (attention_decoder.py:156-158).
 int Engine::attention(int B, const float* cov, float* attn, float* state) {
   if (attn_fused_) {
-    int nl = launch_attn_pack_dfeat(d_, B, dfeat_, dpack_, bb_.active, st_);
+    int nl = dpack_fresh_ ? 0 : launch_attn_pack_dfeat(d_, B, dfeat_, dpack_, bb_.active, st_);
+    dpack_fresh_ = false;
     return nl + launch_attn_fused(d_, B, lens_, bb_.active, enc_feat_, enc_states_, dpack_, cov, w_.v, w_.w_c, e_, att_pctx_,
                                   att_segstat_, att_cnt_, attn, state, d_.SW, n_sms_, st_);
   }
@@ -529,8 +544,13 @@ int Engine::step_launch(int B, int o, int ps) {
     sb.lens = lens_; sb.n_oov = noov_; sb.active = bb_.active; sb.sel_parent = bb_.sel_parent; sb.sel_token = bb_.sel_token;
     sb.emb = w_.emb; sb.state_old = state_[o]; sb.state_new = state_[n]; sb.attn_old = attn_[o]; sb.attn_new = attn_[n];
     sb.cov_old = cov_[o]; sb.cov_new = cov_[n]; sb.xin = xin_; sb.hprev = hprev_; sb.cprev = cprev_;
-    nl += launch_gather_step(d_, B, sb, st_);
     GemmArgs g;
+    if (dec_fused_) {
+      // gather by parent, coverage update, x, LSTM cell and attention features in one launch (dec_cell.cu)
+      nl += dcell_.launch_cell(d_, B, sb, w_.x_b, w_.dec_b, w_.att_b, dfeat_, attn_fused_ ? dpack_ : nullptr, st_);
+      dpack_fresh_ = attn_fused_;
+    } else {
+    nl += launch_gather_step(d_, B, sb, st_);
     // x = [emb(y); ctx] . Linear/Matrix + Bias                                  (attention_decoder.py:150)
     g = GemmArgs(); g.A0 = xin_; g.lda0 = E + A; g.k0 = E + A; g.B = w_.x_MT; g.ldb = E + A; g.bias = w_.x_b;
     g.C = state_[n] + A + 2 * H; g.ldc = SW; g.M = R; g.N = E; g.skinny = 1;
@@ -544,12 +564,18 @@ int Engine::step_launch(int B, int o, int ps) {
     g = GemmArgs(); g.A0 = state_[n] + A; g.lda0 = SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
     g.C = dfeat_; g.ldc = A; g.M = R; g.N = A; g.skinny = 1;
     nl += launch_gemm_nt(g, st_);
+    }
     if (profile_) cudaEventRecord(pev_[5 * ps + 0], st_);
     nl += attention(B, cov_[n], attn_[n], state_[n]);
     if (profile_) cudaEventRecord(pev_[5 * ps + 1], st_);
     // p_gen and the exact logits of the article's words are side branches (stream st2_, a parallel branch of the
     // captured graph): they run beside the out projection and the tensor-core pass and join before the final kernel
     const bool fork = d_.pointer_gen && vocab_tc_ && !profile_;
+    if (dec_fused_) {
+      // output = [h; ctx] . AttnOutputProjection + b (:173) and p_gen (:166-167) in one launch
+      nl += dcell_.launch_out(d_, B, bb_.active, state_[n], w_.out_b, w_.pg_w, w_.pg_b, out_, vocab_tc_ ? out_tf32_ : nullptr,
+                              pgen_, st_);
+    } else {
     if (fork) { cudaEventRecord(fev_[0], st_); cudaStreamWaitEvent(st2_, fev_[0], 0); }
     if (d_.pointer_gen) nl += launch_pgen(d_, R, state_[n], w_.pg_w, w_.pg_b, pgen_, bb_.active, fork ? st2_ : st_);   // :166-167
     // output = [h; ctx] . AttnOutputProjection + b                                (:173)
@@ -557,6 +583,7 @@ int Engine::step_launch(int B, int o, int ps) {
     g.B = w_.out_MT; g.ldb = H + A; g.bias = w_.out_b; g.C = out_; g.ldc = H; g.M = R; g.N = H; g.skinny = 1;
     if (vocab_tc_) { g.C_tf32 = out_tf32_; g.ldc_tf32 = H; }   // the tensor-core pass multiplies the tf32-rounded copy
     nl += launch_gemm_nt(g, st_);
+    }
     if (vocab_tc_) {
       // vocabulary scores on the tensor cores, candidates + softmax statistics in the epilogue   (model.py:236-238)
       int nmb, nr;

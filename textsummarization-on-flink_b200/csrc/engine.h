@@ -10,6 +10,7 @@
 #include "kernels.h"
 #include "text.h"
 #include "vocab_tc.h"
+#include "dec_cell.h"
 
 namespace pgn {
 
@@ -79,6 +80,9 @@ class Engine {
   int* sel_stats_ = nullptr;         // device [2], cumulative
   int32_t* h_selstats_ = nullptr;    // pinned copy, refreshed with every batch's results
   bool enc_persistent_ = true;
+  DecCell dcell_;
+  bool dec_fused_ = false;           // one-launch decoder cell + out projection / p_gen (dec_cell.cu) instead of gather + GEMMs
+  bool dpack_fresh_ = false;         // the decoder cell has written dpack_ for the coming attention pass
   bool attn_fused_ = false;          // one-launch attention (attn_fused.cu) instead of the energy + context pair
   float *att_pctx_ = nullptr, *att_segstat_ = nullptr, *dpack_ = nullptr;
   int* att_cnt_ = nullptr;
