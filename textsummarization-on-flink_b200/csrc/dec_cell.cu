@@ -36,7 +36,7 @@ namespace {
 constexpr int DC_H = 256, DC_E = 128, DC_A = 512, DC_SW = DC_A + 2 * DC_H + DC_E;
 constexpr int DC_RB = 16;                            // decoder rows per cluster
 constexpr int DC_CL = 8;                             // CTAs per cluster
-constexpr int DC_NC = 256, DC_NT = DC_NC + 32;       // compute threads, + one producer warp
+constexpr int DC_NC = 256, DC_NT = DC_NC + 64;       // compute threads, + one producer warp, + one warp for the coverage update
 constexpr int DC_K1 = DC_E + DC_A, DC_K2 = DC_E + DC_H, DC_K3 = 2 * DC_H;      // 640, 384, 512
 constexpr int DC_N1 = DC_E / DC_CL, DC_N2 = 4 * DC_H / DC_CL, DC_N3 = DC_A / DC_CL;   // 16, 128, 64 columns per CTA
 constexpr int DC_STAGE = 16384, DC_STAGES = 4;
@@ -54,7 +54,8 @@ constexpr int OFF_CPREV = OFF_RED + 32768;                       // [16][32]  c 
 constexpr int OFF_XOUT = OFF_CPREV + DC_RB * 32 * 4;             // [16][16]  this CTA's x, source of the exchange
 constexpr int OFF_CHOUT = OFF_XOUT + DC_RB * DC_N1 * 4;          // [16][64]  this CTA's (c | h)
 constexpr int OFF_BAR = OFF_CHOUT + DC_RB * 64 * 4;
-constexpr int DC_SMEM = OFF_BAR + 128;
+constexpr int OFF_ROWOK = OFF_BAR + 128;                         // [16] row exists and its article is still being decoded
+constexpr int DC_SMEM = OFF_ROWOK + 64;
 
 __device__ __forceinline__ uint32_t dc_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void dc_wait(uint64_t* bar, uint32_t parity) {
@@ -164,12 +165,14 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
   const int r0 = (int)(blockIdx.x / DC_CL) * DC_RB;
 
   // a block whose articles have all finished has nothing to do (the same decision in all 8 CTAs)
-  bool any = false;
-  for (int i = 0; i < DC_RB; ++i) {
-    const int r = r0 + i;
-    if (r < a.R && a.active[r / a.K]) any = true;
+  int* rowok = reinterpret_cast<int*>(smem + OFF_ROWOK);
+  int mine = 0;
+  if (tid < DC_RB) {
+    const int r = r0 + tid;
+    mine = (r < a.R && a.active[r / a.K]) ? 1 : 0;
+    rowok[tid] = mine;
   }
-  if (!any) return;
+  if (!__syncthreads_or(mine)) return;
 
   if (tid == 0) {
     for (int s = 0; s < DC_STAGES; ++s) { dc_init(&full[s], 1); dc_init(&empty[s], DC_NC / 32); }
@@ -222,28 +225,47 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
     return;
   }
 
-  // ===== compute warps =====
-  // coverage of the parent + its attention (:114), rows 2c and 2c + 1 of the block
-  if (a.use_cov) {
-    for (int i = 0; i < 2; ++i) {
-      const int r = r0 + 2 * (int)c + i;
-      if (r >= a.R) break;
-      const int art = r / a.K;
-      if (!a.active[art]) continue;
-      const int rp = art * a.K + a.sel_parent[r], len = a.lens[art];
-      const float* co = a.cov_old + (size_t)rp * a.T;
-      const float* ao = a.attn_old + (size_t)rp * a.T;
-      float* cn = a.cov_new + (size_t)r * a.T;
-      if ((a.T & 3) == 0) {
-        for (int t4 = tid; t4 < (len + 3) / 4; t4 += DC_NC) {
-          const float4 x = reinterpret_cast<const float4*>(co)[t4], y = reinterpret_cast<const float4*>(ao)[t4];
-          reinterpret_cast<float4*>(cn)[t4] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+  if (warp == DC_NC / 32 + 1) {
+    // ===== one warp: coverage of the parent + its attention (:114), rows 2c and 2c + 1 of the block =====
+    if (a.use_cov) {
+      for (int i = 0; i < 2; ++i) {
+        const int row = 2 * (int)c + i, r = r0 + row;
+        if (!rowok[row]) continue;
+        const int art = r / a.K;
+        const int rp = art * a.K + a.sel_parent[r], len = a.lens[art];
+        const float* co = a.cov_old + (size_t)rp * a.T;
+        const float* ao = a.attn_old + (size_t)rp * a.T;
+        float* cn = a.cov_new + (size_t)r * a.T;
+        if ((a.T & 3) == 0) {
+          for (int t4 = lane; t4 < (len + 3) / 4; t4 += 128) {        // four float4 pairs in flight per lane
+            float4 x[4], y[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              if (t4 + 32 * q < (len + 3) / 4) { x[q] = reinterpret_cast<const float4*>(co)[t4 + 32 * q]; y[q] = reinterpret_cast<const float4*>(ao)[t4 + 32 * q]; }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              if (t4 + 32 * q < (len + 3) / 4)
+                reinterpret_cast<float4*>(cn)[t4 + 32 * q] = make_float4(x[q].x + y[q].x, x[q].y + y[q].y, x[q].z + y[q].z, x[q].w + y[q].w);
+          }
+        } else {
+          for (int t = lane; t < len; t += 32) cn[t] = co[t] + ao[t];
         }
-      } else {
-        for (int t = tid; t < len; t += DC_NC) cn[t] = co[t] + ao[t];
       }
     }
+    dc_cluster_sync();                                           // (matches the compute warps' final cluster barrier)
+    return;
   }
+
+  // ===== compute warps =====
+  // biases of this thread's outputs, requested now: the epilogues must not wait for an L2 round trip
+  const float bias1 = a.x_b[DC_N1 * c + (tid & 15)];
+  float bias2[2][4], bias3[4];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int g = 0; g < 4; ++g) bias2[i][g] = a.dec_b[g * DC_H + 32 * c + (tid & 31)];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) bias3[i] = a.att_b[DC_N3 * c + (tid & 63)];
   uint32_t n = 0;                                                // weight chunk counter (same sequence as the producer)
   auto chunk_wait = [&]() -> const unsigned char* {
     const uint32_t s = n % DC_STAGES;
@@ -281,10 +303,10 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
       float v = 0.f;
 #pragma unroll
       for (int g = 0; g < 8; ++g) v += red[(g * DC_RB + row) * DC_N1 + cc];
-      v += a.x_b[DC_N1 * c + cc];
+      v += bias1;
       xout[row * DC_N1 + cc] = v;
       const int r = r0 + row;
-      if (r < a.R && a.active[r / a.K]) a.state_new[(size_t)r * DC_SW + DC_A + 2 * DC_H + DC_N1 * c + cc] = v;
+      if (rowok[row]) a.state_new[(size_t)r * DC_SW + DC_A + 2 * DC_H + DC_N1 * c + cc] = v;
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // ordinary stores -> bulk-copy reads
     dc_sync_compute();
@@ -321,15 +343,16 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 #pragma unroll
       for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DC_N2 + col[cc]] = dc_sum2(acc[cc][r]);
     dc_sync_compute();
-    for (int o = tid; o < DC_RB * 32; o += DC_NC) {              // (row, unit): k groups in fixed order, then the cell
-      const int row = o >> 5, u = o & 31;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {                             // (row, unit): k groups in fixed order, then the cell
+      const int o = tid + it * DC_NC, row = o >> 5, u = o & 31;
       float z[4];
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
         float v = 0.f;
 #pragma unroll
         for (int q = 0; q < 4; ++q) v += red[(q * DC_RB + row) * DC_N2 + g * 32 + u];
-        z[g] = v + a.dec_b[g * DC_H + 32 * c + u];
+        z[g] = v + bias2[it][g];
       }
       // LSTMCell: gates i, j, f, o; forget bias 1.0 (model.py:138)
       const float cn = dc_sigmoid(z[2] + 1.0f) * cprev[row * 32 + u] + dc_sigmoid(z[0]) * tanhf(z[1]);
@@ -337,7 +360,7 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
       chout[row * 64 + u] = cn;
       chout[row * 64 + 32 + u] = hn;
       const int r = r0 + row;
-      if (r < a.R && a.active[r / a.K]) {
+      if (rowok[row]) {
         a.state_new[(size_t)r * DC_SW + DC_A + 32 * c + u] = cn;
         a.state_new[(size_t)r * DC_SW + DC_A + DC_H + 32 * c + u] = hn;
       }
@@ -375,14 +398,15 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 #pragma unroll
       for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DC_N3 + col[cc]] = dc_sum2(acc[cc][r]);
     dc_sync_compute();
-    for (int o = tid; o < DC_RB * DC_N3; o += DC_NC) {
-      const int row = o >> 6, cc = o & 63;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int o = tid + it * DC_NC, row = o >> 6, cc = o & 63;
       float v = 0.f;
 #pragma unroll
       for (int q = 0; q < 4; ++q) v += red[(q * DC_RB + row) * DC_N3 + cc];
-      v += a.att_b[DC_N3 * c + cc];
+      v += bias3[it];
       const int r = r0 + row;
-      if (r < a.R && a.active[r / a.K]) {
+      if (rowok[row]) {
         const int f = DC_N3 * c + cc;
         a.dfeat[(size_t)r * DC_A + f] = v;
         if (a.dpack) {                                           // [article][row pair][feature][2], scaled: attn_fused.cu
@@ -403,7 +427,9 @@ constexpr int DO_K = DC_H + DC_A, DO_N = 32, DO_CH = DO_K / 128;           // 76
 constexpr int DO_OFF_A = DC_STAGES * DC_STAGE;                              // [16][768]  h | ctx
 constexpr int DO_OFF_RED = DO_OFF_A + DC_RB * DO_K * 4;                     // [4][16][32]
 constexpr int DO_OFF_BAR = DO_OFF_RED + 4 * DC_RB * DO_N * 4;
-constexpr int DO_SMEM = DO_OFF_BAR + 128;
+constexpr int DO_OFF_ROWOK = DO_OFF_BAR + 128;
+constexpr int DO_SMEM = DO_OFF_ROWOK + 64;
+constexpr int DO_NT = DC_NC + 32;                                           // compute threads + one producer warp
 
 struct DoArgs {
   const int* active;
@@ -414,7 +440,7 @@ struct DoArgs {
   int R, K;
 };
 
-__global__ void __launch_bounds__(DC_NT, 1)
+__global__ void __launch_bounds__(DO_NT, 1)
 dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
   extern __shared__ __align__(1024) unsigned char smem[];
   unsigned char* ring = smem;
@@ -425,18 +451,19 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
   uint64_t* in_bar = empty + DC_STAGES;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int cb = blockIdx.x, r0 = blockIdx.y * DC_RB;
-  bool any = false;
-  for (int i = 0; i < DC_RB; ++i) {
-    const int r = r0 + i;
-    if (r < a.R && a.active[r / a.K]) any = true;
+  int* rowok = reinterpret_cast<int*>(smem + DO_OFF_ROWOK);
+  int mine = 0;
+  if (tid < DC_RB) {
+    const int r = r0 + tid;
+    mine = (r < a.R && a.active[r / a.K]) ? 1 : 0;
+    rowok[tid] = mine;
   }
-  if (!any) return;
   if (tid == 0) {
     for (int s = 0; s < DC_STAGES; ++s) { dc_init(&full[s], 1); dc_init(&empty[s], DC_NC / 32); }
     dc_init(in_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
+  if (!__syncthreads_or(mine)) return;
   if (warp == DC_NC / 32) {
     if (lane < DC_RB) {
       const int r = min(r0 + lane, a.R - 1);
@@ -458,6 +485,7 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
   }
   const int kg = warp & 3, rh = warp >> 2;
   const int col[1] = {lane};
+  const float bias = a.out_b[DO_N * cb + lane];
   unsigned long long acc[1][8];
 #pragma unroll
   for (int r = 0; r < 8; ++r) acc[0][r] = 0ull;
@@ -479,8 +507,8 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
     float v = 0.f;
 #pragma unroll
     for (int q = 0; q < 4; ++q) v += red[(q * DC_RB + row) * DO_N + cc];
-    v += a.out_b[DO_N * cb + cc];
-    if (r < a.R && a.active[r / a.K]) {
+    v += bias;
+    if (rowok[row]) {
       a.out[(size_t)r * DC_H + DO_N * cb + cc] = v;
       if (a.out_tf32) {
         uint32_t t;
@@ -492,7 +520,7 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
   if (cb == 0 && a.pgen) {                                       // p_gen: warp w takes rows 2w, 2w + 1
     for (int i = 0; i < 2; ++i) {
       const int r = r0 + 2 * warp + i;
-      if (r >= a.R || !a.active[r / a.K]) continue;
+      if (!rowok[2 * warp + i]) continue;
       const float4* s4 = reinterpret_cast<const float4*>(a.state + (size_t)r * DC_SW);
       const float4* w4 = reinterpret_cast<const float4*>(a.pg_w);
       float4 sv[DC_SW / 128], wv[DC_SW / 128];
@@ -596,7 +624,7 @@ int DecCell::launch_out(const Dims& d, int B, const int* active, const float* st
   a.active = active; a.state = state; a.out_b = out_b; a.pg_w = pg_w; a.pg_b = pg_b; a.out = out; a.out_tf32 = out_tf32;
   a.pgen = d.pointer_gen ? pgen : nullptr; a.R = B * d.K; a.K = d.K;
   dim3 grid(DC_H / DO_N, (a.R + DC_RB - 1) / DC_RB);
-  dec_out_kernel<<<grid, DC_NT, DO_SMEM, st>>>(tmWo, a);
+  dec_out_kernel<<<grid, DO_NT, DO_SMEM, st>>>(tmWo, a);
   return 1;
 }
 
