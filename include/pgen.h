@@ -104,6 +104,12 @@ PGEN_API const char* pgen_last_error(pgen_t* h);
 /* Replaces the end of BeamSearchDecoder.decode when the stream is exhausted (decode.py:139-142). */
 PGEN_API void pgen_destroy(pgen_t* h);
 
+/* Number of CUDA devices this process can use (0: none, the library then serves nothing).  The operator maps subtask
+ * index -> device ordinal = index % pgen_device_count(): one GPU per Flink subtask, worker_num parallel subtasks
+ * (src/main/java/org/apache/flink/table/ml/lib/tensorflow/param/HasClusterConfig.java:20-24).  No counterpart in
+ * the reference, which runs on CPU (model.py:313). */
+PGEN_API int pgen_device_count(void);
+
 /* Parsed hyper-parameters (run_summarization.py:48-88 names).  Returns the value of an integer or
  * boolean flag after the decode-mode overrides (batch_size := beam_size, :312-313), or -1. */
 PGEN_API int64_t pgen_flag_int(pgen_t* h, const char* name);
@@ -129,7 +135,10 @@ PGEN_API int pgen_decode_ids(pgen_t* h, int n_articles, const int32_t* enc_ids, 
 
 /* The same path split at the PCIe boundary, so that a harness can time the device-resident part
  * alone: upload (H2D of ids), run (encoder + beam search, asynchronous on the handle's stream),
- * sync, download (D2H of the best hypotheses).  n_articles <= articles_per_batch. */
+ * sync, download (D2H of the best hypotheses).  n_articles <= articles_per_batch.
+ * These calls (and pgen_decode_ids, pgen_attention, pgen_debug_*) drive the engine of the slot chosen with
+ * pgen_stage_slot directly; while a batch of pgen_submit rows is in flight on that slot they fail with
+ * PGEN_ERR_STATE -- pgen_poll(flush) first, or keep the row API and the stage API on different handles. */
 PGEN_API int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
                       const int32_t* enc_lens, const int32_t* n_oovs);
 PGEN_API int pgen_stage_run(pgen_t* h);
@@ -196,6 +205,9 @@ PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, 
  *   vocab=tc|simt        tcgen05 tf32 vocabulary pass + exact re-scoring, or the all-fp32 dense path
  *   features=tc|simt     W_h.h_i by the 3xTF32 tcgen05 GEMM, or the fp32 SIMT GEMM
  *   encoder=persistent|steps   one cluster kernel for the whole recurrence, or one launch per time step
+ *   decoder=fused|split  one-launch decoder cell + fused out projection / p_gen (csrc/dec_cell.cu), or gather + four
+ *                        split-K GEMM launches + point-wise kernels
+ *   attention=fused|split   one-launch attention (csrc/attn_fused.cu), or the energy + context kernel pair
  *   graph=1|0, graph_steps=N   replay N (even) decode steps per CUDA graph, or launch every kernel
  *   check_every=N        poll the device every N steps after min_dec_steps and stop early when every article is done
  *   vocab_guard=auto|widen|dense|off   exactness guard of the tensor-core candidate selection: auto (default), or force
@@ -203,7 +215,7 @@ PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, 
  *   profile=1|0          per-step CUDA events for pgen_stats (plain launches)
  *   measure=N            replay the attention pair and the tensor-core pass of the last decoded batch N times each
  *                        from a graph between two events; sums land in ms_attention / ms_vocab, prof_steps = N
- * No counterpart in the reference. */
+ * Fails with PGEN_ERR_STATE while pgen_submit rows are in flight.  No counterpart in the reference. */
 PGEN_API int pgen_set_option(pgen_t* h, const char* key_value);
 
 #ifdef __cplusplus

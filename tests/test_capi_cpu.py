@@ -47,3 +47,11 @@ def test_no_cpu_fallback(tmp_path):
     with pytest.raises(native.PgenError) as e:
         native.Decoder("p --mode=decode --vocab_path=%s --log_root=%s --exp_name=x" % (v, tmp_path))
     assert e.value.code == 3 and "no CPU fallback" in str(e.value)
+
+
+def test_device_count_without_a_gpu():
+    """pgen_device_count() is what PgenNative.deviceCount() binds: 0 when the process sees no CUDA device."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    assert native.device_count() == 0

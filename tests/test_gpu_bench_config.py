@@ -1,0 +1,86 @@
+"""The configurations that are BENCHMARKED, against the oracle (beam_search.py:82-168 end to end).
+
+bench.py times 64 full-size articles per device batch, four batches in flight on four streams, CUDA-graph replay,
+rows in and out through pgen_submit / pgen_poll.  That exact shape -- not a smaller stand-in -- is decoded here and
+every row is compared with the oracle's row; config 4 of BASELINE.json (beam 8, 120 steps, 200 OOVs per article)
+likewise with 16 articles in one batch.  Near-tie accounting as in test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import pgen_oracle as O
+from test_gpu_parity import _has_near_tie, check_against_oracle
+from textsummarization_on_flink_b200 import native, synth, weights_io
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_row(W, vocab, hps, article):
+    """(summary, trace, tokens) of one article text, the way decode.py:95-129 + :159-185 produce the row."""
+    ex = O.make_example(article, vocab, int(hps["max_enc_steps"]))
+    trace = []
+    toks, lps, avg = O.decode_ids(W, hps, ex.enc_input, ex.enc_input_extend_vocab, len(ex.article_oovs), mode="dedup",
+                                  trace=trace)
+    words = O.cut_at_stop(O.outputids2words(toks, vocab, ex.article_oovs))
+    return O.format_summary(words), trace, toks
+
+
+def test_benchmark_shape_rows_match_oracle(model_dir):
+    """64 articles = ONE device batch, --slots=4, graphs on, submit/poll: every row against the oracle.  Three
+    batches are pushed so that the second and third run as graph replays on other slots while the first decodes."""
+    n_batches, B = 3, 64
+    flags = synth.hyperparams_string(model_dir, extra="--articles_per_batch=%d --slots=4 --flush_ms=-1" % B)
+    hps = O.parse_hyperparams(flags)
+    W = weights_io.load_weights(model_dir["weights"])
+    vocab = O.Vocab(model_dir["vocab_path"], 50000)
+    arts = synth.make_article_ids(n_batches * B, seed=2024)
+    texts = [synth.ids_to_article(ext, 50000, salt=i) for i, (_, ext, _) in enumerate(arts)]
+    got = []
+    with native.Decoder(flags) as dec:
+        for i, t in enumerate(texts):
+            dec.submit(b"u%d" % i, t, b"ref %d" % i)
+            got += dec.poll()
+        got += dec.poll(flush=True)
+        st = dec.stats()
+    assert st["batches"] == n_batches and [r[0] for r in got] == [b"u%d" % i for i in range(len(texts))]
+    # the oracle on the middle batch in full (a graph replay on slot 1) and a sample of the other two
+    check = list(range(B, 2 * B)) + list(range(0, B, 8)) + list(range(2 * B, 3 * B, 8))
+    near = 0
+    for i in check:
+        summary, trace, toks = oracle_row(W, vocab, hps, texts[i])
+        assert got[i][1] == texts[i] and got[i][3] == b"ref %d" % i
+        if got[i][2] != summary:
+            gw, rw = got[i][2].split(), summary.split()
+            first = next((j for j, (x, y) in enumerate(zip(gw, rw)) if x != y), min(len(gw), len(rw)))
+            assert _has_near_tie(trace, min(first, len(trace) - 1)), "row %d differs at word %d with no near-tie" % (i, first)
+            near += 1
+    assert near <= max(1, len(check) // 10), "%d of %d rows diverged at near-ties" % (near, len(check))
+
+
+def test_config4_sixteen_articles_one_batch(model_dir):
+    """Config 4 of BASELINE.json in one device batch of 16 articles (128 decoder rows): beam 8, max_dec_steps 120,
+    exactly 200 distinct OOV words per article."""
+    flags = synth.hyperparams_string(model_dir, beam_size=8, max_dec_steps=120, extra="--articles_per_batch=16 --slots=1")
+    hps = O.parse_hyperparams(flags)
+    W = weights_io.load_weights(model_dir["weights"])
+    arts = synth.make_article_ids(16, seed=4004, fixed_oovs=200, full_len_only=True)
+    assert all(k == 200 for _, _, k in arts)
+    with native.Decoder(flags) as dec:
+        check_against_oracle(dec, W, hps, arts, max_near_tie_frac=0.1)
+
+
+def test_articles_do_not_depend_on_the_batch_at_full_size(model_dir):
+    """An article decodes to the same bits alone, among 8 and among 64 (different tile plans of the tensor-core pass,
+    different numbers of clusters / persistent CTAs in the decoder cell and the attention kernel), beam 4 and 8."""
+    for beam, steps in ((4, 40), (8, 30)):
+        arts = synth.make_article_ids(64, seed=77 + beam)
+        outs = {}
+        for B in (64, 8, 1):
+            flags = synth.hyperparams_string(model_dir, beam_size=beam, max_dec_steps=steps, min_dec_steps=10,
+                                             extra="--articles_per_batch=%d --slots=1" % B)
+            with native.Decoder(flags) as dec:
+                sub = arts[:B] if B > 1 else arts[3:4]
+                outs[B] = dec.decode_ids(*native.pack_articles(sub, dec.max_enc_steps))
+        for B, rows in ((8, range(8)), (1, [3])):
+            for j, b in enumerate(rows):
+                for x, y in zip(outs[64], outs[B]):
+                    assert np.array_equal(x[b], y[j]), "beam %d article %d: batch of 64 vs batch of %d" % (beam, b, B)

@@ -57,27 +57,36 @@ static int fail(pgen_t* h, int code, const std::string& msg) {
   return code;
 }
 
-// finish the oldest in-flight batch: wait for it, detokenise, move its rows to `done`
+// finish the oldest in-flight batch: wait for it, detokenise, move its rows to `done`.  The batch leaves the
+// in-flight list only once its results are on the host, so a failed download can be retried and loses no row; a row
+// whose token ids cannot be mapped back to words is emitted with an empty summary and named in the error, the rest
+// of its batch is emitted normally.
 static int collect_oldest(pgen_t* h) {
-  InFlight f = std::move(h->inflight.front());
-  h->inflight.pop_front();
+  InFlight& f = h->inflight.front();
   Engine& e = *h->engs[f.slot];
   const size_t n = f.rows.size();
   const int S = (int)h->hp.max_dec_steps;
   h->b_tok.resize(n * S); h->b_len.resize(n); h->b_lp.resize(n * S); h->b_avg.resize(n);
-  std::string err = e.download(h->b_tok.data(), h->b_len.data(), h->b_lp.data(), h->b_avg.data());
+  std::string err = e.download((int)n, h->b_tok.data(), h->b_len.data(), h->b_lp.data(), h->b_avg.data());
   if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);
   auto t0 = std::chrono::steady_clock::now();
+  std::string bad;
   for (size_t b = 0; b < n; ++b) {
     PendingRow& p = f.rows[b];
     DoneRow d;
-    if (!summary_from_ids(h->vocab, p.enc.oovs, &h->b_tok[b * S], h->b_len[b], &d.summary))
-      return fail(h, PGEN_ERR_STATE, "decoder produced a token id outside the article's extended vocabulary");
+    if (!summary_from_ids(h->vocab, p.enc.oovs, &h->b_tok[b * S], h->b_len[b], &d.summary)) {
+      d.summary.clear();
+      bad += (bad.empty() ? "" : ", ") + p.uuid;
+    }
     h->tokens_out += h->b_len[b];
     d.uuid = std::move(p.uuid); d.article = std::move(p.article); d.reference = std::move(p.reference);
     h->done.push_back(std::move(d));
   }
+  h->inflight.pop_front();
   h->ms_host_text += ms_since(t0);
+  if (!bad.empty())
+    return fail(h, PGEN_ERR_STATE, "decoder produced a token id outside the extended vocabulary of row(s) " + bad +
+                                   " (emitted with an empty summary)");
   return PGEN_OK;
 }
 
@@ -93,25 +102,38 @@ static int launch_pending(pgen_t* h, size_t n) {
   }
   const int T = (int)h->hp.max_enc_steps;
   h->b_ids.assign(n * T, 0); h->b_ext.assign(n * T, 0); h->b_lens.assign(n, 0); h->b_noov.assign(n, 0);
-  InFlight f;
-  f.slot = slot;
-  f.rows.reserve(n);
   for (size_t b = 0; b < n; ++b) {
-    const EncodedArticle& e = h->pending.front().enc;
+    const EncodedArticle& e = h->pending[b].enc;
     h->b_lens[b] = (int)e.enc_ids.size();
     h->b_noov[b] = (int)e.oovs.size();
     memcpy(&h->b_ids[b * T], e.enc_ids.data(), e.enc_ids.size() * 4);
     memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
-    f.rows.push_back(std::move(h->pending.front()));
-    h->pending.pop_front();
   }
   Engine& e = *h->engs[slot];
   std::string err = e.upload((int)n, h->b_ids.data(), h->b_ext.data(), T, h->b_lens.data(), h->b_noov.data());
   if (err.empty()) err = e.run();
-  if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);
+  if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);        // the rows stay in `pending`: nothing is lost
+  InFlight f;
+  f.slot = slot;
+  f.rows.reserve(n);
+  for (size_t b = 0; b < n; ++b) {
+    f.rows.push_back(std::move(h->pending.front()));
+    h->pending.pop_front();
+  }
   h->inflight.push_back(std::move(f));
   h->next_slot = (slot + 1) % (int)h->engs.size();
   return PGEN_OK;
+}
+
+// The stage / tensor-level entry points drive one slot's engine directly: refused while a batch submitted through
+// pgen_submit is in flight on that slot (its buffers would be overwritten under it).
+static bool slot_busy(pgen_t* h) {
+  for (auto& f : h->inflight) if (f.slot == h->stage_slot) return true;
+  return false;
+}
+static int busy_error(pgen_t* h, const char* what) {
+  return fail(h, PGEN_ERR_STATE, std::string(what) + ": slot " + std::to_string(h->stage_slot) +
+                                 " holds a batch of pgen_submit rows in flight; pgen_poll(flush) first or choose another slot");
 }
 
 pgn::Engine* pgen_internal_engine(pgen_t* h) { return &h->eng(); }
@@ -147,6 +169,12 @@ int pgen_create(const char* hyperparams, int device_ordinal, pgen_t** out) {
 }
 
 void pgen_destroy(pgen_t* h) { delete h; }
+
+int pgen_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
 
 const char* pgen_last_error(pgen_t* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
@@ -259,11 +287,13 @@ int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out,
 int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
                       const int32_t* enc_lens, const int32_t* n_oovs) {
   if (!h || n_articles < 0 || (n_articles && (!enc_ids || !enc_ext_ids || !enc_lens))) return h ? fail(h, PGEN_ERR_ARG, "bad arguments") : PGEN_ERR_ARG;
+  if (slot_busy(h)) return busy_error(h, "pgen_stage_upload");
   std::string err = h->eng().upload(n_articles, enc_ids, enc_ext_ids, ld, enc_lens, n_oovs);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_ARG, err);
 }
 int pgen_stage_run(pgen_t* h) {
   if (!h) return PGEN_ERR_ARG;
+  if (slot_busy(h)) return busy_error(h, "pgen_stage_run");
   std::string err = h->eng().run();
   return err.empty() ? PGEN_OK : fail(h, err.find("before") != std::string::npos ? PGEN_ERR_STATE : PGEN_ERR_CUDA, err);
 }
@@ -274,7 +304,8 @@ int pgen_stage_sync(pgen_t* h) {
 }
 int pgen_stage_download(pgen_t* h, int32_t* out_tokens, int32_t* out_lens, float* out_logprobs, double* out_avg) {
   if (!h) return PGEN_ERR_ARG;
-  std::string err = h->eng().download(out_tokens, out_lens, out_logprobs, out_avg);
+  if (slot_busy(h)) return busy_error(h, "pgen_stage_download");
+  std::string err = h->eng().download(-1, out_tokens, out_lens, out_logprobs, out_avg);
   return err.empty() ? PGEN_OK : fail(h, err.find("before") != std::string::npos ? PGEN_ERR_STATE : PGEN_ERR_CUDA, err);
 }
 void* pgen_stream(pgen_t* h) { return h ? (void*)h->eng().stream() : nullptr; }
@@ -312,6 +343,7 @@ int pgen_attention(pgen_t* h, int n_articles, const float* enc_feat, const float
   if (n_articles < 0 || (n_articles && (!enc_feat || !enc_states || !lens || !dfeat || !attn || !ctx)))
     return fail(h, PGEN_ERR_ARG, "pgen_attention: NULL device pointer");
   if (n_articles && h->hp.coverage && !cov) return fail(h, PGEN_ERR_ARG, "pgen_attention: coverage=1 needs cov");
+  if (slot_busy(h)) return busy_error(h, "pgen_attention");
   std::string err = h->eng().attention_op(n_articles, enc_feat, enc_states, lens, dfeat, cov, attn, ctx);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
 }
@@ -365,6 +397,7 @@ int pgen_submit_example(pgen_t* h, const void* example, size_t len) {
 
 int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* logits_dev, int use_tc) {
   if (!h || !out_dev || !logits_dev) return PGEN_ERR_ARG;
+  if (slot_busy(h)) return busy_error(h, "pgen_debug_vocab_logits");
   std::string err = h->eng().vocab_logits_op(rows, out_dev, logits_dev, use_tc);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
 }
@@ -377,6 +410,8 @@ int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, s
 
 int pgen_set_option(pgen_t* h, const char* key_value) {
   if (!h || !key_value) return PGEN_ERR_ARG;
+  if (!h->inflight.empty())
+    return fail(h, PGEN_ERR_STATE, "pgen_set_option: batches of pgen_submit rows are in flight; pgen_poll(flush) first");
   for (auto& e : h->engs) {
     std::string err = e->set_option(key_value);
     if (!err.empty()) return fail(h, PGEN_ERR_ARG, err);

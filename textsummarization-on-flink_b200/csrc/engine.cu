@@ -250,7 +250,8 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     if (share) proj_wT_tf32_ = share->proj_wT_tf32_;
     else DALLOC(proj_wT_tf32_, float, V * H);
     DALLOC(out_tf32_, float, Rpad * H);
-    DALLOC(part_m_, float, (size_t)2 * n_sms_ * R); DALLOC(part_s_, float, (size_t)2 * n_sms_ * R);
+    const size_t n_part = 2 * ((V + 255) / 256);                   // one (max, sum) per row and 128 words
+    DALLOC(part_m_, float, n_part * R); DALLOC(part_s_, float, n_part * R);
     gstride_ = (int)((((V + 31) / 32) + 7) & ~(size_t)7);      // float4 per row, rows 128-byte aligned
     DALLOC(gmax_, float4, (size_t)gstride_ * Rpad);
     sstride_ = (int)((((V + 255) / 256) * 2 + 31) & ~(size_t)31);
@@ -594,7 +595,7 @@ int Engine::step_launch(int B, int o, int ps) {
       ma.artl = artl_; ma.pgen = pgen_; ma.attn = attn_[n]; ma.uniq_ids = uniq_;
       ma.uniq_cnt = ucnt_; ma.pos_start = pstart_; ma.pos_list = plist_; ma.active = bb_.active; ma.lens = lens_;
       ma.topk_ids = topk_ids_; ma.topk_logp = topk_logp_; ma.K = K; ma.K2 = d_.K2; ma.G = vtc_.G; ma.NC = vtc_.G * 8; ma.H = H;
-      ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = 2 * nr; ma.pointer_gen = d_.pointer_gen;
+      ma.V = d_.V; ma.T = T; ma.R = R; ma.n_parts = vtc_.n_parts(); ma.pointer_gen = d_.pointer_gen;
       ma.wnorm_max = w_.proj_wnorm_max; ma.guard = vocab_guard_; ma.sel_stats = sel_stats_;
       if (profile_) cudaEventRecord(pev_[5 * ps + 2], st_);
       if (fork) { cudaEventRecord(fev_[1], st_); cudaStreamWaitEvent(st2_, fev_[1], 0); }      // out_ is complete
@@ -762,8 +763,10 @@ std::string Engine::sync() {
   return check("decode");
 }
 
-std::string Engine::download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg) {
+std::string Engine::download(int expect_rows, int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg) {
   if (!ran_) return "pgen_stage_download before pgen_stage_run";
+  if (expect_rows >= 0 && expect_rows != nB_)
+    return "the slot holds a batch of " + std::to_string(nB_) + " articles, the caller expects " + std::to_string(expect_rows);
   std::string err = sync();
   if (!err.empty()) return err;
   const size_t n = nB_, S = d_.S;

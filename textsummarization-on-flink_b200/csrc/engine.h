@@ -42,7 +42,8 @@ class Engine {
   std::string run();
   std::string sync();
   bool done();                       // the last run() (including its D2H copies) has finished
-  std::string download(int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg);
+  // expect_rows >= 0: refuse unless that many articles were staged (the caller sized its buffers for them)
+  std::string download(int expect_rows, int32_t* out_tokens, int32_t* out_lens, float* out_logp, double* out_avg);
   std::string fetch(const std::string& name, void* out, size_t cap_bytes, size_t* n);
   std::string set_option(const std::string& kv);
   std::string vocab_logits_op(int rows, const float* out_dev, float* logits_dev, int use_tc);

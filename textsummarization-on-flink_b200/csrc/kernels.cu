@@ -15,8 +15,6 @@
 
 namespace pgn {
 
-// Function attributes are per device: a process may hold handles on several GPUs (one per operator subtask).
-static inline int cur_dev() { int dev = 0; cudaGetDevice(&dev); return dev & 63; }
 
 // ======================================================================================
 // Generic fp32 GEMM  C = act([A0|A1] . B^T + bias)
@@ -501,13 +499,8 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
 template <int AG>
 static int pe_launch(const Dims& d, int B, const int* lens, const float* zx, const int* ids, const float* kh, float* h_fin,
                      float* c_fin, float* enc_states, cudaStream_t st) {
-  static bool set[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!set[dev & 63]) {
-    cudaFuncSetAttribute(enc_lstm_persistent_kernel<AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PeCfg<AG>::SMEM);
-    set[dev & 63] = true;
-  }
+  static PerDeviceOnce once;
+  once.ensure(1, [] { cudaFuncSetAttribute(enc_lstm_persistent_kernel<AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PeCfg<AG>::SMEM); });
   dim3 grid(8, 2, (B + AG - 1) / AG);
   enc_lstm_persistent_kernel<AG><<<grid, PE_THREADS, PeCfg<AG>::SMEM, st>>>(d.T, B, lens, zx, ids, d.V, kh, h_fin, c_fin, enc_states);
   return 1;
@@ -516,6 +509,8 @@ static int pe_launch(const Dims& d, int B, const int* lens, const float* zx, con
 // How many clusters of 8 CTAs with this kernel's footprint run at once on the current device.
 static int pe_max_clusters() {
   static int cached[64] = {0};
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lk(mu);
   int dev = 0;
   cudaGetDevice(&dev);
   if (cached[dev & 63] > 0) return cached[dev & 63];
@@ -840,9 +835,8 @@ int launch_attn_energy(const Dims& d, int B, int rpa, const int* lens, const int
     else attn_energy_kernel<8, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   } else {
     const size_t smem = (size_t)(16 * d.A + 2 * d.A) * sizeof(float);
-    static bool set[64] = {false};
-    const int dev = cur_dev();
-    if (!set[dev]) { cudaFuncSetAttribute(attn_energy_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); set[dev] = true; }
+    static PerDeviceOnce once;
+    once.ensure(1, [] { cudaFuncSetAttribute(attn_energy_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); });
     attn_energy_kernel<16, false><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_feat, dfeat, cov, v, w_c, e);
   }
   return 1;
@@ -954,12 +948,9 @@ template <int KMAX>
 static void launch_ctx_t(const Dims& d, int B, int rpa, const int* lens, const int* active,
                          const float* enc_states, const float* e, float* attn, float* state, cudaStream_t st) {
   const size_t smem = (size_t)(KMAX * d.T + 8 * KMAX * CTX_COLS) * sizeof(float);
-  static bool set[64] = {false};
-  const int dev = cur_dev();
-  if (!set[dev] && smem > 48 * 1024) {
-    cudaFuncSetAttribute(attn_context_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    set[dev] = true;
-  }
+  static PerDeviceOnce once;
+  if (smem > 48 * 1024)
+    once.ensure(smem, [&] { cudaFuncSetAttribute(attn_context_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); });
   dim3 grid(d.A / CTX_COLS, B);
   attn_context_kernel<KMAX><<<grid, 256, smem, st>>>(d, rpa, lens, active, enc_states, e, attn, state);
 }
@@ -1162,12 +1153,9 @@ final_topk_kernel(Dims d, FinalArgs a) {
 template <int K2MAX>
 static void launch_final_t(const Dims& d, int B, const FinalArgs& a, cudaStream_t st) {
   const size_t smem = (size_t)((d.V + 31) / 32) * 4 + (size_t)256 * K2MAX * 8 + 8 * 12 + 16;
-  static size_t set[64] = {0};
-  const int dev = cur_dev();
-  if (smem > 48 * 1024 && smem > set[dev]) {
-    cudaFuncSetAttribute(final_topk_kernel<K2MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    set[dev] = smem;
-  }
+  static PerDeviceOnce once;
+  if (smem > 48 * 1024)
+    once.ensure(smem, [&] { cudaFuncSetAttribute(final_topk_kernel<K2MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); });
   final_topk_kernel<K2MAX><<<B * d.K, 256, smem, st>>>(d, a);
 }
 

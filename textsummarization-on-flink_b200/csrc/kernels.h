@@ -3,8 +3,22 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <mutex>
 
 namespace pgn {
+
+// Function attributes (dynamic shared memory limits) are per device and per process: handles on several GPUs, driven
+// from several threads of one process (Flink subtasks of one TaskManager), set them exactly once each.
+struct PerDeviceOnce {
+  std::mutex mu;
+  size_t done[64] = {};
+  template <class F> void ensure(size_t need, F&& set) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (done[dev & 63] < need) { set(); done[dev & 63] = need; }
+  }
+};
 
 // C[M,N] = act( [A0 | A1][M, k0+k1] . B[N, k0+k1]^T + bias[N] ), fp32 SIMT tiles.
 // A0 rows may be gathered through gather0 (row m reads A0 + gather0[m]*lda0).

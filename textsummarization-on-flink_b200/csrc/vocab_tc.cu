@@ -23,6 +23,7 @@
 #include <cstdint>
 #include <string>
 
+#include "kernels.h"
 #include "vocab_tc.h"
 
 namespace pgn {
@@ -253,12 +254,14 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int row = mb * BM + q * 32 + lane;
     float* bsm = bias_s + ew * 128;                            // warp-private bias staging
     const uint32_t t_empty_l0 = mapa_rank(&t_empty[0], 0), t_empty_l1 = mapa_rank(&t_empty[1], 0);
-    float m_run = -FLT_MAX;
-    uint64_t s01 = pack2(0.f, 0.f), s23 = s01;                 // four partial sums of exp2(x - m_run)
     const uint64_t kL2 = pack2(kLog2e, kLog2e);
     uint32_t tcount = 0;
     for (int tile = range; tile < n_tiles; tile += n_ranges, ++tcount) {
       const int acc = tcount & 1;
+      // (max, sum exp2) are kept per HALF TILE, not per CTA: the partition of the vocabulary over CTAs depends on
+      // the number of rows in the batch, and a row's softmax denominator must not
+      float m_run = -FLT_MAX;
+      uint64_t s01 = pack2(0.f, 0.f), s23 = s01;               // four partial sums of exp2(x - m_run)
       const int nb = tile * BN + half * 128;
       __syncwarp();
 #pragma unroll
@@ -318,17 +321,17 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           s23 = add2(s23, pack2(ex2_ftz(y2), ex2_ftz(y3)));
         }
       }
-      if (row < R) smax[(size_t)row * sstride + (nb >> 7)] = tmx;
+      if (row < R) {
+        smax[(size_t)row * sstride + (nb >> 7)] = tmx;
+        const size_t pi = (size_t)(tile * 2 + half) * R + row;
+        part_m[pi] = m_run;
+        float s0, s1, s2, s3;
+        unpack2(s01, s0, s1); unpack2(s23, s2, s3);
+        part_s[pi] = (s0 + s1) + (s2 + s3);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(acc ? t_empty_l1 : t_empty_l0);      // one arrival per epilogue warp of either CTA
-    }
-    if (row < R) {
-      const size_t pi = (size_t)(range * 2 + half) * R + row;
-      part_m[pi] = m_run;
-      float s0, s1, s2, s3;
-      unpack2(s01, s0, s1); unpack2(s23, s2, s3);
-      part_s[pi] = (s0 + s1) + (s2 + s3);
     }
   }
   tc_fence_before();
@@ -1079,6 +1082,8 @@ std::string VocabTC::init(const float* wT_tf32, int V_, int H_, const float* out
   return "";
 }
 
+int VocabTC::n_parts() const { return 2 * n_tiles; }
+
 void VocabTC::plan(int R, int* n_mpairs, int* n_ranges) const {
   *n_mpairs = (R + 2 * BM - 1) / (2 * BM);
   int nr = (sms / 2) / *n_mpairs;
@@ -1119,13 +1124,9 @@ size_t VocabTC::final_smem(int T, int n_parts) const {
 
 int VocabTC::launch_final(const MergeArgs& a, cudaStream_t st) const {
   const size_t smem = final_smem(a.T, a.n_parts);
-  static size_t set[64] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (smem > 48 * 1024 && smem > set[dev & 63]) {
-    cudaFuncSetAttribute(vocab_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    set[dev & 63] = smem;
-  }
+  static PerDeviceOnce once;
+  if (smem > 48 * 1024)
+    once.ensure(smem, [&] { cudaFuncSetAttribute(vocab_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); });
   vocab_final_kernel<<<a.R, SEL_THREADS, smem, st>>>(a);
   return 1;
 }

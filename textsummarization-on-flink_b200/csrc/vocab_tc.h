@@ -12,7 +12,7 @@ struct MergeArgs {
   const float* out;        // [R, H] unrounded decoder outputs
   const float* wT;         // [V, H] unrounded output_projection/w (transposed)
   const float* bias;       // [V]
-  const float* part_m; const float* part_s;      // [n_parts, R]   log2 domain (max, sum exp2) of the tf32 logits
+  const float* part_m; const float* part_s;      // [n_parts, R]   log2 domain (max, sum exp2) of the tf32 logits, per 128 words
   const float4* gmax; int gstride;               // [R, gstride] per row: maxima of the 4 groups of 8 words of each 32-word chunk
   const float* smax; int sstride;                // [R, sstride] per row: maxima of the 128-word supergroups
   float* artl;                                   // [R, T] exact logits of the article's distinct words
@@ -32,6 +32,7 @@ class VocabTC {
   // addresses stay fixed (they are baked into the TMA descriptors).
   std::string init(const float* wT_tf32, int V, int H, const float* out_tf32, int Rcap, int K2, int n_sms);
   void plan(int R, int* n_mpairs, int* n_ranges) const;
+  int n_parts() const;            // (max, sum) statistics per row: one per half tile of 128 words, whatever the grid
   int launch(int R, const float* bias, float* part_m, float* part_s, float4* gmax, int gstride, float* smax, int sstride, float* logits_dbg,
              cudaStream_t st) const;
   int launch_rescore(const MergeArgs& a, int B, cudaStream_t st) const;     // article words

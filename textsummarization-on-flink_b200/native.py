@@ -16,7 +16,7 @@ EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_st
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
            "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
            "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot",
-           "pgen_example_parse", "pgen_example_write", "pgen_submit_example"]
+           "pgen_example_parse", "pgen_example_write", "pgen_submit_example", "pgen_device_count"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -81,6 +81,8 @@ def lib() -> C.CDLL:
         L.pgen_example_write.argtypes = [C.POINTER(Row), C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_submit_example.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
         L.pgen_stream.restype = C.c_void_p
+        L.pgen_device_count.argtypes = []
+        L.pgen_device_count.restype = C.c_int
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
         L.pgen_attention.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
@@ -88,6 +90,11 @@ def lib() -> C.CDLL:
         L.pgen_attention_static.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
         _lib = L
     return _lib
+
+
+def device_count() -> int:
+    """CUDA devices visible to the library (0 without a GPU)."""
+    return int(lib().pgen_device_count())
 
 
 def _p(a: np.ndarray, t):
