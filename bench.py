@@ -7,17 +7,19 @@ One "step" = one pass of the hot path (encoder + beam search) over one device ba
 CNN/DailyMail-shaped articles (BASELINE.json configs[2]).  Prints ONE JSON line on rank 0.
 
   value     articles/s with the batch's ids already in HBM when each timed interval starts
-            (CUDA events on the library's stream around pgen_stage_run, summed over the K steps)
+            (CUDA events on the library's streams around pgen_stage_run, max over ranks)
   e2e       the same metric through the operator-facing C ABI (pgen_submit / pgen_poll with article
             byte strings in host memory): tokenisation, H2D, decode, D2H and detokenisation inside
-            the timed region
-  roofline  the dominant kernel (pair) of the step, timed live: after a profiled extra batch the library replays the
-            attention pair and the tensor-core pass 50 times each from a graph between two CUDA events on its
-            stream (option measure=50); the per-step interval of the profiled batch is reported beside it
-  cpu_baseline  the oracle in reference-faithful ("literal") mode on the host cores, bounded sample
+            the timed region; `verified_rows` of those rows are then compared with the oracle
+  roofline  the dominant kernel of the decode step (the attention pass), timed live: its interval in every step of
+            one extra batch run with plain launches and CUDA events inside the library (option profile=1), against the
+            measured HBM peak; `roofline_other` is the tensor-core vocabulary pass against a TF32 dense peak measured
+            here with the same recipe MEASURED_PEAKS.json used for bf16
+  config2 / config4   BASELINE.json configs[1] (encoder only) and configs[3] (beam 8, 120 steps, 200 OOVs) at this N
+  cpu_baseline  the reference's algorithm restated for the CPU (PyTorch fp32, every host thread; TensorFlow 1.x,
+            which the reference needs, cannot be installed here: DESIGN.md), bounded sample, rank 0 only
 
---impl reference times that CPU restatement alone (TensorFlow 1.x, which the reference needs, is not
-installable here: see DESIGN.md), on rank 0 only.
+--impl reference times that CPU restatement alone, on rank 0's host cores whatever N is.
 """
 from __future__ import annotations
 
@@ -124,29 +126,36 @@ def ensure_model(rank: int, barrier) -> dict:
 
 def use_all_host_threads() -> int:
     """torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core."""
-    n = os.cpu_count() or 1
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pgen_oracle_torch as OT
+    n = OT.use_all_threads()
     try:
         from threadpoolctl import threadpool_limits
-        threadpool_limits(limits=n)
+        threadpool_limits(limits=os.cpu_count() or 1)
     except Exception:
         pass
     return n
 
 
-def cpu_reference_sample(paths: dict, n_articles: int, seed: int) -> tuple:
-    """The oracle in reference-faithful mode (K replicated rows, W_h.h_i recomputed every step, two
-    attention passes, host-side beam search).  bench.py is one of the few places allowed to import it."""
+CPU_KIND_NOTE = ("PyTorch-CPU fp32 restatement of the reference algorithm (TensorFlow 1.x unavailable), one article at a "
+                 "time, K replicated rows, W_h.h_i recomputed every step, two attention passes, host-side beam search")
+
+
+def cpu_arm(paths: dict, arts, mode: str) -> float:
+    """Seconds to decode `arts` with oracle/pgen_oracle_torch.py (bench.py is one of the few places allowed to import
+    it).  mode "literal" = the work the reference does; "dedup" = without its redundancy (features once, one attention
+    pass per step), so that the speed-up is not inflated by it."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
     import pgen_oracle as O
+    import pgen_oracle_torch as OT
     from textsummarization_on_flink_b200 import weights_io
     W = weights_io.load_weights(paths["weights"])
     hps = O.parse_hyperparams(synth.hyperparams_string(paths))
-    arts = synth.make_article_ids(n_articles, vsize=V, seed=seed, full_len_only=False)
-    use_all_host_threads()
     t0 = time.perf_counter()
     for ids, ext, n_oov in arts:
-        O.decode_ids(W, hps, ids, ext, n_oov, mode="literal")
-    return time.perf_counter() - t0, n_articles
+        OT.decode_ids(W, hps, ids, ext, n_oov, mode=mode, dtype=torch.float32)
+    return time.perf_counter() - t0
 
 
 def run_reference(args, rank: int, world: int):
@@ -154,33 +163,74 @@ def run_reference(args, rank: int, world: int):
         return
     paths = ensure_model(0, lambda: None)
     per_step = 2
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import pgen_oracle as O
-    from textsummarization_on_flink_b200 import weights_io
-    W = weights_io.load_weights(paths["weights"])
-    hps = O.parse_hyperparams(synth.hyperparams_string(paths))
-    arts = synth.make_article_ids(per_step * (args.steps + args.warmup), vsize=V, seed=4321)
-    use_all_host_threads()
+    threads = use_all_host_threads()
+    arts = synth.make_article_ids(per_step * (args.steps + args.warmup) + 2, vsize=V, seed=4321)
     times = []
     for s in range(args.steps + args.warmup):
-        t0 = time.perf_counter()
-        for ids, ext, n_oov in arts[s * per_step:(s + 1) * per_step]:
-            O.decode_ids(W, hps, ids, ext, n_oov, mode="literal")
+        secs = cpu_arm(paths, arts[s * per_step:(s + 1) * per_step], "literal")
         if s >= args.warmup:
-            times.append(time.perf_counter() - t0)
+            times.append(secs)
     total = sum(times)
     value = per_step * args.steps / total
-    cores = os.cpu_count()
-    sample = ("%d articles per step of the same synthetic workload, one at a time, reference-faithful mode "
-              "(NumPy fp32 restatement; TensorFlow 1.x unavailable)" % per_step)
+    dedup = 2 / cpu_arm(paths, arts[-2:], "dedup")
+    sample = "%d articles per step of the same synthetic workload; %s" % (per_step, CPU_KIND_NOTE)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "articles/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args.gpus),
-        "cpu_baseline": {"value": value, "unit": "articles/s", "cores": cores, "kind": "port", "sample": sample},
+        "note": "the CPU arm runs once, on rank 0's host cores, whatever --gpus says: it is not multiplied by N",
+        "cpu_baseline": {"value": value, "unit": "articles/s", "cores": threads, "kind": "port", "sample": sample,
+                         "dedup_value": dedup},
         "e2e": {"value": value, "unit": "articles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def measure_tf32_peak(torch, dev) -> dict:
+    """Dense TF32 GEMM rate of this GPU the way MEASURED_PEAKS.json measured bf16: torch.matmul 8192^3 fp32 with TF32
+    allowed (cuBLAS), best of 10 (burst) and back to back for ~1.5 s (sustained)."""
+    n = 8192
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn(n, n, device=dev)
+        b = torch.randn(n, n, device=dev)
+        for _ in range(3):
+            a @ b
+        torch.cuda.synchronize(dev)
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        reps = max(10, int(1500.0 / best))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record()
+        e1.synchronize()
+        sustained = e0.elapsed_time(e1) / reps
+        fl = 2.0 * n ** 3
+        return {"tf32_tflops": fl / best / 1e9, "tf32_tflops_sustained": fl / sustained / 1e9,
+                "how": "torch.matmul fp32 8192^3 with allow_tf32 (cuBLAS): best of 10 and %d back to back" % reps}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+        del a, b
+        torch.cuda.empty_cache()
+
+
+def profile_notes() -> dict:
+    """Numbers that come from an ncu capture, not from this run: read from profiles/r2_ncu.json (which names the
+    capture and its date), never typed into this file."""
+    p = os.path.join(ROOT, "profiles", "r2_ncu.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return {}
 
 
 def main():
@@ -190,6 +240,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cpu-articles", type=int, default=8, help="size of the bounded CPU-baseline sample")
+    ap.add_argument("--verify", type=int, default=8, help="e2e rows compared with the oracle after the timed regions")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -297,11 +348,12 @@ def main():
     barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    n_rows = 0
+    e2e_rows = []
     for i in range(args.warmup * ARTICLES_PER_STEP, n_total * ARTICLES_PER_STEP):
         dec.submit(b"uuid-%d" % i, texts[i], b"reference %d." % i)
-        n_rows += len(dec.poll())
-    n_rows += len(dec.poll(flush=True))
+        e2e_rows += dec.poll()
+    e2e_rows += dec.poll(flush=True)
+    n_rows = len(e2e_rows)
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
@@ -310,48 +362,140 @@ def main():
     h2d = ARTICLES_PER_STEP * (5 * T_ENC + 4) * 4
     d2h = ARTICLES_PER_STEP * (2 * S_DEC * 4 + 4 * 3 + 8)
 
-    # ---------------- roofline of the dominant kernel (profiled extra step, CUDA events in the library) ----------
-    dec.set_option("profile=1")
+    # ---------------- verification: e2e rows of the timed region against the oracle ----------------
+    verified = 0
+    if rank == 0 and args.verify > 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import pgen_oracle as O
+        from textsummarization_on_flink_b200 import weights_io
+        Wv = weights_io.load_weights(paths["weights"])
+        hpsv = O.parse_hyperparams(flags)
+        vocab = O.Vocab(paths["vocab_path"], V)
+        first = args.warmup * ARTICLES_PER_STEP
+        near = 0
+        for i in range(first, first + args.verify):
+            uuid, article, summary, reference = e2e_rows[i - first]
+            assert uuid == b"uuid-%d" % i and article == texts[i], "e2e row %d out of order" % i
+            ex = O.make_example(texts[i], vocab, T_ENC)
+            tr = []
+            toks, _, _ = O.decode_ids(Wv, hpsv, ex.enc_input, ex.enc_input_extend_vocab, len(ex.article_oovs), mode="dedup", trace=tr)
+            want = O.format_summary(O.cut_at_stop(O.outputids2words(toks, vocab, ex.article_oovs)))
+            if summary != want:                                   # tolerated only where the oracle's own candidates tie
+                gw, rw = summary.split(), want.split()
+                k = next((j for j, (x, y) in enumerate(zip(gw, rw)) if x != y), min(len(gw), len(rw)))
+                gaps = [abs(x[1] - y[1]) / max(1e-12, abs(x[1])) for step in tr[:k + 1] for x, y in zip(step, step[1:])
+                        if np.isfinite(x[1]) and np.isfinite(y[1])]
+                if not gaps or min(gaps) >= 2e-5:
+                    raise SystemExit("bench.py: e2e row %d differs from the oracle at word %d with no near-tie" % (i, k))
+                near += 1
+            verified += 1
+        if near > max(1, args.verify // 4):
+            raise SystemExit("bench.py: %d of %d verified rows diverged at near-ties" % (near, args.verify))
+
+    # ---------------- roofline: intervals inside one extra batch run with plain launches + CUDA events ----------
+    # Only the first min_dec_steps (35) steps are averaged: no hypothesis may end before that (beam_search.py:146-149),
+    # so every article is live in them and a launch does the full algorithmic work.
+    dec.set_option("profile=35")
     dec.stage_upload(*batches[-1])
     dec.stage_run()
     dec.stage_sync()
     ps = dec.stats()
-    steps_done = dec.debug_fetch("steps_done", ARTICLES_PER_STEP, np.int32)
     dec.set_option("profile=0")
-    # kernel-only durations: the attention pair and the tensor-core pass of that batch replayed 50 times each from a
-    # graph between two CUDA events on the library's stream (no launch gaps; every article active)
-    step_ms_vocab = ps["ms_vocab"] / max(1.0, ps["prof_steps"])
-    step_ms_attn = ps["ms_attention"] / max(1.0, ps["prof_steps"])
-    dec.set_option("measure=50")
+    n_prof = max(1.0, ps["prof_steps"])
+    step_ms_vocab = ps["ms_vocab"] / n_prof
+    step_ms_attn = ps["ms_attention"] / n_prof
+    steps_done = dec.debug_fetch("steps_done", ARTICLES_PER_STEP, np.int32).astype(np.float64)
+    # ... and the two kernels replayed alone from a graph (no launch gaps; every article active).  NOT the headline:
+    # replayed back to back, the tensor-core pass finds its 51 MB of weights in the 126 MB L2.
+    dec.set_option("measure=30")
     pm = dec.stats()
+    n_rep = max(1.0, pm["prof_steps"])
     pk = peaks()
-    n_prof = max(1.0, pm["prof_steps"])
-    ms_vocab, ms_attn = pm["ms_vocab"] / n_prof, pm["ms_attention"] / n_prof
+    notes = profile_notes()
     R = ARTICLES_PER_STEP * BEAM
     lens = batches[-1][2].astype(np.float64)
     A = 2 * H
-    attn_bytes_total = float(np.sum(2 * lens * A * 4 + 3 * BEAM * lens * 4)) * n_prof
-    roof_attn = {"bound": "hbm", "kernel": "attn_energy + attn_context (per step)",
-                 "achieved": attn_bytes_total / (pm["ms_attention"] * 1e-3) / 1e9 if pm["ms_attention"] > 0 else None,
-                 "peak": pk["hbm_gbs"], "unit": "GB/s", "ms_per_launch": ms_attn,
-                 "ms_per_launch_in_profiled_step": step_ms_attn,
-                 # dram__bytes_read.sum + dram__bytes_write.sum of one attn_energy + attn_context launch pair from the
-                 # ncu --set full capture summarised in profiles/r1b_summary.md (batch with mean length 372:
-                 # 96.9 MB algorithmic): bytes per launch pair
-                 "traffic": 96.60e6, "algorithmic_bytes_per_launch": attn_bytes_total / max(1.0, n_prof)}
+    # algorithmic bytes of the attention pass: F and h of every live article once, coverage in, attn out
+    per_article = 2 * lens * A * 4 + 3 * BEAM * lens * 4
+    attn_bytes_total = float(np.sum(per_article * np.minimum(steps_done, n_prof)))      # an article costs only while it is live
+    roof_attn = {"bound": "hbm", "kernel": "attention pass per decode step (attn_fused_kernel + attn_merge_kernel)",
+                 "achieved": attn_bytes_total / (ps["ms_attention"] * 1e-3) / 1e9 if ps["ms_attention"] > 0 else None,
+                 "peak": pk["hbm_gbs"], "unit": "GB/s", "ms_per_launch": step_ms_attn,
+                 "ms_per_launch_replayed_alone": pm["ms_attention"] / n_rep,
+                 "algorithmic_bytes_per_launch": attn_bytes_total / n_prof,
+                 "traffic": notes.get("attention", {}).get("dram_bytes_per_launch"),
+                 "traffic_source": notes.get("attention", {}).get("source"),
+                 "bound_note": "the pass also needs 1.25 special-function operations per tanh: 65.5 M per step = 14 us "
+                               "at 16 per clock and SM; the HBM bytes take 16 us at the measured peak"}
     if roof_attn["achieved"]:
         roof_attn["frac"] = roof_attn["achieved"] / pk["hbm_gbs"]
+    tf32 = measure_tf32_peak(torch, dev)
     flops = 2.0 * R * H * V
-    roof_vocab = {"bound": "tensor", "kernel": "vocab projection GEMM (per step)",
-                  "achieved": flops / (ms_vocab * 1e-3) / 1e12 if ms_vocab > 0 else None,
-                  "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "ms_per_launch": ms_vocab,
-                  "ms_per_launch_in_profiled_step": step_ms_vocab,
-                  "traffic": 51.91e6, "note": "tf32 operands (kind::tf32); peak is the measured bf16 figure, the tf32 "
-                                               "tensor peak is half of it; traffic = dram bytes of one vocab_tc_kernel launch"}
+    roof_vocab = {"bound": "tensor", "kernel": "vocab_tc_kernel (tcgen05 kind::tf32) per decode step",
+                  "achieved": flops / (step_ms_vocab * 1e-3) / 1e12 if step_ms_vocab > 0 else None,
+                  "peak": tf32["tf32_tflops_sustained"], "peak_burst": tf32["tf32_tflops"], "peak_source": tf32["how"],
+                  "unit": "TFLOP/s", "ms_per_launch": step_ms_vocab, "ms_per_launch_replayed_alone_l2_hot": pm["ms_vocab"] / n_rep,
+                  "bf16_peak_for_context": pk.get("bf16_tflops_sustained"),
+                  "tensor_pipe_active_pct_ncu": notes.get("vocab_tc", {}).get("tensor_pipe_active_pct"),
+                  "traffic": notes.get("vocab_tc", {}).get("dram_bytes_per_launch"),
+                  "traffic_source": notes.get("vocab_tc", {}).get("source")}
     if roof_vocab["achieved"]:
-        roof_vocab["frac"] = roof_vocab["achieved"] / pk["bf16_tflops_sustained"]
-    dominant = roof_vocab if ms_vocab >= ms_attn else roof_attn
-    dominant = dict(dominant, peak_source=pk.get("source"))
+        roof_vocab["frac"] = roof_vocab["achieved"] / tf32["tf32_tflops_sustained"]
+    dominant = dict(roof_attn if step_ms_attn >= step_ms_vocab else roof_vocab, peak_source=pk.get("source"))
+
+    # ---------------- config 2: encoder only (BASELINE.json configs[1]) ----------------
+    enc_ms, rec_ms, feat_ms = ps["ms_encoder"], ps["ms_enc_recurrence"], ps["ms_enc_features"]
+    n_cl = 2 * ((ARTICLES_PER_STEP + 9) // 10)                    # clusters of the recurrence: 2 directions x groups of 10 articles
+    dsmem_bytes = float(lens.max()) * n_cl * 8 * 8 * 32 * 12 * 4  # per time step every CTA sends its 32 x 12 floats to 8 CTAs
+    config2 = {"workload": "BASELINE.json configs[1]: encoder-only BiLSTM forward, 64 articles x 400 tokens",
+               "encoder_ms": enc_ms, "recurrence_ms": rec_ms, "us_per_time_step": 1e3 * rec_ms / max(1.0, float(lens.max())),
+               "dsmem_gbs": dsmem_bytes / (rec_ms * 1e-3) / 1e9 if rec_ms > 0 else None,
+               "features_ms": feat_ms,
+               "features_tflops_fp32_equivalent": 2.0 * float(lens.sum()) * A * A / (feat_ms * 1e-3) / 1e12 if feat_ms > 0 else None,
+               "articles_per_s": ARTICLES_PER_STEP / (enc_ms * 1e-3) if enc_ms > 0 else None,
+               "note": "input projection is a per-word table (no GEMM per batch); recurrence = one cluster kernel, "
+                       "latency / DSMEM bound; features = 3xTF32 tcgen05 GEMM incl. the hi/lo split"}
+    dec.close()
+
+    # ---------------- config 4: beam 8, 120 steps, 200 OOVs per article (BASELINE.json configs[3]) ----------------
+    c4_steps = max(2, min(4, args.steps))
+    flags4 = synth.hyperparams_string(paths, beam_size=8, max_enc_steps=T_ENC, max_dec_steps=120, vocab_size=V,
+                                      extra="--articles_per_batch=%d --flush_ms=-1" % ARTICLES_PER_STEP)
+    dec4 = native.Decoder(flags4, device=local_rank)
+    arts4 = synth.make_article_ids(ARTICLES_PER_STEP * 2, vsize=V, seed=4040 + rank, fixed_oovs=200)
+    b4 = [native.pack_articles(arts4[i * ARTICLES_PER_STEP:(i + 1) * ARTICLES_PER_STEP], T_ENC) for i in range(2)]
+    n4 = max(1, dec4.flag("slots"))
+    str4 = []
+    for sl in range(n4):
+        dec4.stage_slot(sl)
+        str4.append(torch.cuda.ExternalStream(dec4.stream_ptr(), device=dev))
+        for _ in range(2):                                        # plain launches, then the graph capture
+            dec4.stage_upload(*b4[sl % 2])
+            dec4.stage_run()
+    for sl in range(n4):
+        dec4.stage_slot(sl)
+        dec4.stage_sync()
+    barrier()
+    torch.cuda.synchronize()
+    f0 = torch.cuda.Event(enable_timing=True)
+    f0.record(str4[0])
+    for i in range(c4_steps * n4):
+        dec4.stage_slot(i % n4)
+        dec4.stage_run()
+    ends4 = []
+    for sl in range(n4):
+        f1 = torch.cuda.Event(enable_timing=True)
+        f1.record(str4[sl])
+        ends4.append(f1)
+    for sl in range(n4):
+        dec4.stage_slot(sl)
+        dec4.stage_sync()
+    torch.cuda.synchronize()
+    ms4 = max_over_ranks(max(f0.elapsed_time(f1) for f1 in ends4))
+    config4 = {"workload": "BASELINE.json configs[3]: beam 8, max_dec_steps 120, 200 distinct OOVs per article, 64 articles "
+                           "per device batch", "articles_per_s": ARTICLES_PER_STEP * c4_steps * n4 * world / (ms4 * 1e-3),
+               "ms_per_batch": ms4 / (c4_steps * n4), "batches_timed_per_gpu": c4_steps * n4, "n_gpus": world}
+    dec4.close()
 
     out = {
         "metric": METRIC, "value": value, "unit": "articles/s", "n_gpus": world, "steps": args.steps,
@@ -359,23 +503,27 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(world),
         "e2e": {"value": e2e_value, "unit": "articles/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "pgen_submit/pgen_poll with article byte strings"},
+        "verified_rows": verified,
         "gpu_launches": launches, "clocks": clocks, "roofline": dominant,
-        "roofline_other": roof_attn if dominant.get("kernel") == roof_vocab["kernel"] else roof_vocab,
+        "roofline_other": roof_vocab if dominant.get("kernel") == roof_attn["kernel"] else roof_attn,
+        "config2": config2, "config4": config4,
+        "selection_guard": {"rows_widened": ps["selection_widened"], "rows_dense": ps["selection_fallbacks"]},
         "stage_ms_last_batch": {"h2d": ps["ms_h2d"], "encoder": ps["ms_encoder"], "decoder": ps["ms_decoder"],
                                 "d2h": ps["ms_d2h"], "decode_steps": ps["prof_steps"]},
     }
     if rank == 0:
         try:
-            secs, n = cpu_reference_sample(paths, args.cpu_articles, seed=99)
-            out["cpu_baseline"] = {"value": n / secs, "unit": "articles/s", "cores": os.cpu_count(), "kind": "port",
-                                   "sample": "%d articles of the same synthetic workload decoded one at a time by the "
-                                             "NumPy restatement in reference-faithful mode (TF1 unavailable), %.1f s"
-                                             % (n, secs)}
+            threads = use_all_host_threads()
+            sample_arts = synth.make_article_ids(args.cpu_articles, vsize=V, seed=99, full_len_only=False)
+            secs = cpu_arm(paths, sample_arts, "literal")
+            secs_d = cpu_arm(paths, sample_arts[:max(2, args.cpu_articles // 2)], "dedup")
+            out["cpu_baseline"] = {"value": args.cpu_articles / secs, "unit": "articles/s", "cores": threads, "kind": "port",
+                                   "dedup_value": max(2, args.cpu_articles // 2) / secs_d,
+                                   "sample": "%d articles of the same synthetic workload, %.1f s; %s" % (args.cpu_articles, secs, CPU_KIND_NOTE)}
         except Exception as ex:      # the CPU baseline must never take the GPU number down with it
             out["cpu_baseline"] = {"value": None, "unit": "articles/s", "cores": os.cpu_count(), "kind": "port",
                                    "sample": "failed: %r" % (ex,)}
         print(json.dumps(out))
-    dec.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -71,6 +71,7 @@ typedef struct {
    * is checked against an error bound after its exact re-scoring: rows that needed extra candidate groups, and rows
    * that had to score the whole vocabulary in fp32 (flat or tied distributions).  Either way the row's top-2K is exact. */
   uint64_t selection_widened, selection_fallbacks;
+  double ms_enc_recurrence, ms_enc_features;   /* parts of ms_encoder of the last batch: BiLSTM recurrence, W_h.h_i product */
 } pgen_stats_t;
 
 /* Replaces main_on_flink/inference_on_flink/default_setup (run_summarization.py:402-426,
@@ -212,7 +213,8 @@ PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, 
  *   check_every=N        poll the device every N steps after min_dec_steps and stop early when every article is done
  *   vocab_guard=auto|widen|dense|off   exactness guard of the tensor-core candidate selection: auto (default), or force
  *                        the widened / dense re-scoring on every row (tests), or switch the check off (A-B timing)
- *   profile=1|0          per-step CUDA events for pgen_stats (plain launches)
+ *   profile=1|0|N        per-step CUDA events for pgen_stats (plain launches); N > 1: sums over the first N steps only
+ *                        (no article can finish before min_dec_steps, so those steps have every article live)
  *   measure=N            replay the attention pair and the tensor-core pass of the last decoded batch N times each
  *                        from a graph between two events; sums land in ms_attention / ms_vocab, prof_steps = N
  * Fails with PGEN_ERR_STATE while pgen_submit rows are in flight.  No counterpart in the reference. */

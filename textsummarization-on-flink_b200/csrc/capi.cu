@@ -258,6 +258,7 @@ int pgen_stats(pgen_t* h, pgen_stats_t* out) {
   out->ms_attention = last.ms_attention; out->ms_vocab = last.ms_vocab; out->ms_select = last.ms_beam;
   out->prof_steps = (double)last.prof_steps;
   out->selection_widened = s.selection_widened; out->selection_fallbacks = s.selection_fallbacks;
+  out->ms_enc_recurrence = last.ms_enc_recurrence; out->ms_enc_features = last.ms_enc_features;
   return PGEN_OK;
 }
 

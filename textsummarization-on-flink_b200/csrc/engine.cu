@@ -42,6 +42,7 @@ Engine::~Engine() {
                   (void*)h_out_lp_, (void*)h_out_avg_, (void*)h_steps_, (void*)h_rescnt_, (void*)h_selstats_})
     if (p) cudaFreeHost(p);
   for (auto& e : ev_) if (e) cudaEventDestroy(e);
+  for (auto& e : eev_) if (e) cudaEventDestroy(e);
   for (auto& e : pev_) if (e) cudaEventDestroy(e);
   if (st2_) cudaStreamDestroy(st2_);
   for (auto& e : fev_) if (e) cudaEventDestroy(e);
@@ -208,6 +209,7 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   CK(cudaStreamCreateWithFlags(&st2_, cudaStreamNonBlocking));
   for (auto& e : fev_) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (auto& e : ev_) CK(cudaEventCreate(&e));
+  for (auto& e : eev_) CK(cudaEventCreate(&e));
 
   *code = PGEN_ERR_IO;
   std::string wpath = hp.weights_path;
@@ -404,6 +406,7 @@ std::string Engine::set_option(const std::string& kv) {
   if (k == "measure") return ran_ ? measure(std::max(1, atoi(v.c_str()))) : std::string();
   if (k == "profile") {
     profile_ = atoi(v.c_str()) != 0;
+    profile_first_ = std::max(0, atoi(v.c_str()));        // N > 1: the sums cover the first N steps only
     if (profile_ && pev_.empty()) {
       pev_.resize((size_t)5 * d_.S);
       for (auto& e : pev_) CK(cudaEventCreate(&e));
@@ -491,6 +494,7 @@ void Engine::encoder() {
     nl += launch_gemm_nt(g, st_);
   }
   const float* hfin;
+  cudaEventRecord(eev_[0], st_);
   if (H == 256 && enc_persistent_) {                   // model.py:90-93, one launch
     nl += launch_enc_lstm_persistent(d_, B, lens_, table ? zx_tab_ : zx_, table ? ids_ : nullptr, w_.enc_kh[0], h_enc_[1], c_enc_,
                                      enc_states_, st_);
@@ -501,6 +505,7 @@ void Engine::encoder() {
                                  enc_states_, st_);
     hfin = h_enc_[max_len_ & 1];
   }
+  cudaEventRecord(eev_[1], st_);
   {                                                    // model.py:117-120 -> row b*K of the "old" state
     GemmArgs g;
     g.A0 = c_enc_; g.lda0 = H; g.k0 = H; g.A1 = c_enc_ + (size_t)B * H; g.lda1 = H; g.k1 = H;
@@ -511,6 +516,7 @@ void Engine::encoder() {
     nl += launch_gemm_nt(g, st_);
   }
   {                                                    // attention_decoder.py:67, once per article
+    cudaEventRecord(eev_[2], st_);
     if (feat_tc_) {
       nl += launch_split_tf32(enc_states_, es_hi_, es_lo_, (size_t)B * T * A, st_);
       nl += g3_.launch(B * T, enc_feat_, A, st_);
@@ -520,6 +526,7 @@ void Engine::encoder() {
       g.C = enc_feat_; g.ldc = A; g.M = B * T; g.N = A;
       nl += launch_gemm_nt(g, st_);
     }
+    cudaEventRecord(eev_[3], st_);
   }
 }
 
@@ -749,14 +756,17 @@ std::string Engine::sync() {
     if (cudaEventElapsedTime(&ms, ev_[2], ev_[3]) == cudaSuccess) stats.ms_encoder = ms;
     if (cudaEventElapsedTime(&ms, ev_[3], ev_[4]) == cudaSuccess) stats.ms_decoder = ms;
     if (cudaEventElapsedTime(&ms, ev_[5], ev_[6]) == cudaSuccess) stats.ms_d2h = ms;
+    if (nB_ > 0 && cudaEventElapsedTime(&ms, eev_[0], eev_[1]) == cudaSuccess) stats.ms_enc_recurrence = ms;
+    if (nB_ > 0 && cudaEventElapsedTime(&ms, eev_[2], eev_[3]) == cudaSuccess) stats.ms_enc_features = ms;
     if (pev_used_ > 0) {
       stats.ms_attention = stats.ms_vocab = stats.ms_beam = 0;
-      for (int s = 0; s < pev_used_; ++s) {
+      const int upto = profile_first_ > 1 ? std::min(profile_first_, pev_used_) : pev_used_;
+      for (int s = 0; s < upto; ++s) {
         if (cudaEventElapsedTime(&ms, pev_[5 * s], pev_[5 * s + 1]) == cudaSuccess) stats.ms_attention += ms;
         if (cudaEventElapsedTime(&ms, pev_[5 * s + 2], pev_[5 * s + 3]) == cudaSuccess) stats.ms_vocab += ms;
         if (cudaEventElapsedTime(&ms, pev_[5 * s + 3], pev_[5 * s + 4]) == cudaSuccess) stats.ms_beam += ms;
       }
-      stats.prof_steps = pev_used_;
+      stats.prof_steps = upto;
     }
     synced_ = true;
   }

@@ -25,6 +25,7 @@ struct DeviceWeights {
 struct EngineStats {
   uint64_t batches = 0, decode_steps = 0, article_steps = 0, early_stops = 0, kernel_launches = 0;
   double ms_h2d = 0, ms_encoder = 0, ms_decoder = 0, ms_d2h = 0;
+  double ms_enc_recurrence = 0, ms_enc_features = 0;    // parts of ms_encoder: BiLSTM recurrence, W_h.h_i product
   double ms_attention = 0, ms_vocab = 0, ms_beam = 0;   // summed over the steps of the last profiled batch
   uint64_t prof_steps = 0;
   uint64_t selection_widened = 0, selection_fallbacks = 0;   // rows whose tf32 candidate set failed the exactness guard
@@ -77,6 +78,7 @@ class Engine {
   int check_every_ = 0;              // > 0: poll the device every N steps (after min_dec_steps) to stop early;
                                      // 0: never block the host -- run() is fully asynchronous
   bool profile_ = false;
+  int profile_first_ = 0;            // profile=N (N > 1): per-step sums over the first N steps only
   int vocab_guard_ = 0;              // MergeArgs::guard
   int* sel_stats_ = nullptr;         // device [2], cumulative
   int32_t* h_selstats_ = nullptr;    // pinned copy, refreshed with every batch's results
@@ -104,6 +106,7 @@ class Engine {
   cudaStream_t st2_ = nullptr;       // side branch of a decode step (p_gen, article-word logits)
   cudaEvent_t fev_[3] = {nullptr, nullptr, nullptr};
   cudaEvent_t ev_[7] = {};
+  cudaEvent_t eev_[4] = {};          // encoder: recurrence begin / end, features begin / end
   DeviceWeights w_{};
   std::vector<void*> allocs_;
   // host staging (pinned)

@@ -43,7 +43,8 @@ class Stats(C.Structure):
                                            "article_steps", "early_stops", "kernel_launches")] + \
                [(n, C.c_double) for n in ("ms_host_text", "ms_h2d", "ms_encoder", "ms_decoder", "ms_d2h",
                                           "ms_attention", "ms_vocab", "ms_select", "prof_steps")] + \
-               [(n, C.c_uint64) for n in ("selection_widened", "selection_fallbacks")]
+               [(n, C.c_uint64) for n in ("selection_widened", "selection_fallbacks")] + \
+               [(n, C.c_double) for n in ("ms_enc_recurrence", "ms_enc_features")]
 
 
 _lib = None
