@@ -1,4 +1,6 @@
-"""The N>1 path on CPU: world_size-2 gloo run of the row sharding + timing aggregation bench.py uses."""
+"""The N>1 path on CPU: world_size-2 gloo run of the row sharding (sharding.shard_rows / owner: what the pipeline stage
+and tools/stream_config5.py deal rows with) and of the timing aggregation bench.py computes `value` with
+(sharding.job_throughput)."""
 import os
 import socket
 import sys

@@ -15,7 +15,7 @@ from __future__ import annotations
 import json
 from typing import Dict, Iterable, Iterator, List, Optional, Sequence
 
-from . import native
+from . import native, sharding
 
 STRING = "STRING"            # DataTypes.STRING (util/CodingUtils.java:37-62)
 
@@ -142,8 +142,8 @@ class TFModel:
                 nonlocal emitted
                 for w, q in zip(workers, queues):
                     q.extend(w.poll(flush=flush))
-                while queues[emitted % n_workers]:
-                    uuid, article, summary, reference = queues[emitted % n_workers].pop(0)
+                while queues[sharding.owner(emitted, n_workers)]:
+                    uuid, article, summary, reference = queues[sharding.owner(emitted, n_workers)].pop(0)
                     full = {"uuid": uuid, "article": article, "summary": summary, "reference": reference}
                     emitted += 1
                     yield {c: full[c] for c in out_cols}
@@ -155,7 +155,7 @@ class TFModel:
                         raise RuntimeError("input row lacks selected column '%s'" % c)
                     v = row[c]
                     vals[c] = v.encode() if isinstance(v, str) else bytes(v)
-                workers[submitted % n_workers].submit(vals["uuid"], vals["article"], vals["reference"])
+                workers[sharding.owner(submitted, n_workers)].submit(vals["uuid"], vals["article"], vals["reference"])
                 submitted += 1
                 yield from drain(False)
             yield from drain(True)

@@ -9,6 +9,12 @@ from typing import List, Sequence, TypeVar
 T = TypeVar("T")
 
 
+def owner(i: int, world: int) -> int:
+    """Subtask (rank, GPU) that decodes the i-th row of the stream: round-robin, like a rebalanced Flink stream.  Rank r
+    returns its rows in submission order, so reading the ranks in the same round-robin order restores the stream's."""
+    return i % world
+
+
 def shard_rows(rows: Sequence[T], rank: int, world: int) -> List[T]:
     """Round-robin partition, the way a rebalanced Flink stream deals rows to subtasks."""
     if not 0 <= rank < world:

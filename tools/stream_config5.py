@@ -25,7 +25,7 @@ import numpy as np  # noqa: E402
 import pgen_pkg  # noqa: E402
 
 pgen_pkg.load()
-from textsummarization_on_flink_b200 import native, synth  # noqa: E402
+from textsummarization_on_flink_b200 import native, sharding, synth  # noqa: E402
 
 
 def main():
@@ -52,7 +52,7 @@ def main():
 
     def subtask(k):
         try:
-            rows = range(k, args.rows, P)                               # rebalance: row i -> subtask i mod P
+            rows = sharding.shard_rows(range(args.rows), k, P)          # rebalance: row i -> subtask i mod P
             with native.Decoder(flags, device=k % n_gpu) as dec:        # open()
                 for i in range(2 * args.articles_per_batch):            # warm-up: plain launches, then the graph capture
                     dec.submit(b"w", pool[i % len(pool)], b"")
