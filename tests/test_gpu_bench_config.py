@@ -84,3 +84,40 @@ def test_articles_do_not_depend_on_the_batch_at_full_size(model_dir):
             for j, b in enumerate(rows):
                 for x, y in zip(outs[64], outs[B]):
                     assert np.array_equal(x[b], y[j]), "beam %d article %d: batch of 64 vs batch of %d" % (beam, b, B)
+
+
+def test_repeated_runs_are_bit_identical(model_dir):
+    """compute-sanitizer (racecheck / memcheck) is closed on this pool, so the hand-rolled mbarrier / DSMEM protocols
+    (persistent encoder, tensor-core pass, decoder cell, one-launch attention) are checked the way that is left: a race
+    shows up as a result that depends on timing.  The same 64 articles are decoded eight times -- alone on the GPU,
+    then with four batches in flight on four streams -- and every output and every beam trace must be bit-identical
+    (every mbarrier wait also traps after 2^26 polls, so a lost signal is an error, not a hang)."""
+    B = 64
+    arts = synth.make_article_ids(B, seed=909)
+    flags = synth.hyperparams_string(model_dir, max_dec_steps=50, min_dec_steps=20, extra="--articles_per_batch=%d --slots=4" % B)
+    with native.Decoder(flags) as dec:
+        packed = native.pack_articles(arts, dec.max_enc_steps)
+        S, K = dec.max_dec_steps, dec.beam_size
+        ref = None
+        for rep in range(4):                                         # one slot at a time
+            dec.stage_upload(*packed)
+            dec.stage_run()
+            dec.stage_sync()
+            out = dec.stage_download() + (dec.debug_fetch("trace_logp", B * S * K).copy(),
+                                          dec.debug_fetch("enc_states", B * dec.max_enc_steps * 512).copy())
+            if ref is None:
+                ref = out
+            for x, y in zip(ref, out):
+                assert np.array_equal(x, y), "run %d differs from run 0" % rep
+        for rep in range(2):                                         # four slots decoding the same batch concurrently
+            for sl in range(4):
+                dec.stage_slot(sl)
+                dec.stage_upload(*packed)
+                dec.stage_run()
+            for sl in range(4):
+                dec.stage_slot(sl)
+                dec.stage_sync()
+                out = dec.stage_download()
+                for x, y in zip(ref[:4], out):
+                    assert np.array_equal(x, y), "slot %d of concurrent round %d differs" % (sl, rep)
+        dec.stage_slot(0)
