@@ -306,6 +306,25 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     vocab_tc_ = vtc_.ready;
   }
 #undef DALLOC
+  {
+    // Dynamic shared memory of the kernels whose footprint grows with max_enc_steps / beam_size / vocab_size: refuse
+    // at create, with the numbers, rather than fail at the first batch with a bare launch error.
+    int optin = 0;
+    CK(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device_));
+    const size_t KM = d_.K <= 4 ? 4 : d_.K <= 8 ? 8 : 16, K2M = d_.K2 <= 8 ? 8 : d_.K2 <= 16 ? 16 : 32;
+    struct { const char* what; size_t bytes; } need[] = {
+        {"attn_context_kernel (softmax + context, max_enc_steps x beam)", (KM * d_.T + 8 * KM * 64) * sizeof(float)},
+        {"attn_energy_kernel (decoder features, beam x 2 hidden_dim)", (KM * d_.A + 2 * (size_t)d_.A) * sizeof(float)},
+        {"vocab_final_kernel (candidates + article words, max_enc_steps)", vocab_tc_ ? vtc_.final_smem(d_.T, vtc_.n_parts()) : 0},
+        {"final_topk_kernel (fp32 vocabulary path: vocab_size bitmap + per-thread lists)",
+         (size_t)((d_.V + 31) / 32) * 4 + (size_t)256 * K2M * 8 + 128}};
+    for (auto& n : need)
+      if (n.bytes > (size_t)optin) {
+        *code = PGEN_ERR_UNSUPPORTED;
+        return std::string(n.what) + " needs " + std::to_string(n.bytes) + " bytes of shared memory per block, this GPU allows " +
+               std::to_string(optin) + ": lower max_enc_steps / beam_size";
+      }
+  }
   CK(cudaDeviceSynchronize());
   *code = PGEN_OK;
   return "";
