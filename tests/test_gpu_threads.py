@@ -105,7 +105,7 @@ def test_device_count_export():
 def test_create_refuses_sizes_beyond_shared_memory(small_cfg, small_model_dir):
     """max_enc_steps so large that the softmax / selection kernels cannot hold a row in shared memory: pgen_create
     says so (PGEN_ERR_UNSUPPORTED with the numbers) instead of failing at the first batch with a launch error."""
-    flags = small_flags(small_model_dir, small_cfg, beam=8, max_enc=20000)
+    flags = small_flags(small_model_dir, small_cfg, beam=8, max_enc=20000, extra="--articles_per_batch=1 --slots=1")
     with pytest.raises(native.PgenError) as e:
         native.Decoder(flags)
     assert e.value.code == 5 and "shared memory" in str(e.value)

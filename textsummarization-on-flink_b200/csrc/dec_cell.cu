@@ -36,7 +36,9 @@ namespace {
 constexpr int DC_H = 256, DC_E = 128, DC_A = 512, DC_SW = DC_A + 2 * DC_H + DC_E;
 constexpr int DC_RB = 16;                            // decoder rows per cluster
 constexpr int DC_CL = 8;                             // CTAs per cluster
-constexpr int DC_NC = 256, DC_NT = DC_NC + 64;       // compute threads, + one producer warp, + one warp for the coverage update
+constexpr int DC_NC = 512, DC_NT = DC_NC + 64;       // compute threads (16 warps: four per scheduler, so that one warp's
+                                                     // dependent FFMA2 pairs and shared-memory latencies hide behind the others), + one
+                                                     // producer warp, + one warp for the coverage update
 constexpr int DC_K1 = DC_E + DC_A, DC_K2 = DC_E + DC_H, DC_K3 = 2 * DC_H;      // 640, 384, 512
 constexpr int DC_N1 = DC_E / DC_CL, DC_N2 = 4 * DC_H / DC_CL, DC_N3 = DC_A / DC_CL;   // 16, 128, 64 columns per CTA
 constexpr int DC_STAGE = 16384, DC_STAGES = 4;
@@ -259,13 +261,10 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
   // ===== compute warps =====
   // biases of this thread's outputs, requested now: the epilogues must not wait for an L2 round trip
   const float bias1 = a.x_b[DC_N1 * c + (tid & 15)];
-  float bias2[2][4], bias3[4];
+  float bias2[4];
 #pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int g = 0; g < 4; ++g) bias2[i][g] = a.dec_b[g * DC_H + 32 * c + (tid & 31)];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) bias3[i] = a.att_b[DC_N3 * c + (tid & 63)];
+  for (int g = 0; g < 4; ++g) bias2[g] = a.dec_b[g * DC_H + 32 * c + (tid & 31)];
+  const float bias3 = a.att_b[DC_N3 * c + (tid & 63)];
   uint32_t n = 0;                                                // weight chunk counter (same sequence as the producer)
   auto chunk_wait = [&]() -> const unsigned char* {
     const uint32_t s = n % DC_STAGES;
@@ -281,28 +280,28 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 
   // ---------------- stage 1: x = [emb; ctx] . M + b, columns [16c, +16) ----------------
   {
-    const int kg = warp, rh = lane >> 4;                         // 8 k groups; lane = (column, row half)
+    const int kg = warp, rh = lane >> 4;                         // 16 k groups; lane = (column, row half)
     const int col[1] = {lane & 15};
     unsigned long long acc[1][8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) acc[0][r] = 0ull;
     for (int q = 0; q < DC_CH1; ++q) {
-      const unsigned char* w = chunk_wait() + (kg >> 1) * (DC_N1 * 128);     // the box of this warp's 16 k
+      const unsigned char* w = chunk_wait() + (kg >> 2) * (DC_N1 * 128);     // the box of this warp's 8 k
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int jj = 4 * (kg & 1) + i;
-        dc_step<1>(acc, A1 + (rh * 8) * DC_K1 + 128 * q + 32 * (kg >> 1) + 4 * jj, DC_K1, w, col, jj);
+      for (int i = 0; i < 2; ++i) {
+        const int jj = 2 * (kg & 3) + i;
+        dc_step<1>(acc, A1 + (rh * 8) * DC_K1 + 128 * q + 32 * (kg >> 2) + 4 * jj, DC_K1, w, col, jj);
       }
       chunk_done();
     }
 #pragma unroll
     for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DC_N1 + col[0]] = dc_sum2(acc[0][r]);
     dc_sync_compute();
-    {                                                            // 256 outputs, one per thread; k groups in fixed order
+    if (tid < DC_RB * DC_N1) {                                   // 256 outputs; k groups in fixed order
       const int row = tid >> 4, cc = tid & 15;
       float v = 0.f;
 #pragma unroll
-      for (int g = 0; g < 8; ++g) v += red[(g * DC_RB + row) * DC_N1 + cc];
+      for (int g = 0; g < 16; ++g) v += red[(g * DC_RB + row) * DC_N1 + cc];
       v += bias1;
       xout[row * DC_N1 + cc] = v;
       const int r = r0 + row;
@@ -319,11 +318,11 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 
   // ---------------- stage 2: gates of units [32c, +32), LSTM cell ----------------
   {
-    const int kg = warp & 3, rh = warp >> 2;                     // 4 k groups x 2 row halves; lane = 4 columns
-    const int col[4] = {lane, lane + 32, lane + 64, lane + 96};  // local column = gate * 32 + unit
-    unsigned long long acc[4][8];
+    const int kg = warp & 3, rh = (warp >> 2) & 1, ch = warp >> 3;    // 4 k groups x 2 row halves x 2 column halves
+    const int col[2] = {64 * ch + lane, 64 * ch + lane + 32};    // local column = gate * 32 + unit
+    unsigned long long acc[2][8];
 #pragma unroll
-    for (int cc = 0; cc < 4; ++cc)
+    for (int cc = 0; cc < 2; ++cc)
 #pragma unroll
       for (int r = 0; r < 8; ++r) acc[cc][r] = 0ull;
     for (int i = 0; i < DC_CH2; ++i) {
@@ -333,26 +332,25 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         const int jj = 2 * kg + u, k = 32 * q + 4 * jj;
-        if (q >= 4) dc_step<4>(acc, A2h + (rh * 8) * DC_H + (k - DC_E), DC_H, w, col, jj);
-        else dc_step<4>(acc, A2x + (k >> 4) * (DC_RB * DC_N1) + (rh * 8) * DC_N1 + (k & 15), DC_N1, w, col, jj);
+        if (q >= 4) dc_step<2>(acc, A2h + (rh * 8) * DC_H + (k - DC_E), DC_H, w, col, jj);
+        else dc_step<2>(acc, A2x + (k >> 4) * (DC_RB * DC_N1) + (rh * 8) * DC_N1 + (k & 15), DC_N1, w, col, jj);
       }
       chunk_done();
     }
 #pragma unroll
-    for (int cc = 0; cc < 4; ++cc)
+    for (int cc = 0; cc < 2; ++cc)
 #pragma unroll
       for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DC_N2 + col[cc]] = dc_sum2(acc[cc][r]);
     dc_sync_compute();
-#pragma unroll
-    for (int it = 0; it < 2; ++it) {                             // (row, unit): k groups in fixed order, then the cell
-      const int o = tid + it * DC_NC, row = o >> 5, u = o & 31;
+    {                                                            // (row, unit): k groups in fixed order, then the cell
+      const int row = tid >> 5, u = tid & 31;
       float z[4];
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
         float v = 0.f;
 #pragma unroll
         for (int q = 0; q < 4; ++q) v += red[(q * DC_RB + row) * DC_N2 + g * 32 + u];
-        z[g] = v + bias2[it][g];
+        z[g] = v + bias2[g];
       }
       // LSTMCell: gates i, j, f, o; forget bias 1.0 (model.py:138)
       const float cn = dc_sigmoid(z[2] + 1.0f) * cprev[row * 32 + u] + dc_sigmoid(z[0]) * tanhf(z[1]);
@@ -376,35 +374,31 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 
   // ---------------- stage 3: attention features d = [c; h] . W_s + b, columns [64c, +64) ----------------
   {
-    const int kg = warp & 3, rh = warp >> 2;
-    const int col[2] = {lane, lane + 32};
-    unsigned long long acc[2][8];
+    const int kg = warp & 3, rh = (warp >> 2) & 1, ch = warp >> 3;
+    const int col[1] = {32 * ch + lane};
+    unsigned long long acc[1][8];
 #pragma unroll
-    for (int cc = 0; cc < 2; ++cc)
-#pragma unroll
-      for (int r = 0; r < 8; ++r) acc[cc][r] = 0ull;
+    for (int r = 0; r < 8; ++r) acc[0][r] = 0ull;
     dc_wait(ch_bar, 0);                                          // (c, h) of all 8 CTAs
     for (int q = 0; q < DC_CH3; ++q) {                           // chunk q = the 64 values that came from CTA q
       const unsigned char* w = chunk_wait() + (kg >> 1) * (DC_N3 * 128);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int jj = 4 * (kg & 1) + u;
-        dc_step<2>(acc, A3 + q * (DC_RB * 64) + (rh * 8) * 64 + 32 * (kg >> 1) + 4 * jj, 64, w, col, jj);
+        dc_step<1>(acc, A3 + q * (DC_RB * 64) + (rh * 8) * 64 + 32 * (kg >> 1) + 4 * jj, 64, w, col, jj);
       }
       chunk_done();
     }
 #pragma unroll
-    for (int cc = 0; cc < 2; ++cc)
-#pragma unroll
-      for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DC_N3 + col[cc]] = dc_sum2(acc[cc][r]);
+    for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DC_N3 + col[0]] = dc_sum2(acc[0][r]);
     dc_sync_compute();
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {
+    for (int it = 0; it < 2; ++it) {
       const int o = tid + it * DC_NC, row = o >> 6, cc = o & 63;
       float v = 0.f;
 #pragma unroll
       for (int q = 0; q < 4; ++q) v += red[(q * DC_RB + row) * DC_N3 + cc];
-      v += bias3[it];
+      v += bias3;
       const int r = r0 + row;
       if (rowok[row]) {
         const int f = DC_N3 * c + cc;
@@ -425,8 +419,8 @@ dec_cell_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_constant_
 // ---------------------------------------------------------------------------------------------
 constexpr int DO_K = DC_H + DC_A, DO_N = 32, DO_CH = DO_K / 128;           // 768, 32 columns per CTA, 6 chunks
 constexpr int DO_OFF_A = DC_STAGES * DC_STAGE;                              // [16][768]  h | ctx
-constexpr int DO_OFF_RED = DO_OFF_A + DC_RB * DO_K * 4;                     // [4][16][32]
-constexpr int DO_OFF_BAR = DO_OFF_RED + 4 * DC_RB * DO_N * 4;
+constexpr int DO_OFF_RED = DO_OFF_A + DC_RB * DO_K * 4;                     // [8 k groups][16][32]
+constexpr int DO_OFF_BAR = DO_OFF_RED + 8 * DC_RB * DO_N * 4;
 constexpr int DO_OFF_ROWOK = DO_OFF_BAR + 128;
 constexpr int DO_SMEM = DO_OFF_ROWOK + 64;
 constexpr int DO_NT = DC_NC + 32;                                           // compute threads + one producer warp
@@ -483,7 +477,7 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
     }
     return;
   }
-  const int kg = warp & 3, rh = warp >> 2;
+  const int kg = warp & 7, rh = warp >> 3;                       // 8 k groups x 2 row halves; lane = column
   const int col[1] = {lane};
   const float bias = a.out_b[DO_N * cb + lane];
   unsigned long long acc[1][8];
@@ -493,20 +487,23 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
   for (uint32_t n = 0; n < (uint32_t)DO_CH; ++n) {
     const uint32_t s = n % DC_STAGES;
     dc_wait(&full[s], (n / DC_STAGES) & 1);
-    const unsigned char* w = ring + (size_t)s * DC_STAGE + kg * (DO_N * 128);
+    const unsigned char* w = ring + (size_t)s * DC_STAGE + (kg >> 1) * (DO_N * 128);
 #pragma unroll
-    for (int jj = 0; jj < 8; ++jj) dc_step<1>(acc, A + (rh * 8) * DO_K + 128 * n + 32 * kg + 4 * jj, DO_K, w, col, jj);
+    for (int u = 0; u < 4; ++u) {
+      const int jj = 4 * (kg & 1) + u;
+      dc_step<1>(acc, A + (rh * 8) * DO_K + 128 * n + 32 * (kg >> 1) + 4 * jj, DO_K, w, col, jj);
+    }
     __syncwarp();
     if (lane == 0) dc_arrive(&empty[s]);
   }
 #pragma unroll
   for (int r = 0; r < 8; ++r) red[(kg * DC_RB + rh * 8 + r) * DO_N + lane] = dc_sum2(acc[0][r]);
   dc_sync_compute();
-  for (int o = tid; o < DC_RB * DO_N; o += DC_NC) {
-    const int row = o >> 5, cc = o & 31, r = r0 + row;
+  {
+    const int row = tid >> 5, cc = tid & 31, r = r0 + row;       // 512 outputs, one per thread; k groups in fixed order
     float v = 0.f;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) v += red[(q * DC_RB + row) * DO_N + cc];
+    for (int q = 0; q < 8; ++q) v += red[(q * DC_RB + row) * DO_N + cc];
     v += bias;
     if (rowok[row]) {
       a.out[(size_t)r * DC_H + DO_N * cb + cc] = v;
@@ -517,10 +514,10 @@ dec_out_kernel(const __grid_constant__ CUtensorMap tmW, DoArgs a) {
       }
     }
   }
-  if (cb == 0 && a.pgen) {                                       // p_gen: warp w takes rows 2w, 2w + 1
-    for (int i = 0; i < 2; ++i) {
-      const int r = r0 + 2 * warp + i;
-      if (!rowok[2 * warp + i]) continue;
+  if (cb == 0 && a.pgen) {                                       // p_gen: warp w takes row w
+    {
+      const int r = r0 + warp;
+      if (!rowok[warp]) return;
       const float4* s4 = reinterpret_cast<const float4*>(a.state + (size_t)r * DC_SW);
       const float4* w4 = reinterpret_cast<const float4*>(a.pg_w);
       float4 sv[DC_SW / 128], wv[DC_SW / 128];
