@@ -299,7 +299,11 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
     if (H == 256 && E == 128) {
       if (share) dcell_.share(share->dcell_);
       else dcell_.init(d_, w_.x_MT, w_.dec_kT, w_.att_MT, w_.out_MT, [&](size_t nf) { return dalloc<float>(nf); }, st_);
-      dec_fused_ = dcell_.ready;
+      // One batch in flight: the one-launch cell is 15 % faster end to end (latency).  Several batches in flight: the GPU
+      // is occupied in SM-time, the cell holds 128 SMs exclusively (203 KB of shared memory per CTA) while the split-K
+      // GEMMs of one batch share SMs with the kernels of the others, and the split path decodes 6 % more articles/s
+      // (tools/slot_sweep.py).  --decoder=fused|split overrides.
+      dec_fused_ = dcell_.ready && (hp.decoder == "fused" || (hp.decoder == "auto" && hp.slots == 1));
     }
     if (V >= 128) vtc_why_ = vtc_.init(proj_wT_tf32_, (int)V, (int)H, out_tf32_, (int)Rpad, 2 * (int)K, n_sms_);
     else vtc_why_ = "vocabulary smaller than one 128-word tile";

@@ -58,7 +58,7 @@ std::vector<FlagRef> flag_table(HyperParams* h) {
       {"convert_to_coverage_model", 2, &h->convert_to_coverage_model},
       {"restore_best_model", 2, &h->restore_best_model}, {"debug", 2, &h->debug},
       {"articles_per_batch", 1, &h->articles_per_batch}, {"flush_ms", 1, &h->flush_ms}, {"slots", 1, &h->slots}, {"encoder_table", 1, &h->encoder_table},
-      {"weights_path", 0, &h->weights_path},
+      {"weights_path", 0, &h->weights_path}, {"decoder", 0, &h->decoder},
   };
 }
 
@@ -106,6 +106,7 @@ std::string parse_hyperparams(const std::string& s, HyperParams* hp) {
         break;                                               // float flags: training only
     }
   }
+  if (hp->decoder != "auto" && hp->decoder != "fused" && hp->decoder != "split") return "flag --decoder must be auto, fused or split";
   if (hp->mode == "decode") hp->batch_size = hp->beam_size;  // run_summarization.py:312-313
   return "";
 }

@@ -26,6 +26,7 @@ struct HyperParams {                       // run_summarization.py:48-88 (names 
   int64_t flush_ms = 50;                   // deadline after which poll() decodes a partial batch
   int64_t slots = 4;                       // device batches in flight per handle (each with its own stream)
   std::string weights_path;                // overrides <log_root>/<exp_name>/train/model.pgenw
+  std::string decoder = "auto";            // fused | split | auto (fused with one batch in flight, split with several)
 };
 
 // Returns "" on success, else the error message.  Token 0 is a dummy program name

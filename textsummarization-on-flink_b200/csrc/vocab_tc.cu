@@ -27,9 +27,8 @@
 #include "vocab_tc.h"
 
 namespace pgn {
-__device__ long long vf_dbg[512 * 12];
+
 namespace {
-#define VTCK(i) do { if (threadIdx.x == 0) { long long now_ = clock64(); tacc[i] += now_ - tlast; tlast = now_; } } while (0)
 
 constexpr int BM = 128, BN = 256, BK = 32;          // CTA-pair tile: 2 x 128 rows, 256 words (128 staged per CTA), 32 tf32 of K
 constexpr int BNH = BN / 2;                          // words of a tile staged by each CTA of the pair
@@ -739,7 +738,6 @@ vocab_final_kernel(MergeArgs a) {
   float* gf = MS + 2;                               // [2] 2K-th final value of the last pass, |out|
   uint32_t* gi = reinterpret_cast<uint32_t*>(gf + 2);  // [4] best unselected supergroup key, group key, counters
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  long long tacc[12] = {0,0,0,0,0,0,0,0,0,0,0,0}; long long tlast = clock64();
 
   // ---- 0: everything this row needs, one round of loads
   // (every load of a thread is requested before its first store: one memory round trip, not one per array)
@@ -786,7 +784,6 @@ vocab_final_kernel(MergeArgs a) {
     a.topk_ids[(size_t)r * K2 + threadIdx.x] = 0;
     a.topk_logp[(size_t)r * K2 + threadIdx.x] = -INFINITY;
   }
-  VTCK(0);
   // ---- 1a: the G (+1) best supergroups: per-warp lists, then warp 0 merges them; meanwhile the last warp combines
   // the per-part softmax statistics of the tensor-core pass and the one before it takes the norm of the output
   warp_top_rounds(sgv > -FLT_MAX ? f2ord(sgv) : 0u, threadIdx.x, G1, wk + warp * G1, wi + warp * G1, lane);
@@ -811,7 +808,6 @@ vocab_final_kernel(MergeArgs a) {
     if (lane == 0) gf[1] = sqrtf(q);
   }
   __syncthreads();
-  VTCK(1);
   // ---- 1b: the G (+1) best groups among the 16 G groups of the G best supergroups (thread = group, 64 contiguous
   // bytes of the row's group maxima per supergroup)
   {
@@ -826,11 +822,9 @@ vocab_final_kernel(MergeArgs a) {
     if (warp == 0) warp_merge_heads(wk, wi, nw2, G1, G1, sel, &gi[1], lane);
   }
   __syncthreads();
-  VTCK(2);
   // ---- 2: exact fp32 logit and tf32-emulated logit of every word of the selected groups
   rescore_groups(a, sel, G, 0, outs, outt, cx, ca, cid, warp, lane);
   __syncthreads();
-  VTCK(3);
 
   const float M = MS[0];
   const float pg = a.pointer_gen ? a.pgen[r] : 1.f;
@@ -876,7 +870,6 @@ vocab_final_kernel(MergeArgs a) {
       fin[c] = id >= 0 ? ((unsigned long long)f2ord(val) << 32) | (0xffffffffu - (uint32_t)id) : 0ull;
     }
     __syncthreads();
-    VTCK(4);
     // ---- 4b: top-2K by counting: every warp ranks the keys of a contiguous sixteenth among themselves (keys are
     // unique: (value, ~id) with distinct ids) and lists its 2K best in descending order; then every list entry is
     // ranked against the other lists by binary search and the 2K best overall are written out.
@@ -894,22 +887,14 @@ vocab_final_kernel(MergeArgs a) {
       }
     }
     __syncthreads();
-    if (threadIdx.x < SEL_WARPS * K2) {
-      const int w = threadIdx.x / K2, i = threadIdx.x - w * K2;
+    if (threadIdx.x < SEL_WARPS * K2) {               // the 2K best of the warps' winners, by counting (keys are unique)
       const unsigned long long mine = ck[threadIdx.x];
       if (mine) {
-        int rank = i;
-        for (int w0 = 0; w0 < SEL_WARPS; w0 += 4) {
-          int cnt[4] = {0, 0, 0, 0};
-#pragma unroll
-          for (int st = 16; st > 0; st >>= 1) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const int wq = w0 + q, idx = cnt[q] + st - 1;
-              if (wq != w && idx < K2 && ck[wq * K2 + idx] > mine) cnt[q] += st;
-            }
-          }
-          rank += cnt[0] + cnt[1] + cnt[2] + cnt[3];
+        int rank = 0;
+        const ulonglong2* c2 = reinterpret_cast<const ulonglong2*>(ck);
+        for (int j = 0; j < SEL_WARPS * K2 / 2; ++j) {
+          const ulonglong2 o = c2[j];
+          rank += (o.x > mine ? 1 : 0) + (o.y > mine ? 1 : 0);
         }
         if (rank < K2) {
           const float v = ord2f((uint32_t)(mine >> 32));
@@ -919,8 +904,6 @@ vocab_final_kernel(MergeArgs a) {
         }
       }
     }
-    VTCK(5);
-    if (threadIdx.x == 0 && blockIdx.x < 512) for (int i = 0; i < 12; ++i) vf_dbg[blockIdx.x * 12 + i] = tacc[i];
     if (pass == 1 || a.guard == GUARD_OFF) break;
     __syncthreads();
     // ---- 5: guard (every quantity below is block-uniform)
@@ -1183,5 +1166,3 @@ int launch_round_tf32(const float* in, float* out, size_t n, cudaStream_t st) {
 }
 
 }  // namespace pgn
-
-extern "C" __attribute__((visibility("default"))) int pgen_debug_vfdbg(long long* out) { return (int)cudaMemcpyFromSymbol(out, pgn::vf_dbg, sizeof(long long) * 512 * 12); }

@@ -15,7 +15,7 @@ with native.Decoder(flags) as dec:
     out = np.zeros(512 * 12, np.int64)
     rc = native.lib().pgen_debug_vfdbg(out.ctypes.data_as(C.c_void_p))
     d = out.reshape(512, 12)[:256]
-    names = ["0 loads", "1a supergroups", "1b groups", "2 rescore", "3+4a dist", "4b top-2K"]
+    names = ["0 loads", "1a supergroups", "1b groups", "2 rescore", "3+4a dist", "4b merge+store", "4b rank count", "4b sync"]
     for i, n in enumerate(names):
         print("  %-16s mean %8.0f  max %8.0f  min %8.0f" % (n, d[:, i].mean(), d[:, i].max(), d[:, i].min()))
-    print("  total mean %.0f max %.0f" % (d[:, :6].sum(1).mean(), d[:, :6].sum(1).max()))
+    print("  total mean %.0f max %.0f" % (d[:, :8].sum(1).mean(), d[:, :8].sum(1).max()))
