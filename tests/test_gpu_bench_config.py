@@ -121,3 +121,24 @@ def test_repeated_runs_are_bit_identical(model_dir):
                 for x, y in zip(ref[:4], out):
                     assert np.array_equal(x, y), "slot %d of concurrent round %d differs" % (sl, rep)
         dec.stage_slot(0)
+
+
+@pytest.mark.parametrize("beam", [4, 8])
+def test_fused_and_split_decoder_paths_agree(model_dir, beam):
+    """--decoder=fused (one-launch cell + fused out projection / p_gen, csrc/dec_cell.cu) and --decoder=split (gather +
+    split-K GEMMs + point-wise kernels), likewise attention=fused / split: same articles, both against the oracle, and
+    beam traces against each other (different fp32 summation orders: equal up to near-ties)."""
+    from test_gpu_vocab_guard import _traces, compare_traces
+    arts = synth.make_article_ids(16, seed=31 + beam)
+    W = weights_io.load_weights(model_dir["weights"])
+    runs = {}
+    for decoder in ("fused", "split"):
+        flags = synth.hyperparams_string(model_dir, beam_size=beam, max_dec_steps=50, min_dec_steps=20,
+                                         extra="--articles_per_batch=16 --slots=2 --decoder=%s" % decoder)
+        hps = O.parse_hyperparams(flags)
+        with native.Decoder(flags) as dec:
+            if decoder == "split":
+                dec.set_option("attention=split")
+            check_against_oracle(dec, W, hps, arts[:6])
+            runs[decoder] = _traces(dec, native.pack_articles(arts, dec.max_enc_steps), len(arts))
+    compare_traces(runs["fused"], runs["split"], len(arts), max_diverged=2)
