@@ -215,8 +215,9 @@ PGEN_API int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, 
  *                        the widened / dense re-scoring on every row (tests), or switch the check off (A-B timing)
  *   profile=1|0|N        per-step CUDA events for pgen_stats (plain launches); N > 1: sums over the first N steps only
  *                        (no article can finish before min_dec_steps, so those steps have every article live)
- *   measure=N            replay the attention pair and the tensor-core pass of the last decoded batch N times each
- *                        from a graph between two events; sums land in ms_attention / ms_vocab, prof_steps = N
+ *   measure=N            replay the attention pass and the tensor-core pass of the last decoded batch N times each
+ *                        from a graph between two events, with an L2 flush between replays (its time subtracted); sums
+ *                        land in ms_attention / ms_vocab, prof_steps = N
  * Fails with PGEN_ERR_STATE while pgen_submit rows are in flight.  No counterpart in the reference. */
 PGEN_API int pgen_set_option(pgen_t* h, const char* key_value);
 

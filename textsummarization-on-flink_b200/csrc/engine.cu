@@ -334,24 +334,34 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   return "";
 }
 
-// Kernel-only timing for the roofline: the attention pair and the tensor-core pass of the last decoded batch, each
-// replayed `reps` times from a graph (both are idempotent on the buffers the batch left behind) between two CUDA
-// events on this engine's stream -- no launch gaps, caches as warm as in the step loop.  Results land in the profile
-// fields of the stats (sums over `reps` launches, prof_steps = reps).  Re-initialises the beam state: call it after
-// the batch's results have been taken.
+// Kernel-only timing for the roofline: the attention pass and the tensor-core pass of the last decoded batch, each
+// replayed `reps` times from a graph (both are idempotent on the buffers the batch left behind) between two CUDA events
+// on this engine's stream -- no launch gaps.  Between two replays the graph overwrites a 256 MB scratch buffer, twice
+// the L2: back to back the attention pass would find its 105 MB of encoder states / features, and the tensor-core
+// pass its 51 MB of weights, in the 126 MB L2, which they never do in a decode step.  The same graph with the
+// flushes alone is timed too and subtracted.  Results land in the profile fields of the stats (sums over `reps`
+// launches, prof_steps = reps).  Re-initialises the beam state: call it after the batch's results have been taken.
 std::string Engine::measure(int reps) {
   std::string err = sync();
   if (!err.empty()) return err;
   const int B = nB_, K = d_.K, R = B * K;
   if (B <= 0) return "";
   launch_init_beam(d_, B, lens_, bb_, st_);                    // every article active again
+  const size_t flush_bytes = (size_t)256 << 20;
+  if (!flush_) {
+    CK(cudaMalloc((void**)&flush_, flush_bytes));
+    allocs_.push_back(flush_);
+  }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   auto timed = [&](const std::function<void()>& body, double* total_ms) -> std::string {
-    body();                                                    // lazy function attributes outside the capture
+    if (body) body();                                          // lazy function attributes outside the capture
     cudaGraph_t g = nullptr; cudaGraphExec_t ge = nullptr;
     if (cudaStreamBeginCapture(st_, cudaStreamCaptureModeRelaxed) != cudaSuccess) return "measure: capture failed";
-    for (int i = 0; i < reps; ++i) body();
+    for (int i = 0; i < reps; ++i) {
+      cudaMemsetAsync(flush_, i & 0xff, flush_bytes, st_);
+      if (body) body();
+    }
     if (cudaStreamEndCapture(st_, &g) != cudaSuccess || !g || cudaGraphInstantiate(&ge, g, 0) != cudaSuccess) {
       if (g) cudaGraphDestroy(g);
       return "measure: graph instantiation failed";
@@ -368,13 +378,15 @@ std::string Engine::measure(int reps) {
     *total_ms = ms;
     return "";
   };
-  double ms_att = 0, ms_voc = 0;
-  err = timed([&] { attention(B, cov_[0], attn_[0], state_[0]); }, &ms_att);
+  double ms_flush = 0, ms_att = 0, ms_voc = 0;
+  err = timed(nullptr, &ms_flush);
+  if (err.empty()) err = timed([&] { attention(B, cov_[0], attn_[0], state_[0]); }, &ms_att);
   if (err.empty() && vocab_tc_)
     err = timed([&] { vtc_.launch(R, w_.proj_v, part_m_, part_s_, gmax_, gstride_, smax_, sstride_, nullptr, st_); }, &ms_voc);
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   if (!err.empty()) return err;
-  stats.ms_attention = ms_att; stats.ms_vocab = ms_voc; stats.ms_beam = 0; stats.prof_steps = (uint64_t)reps;
+  stats.ms_attention = std::max(0.0, ms_att - ms_flush); stats.ms_vocab = vocab_tc_ ? std::max(0.0, ms_voc - ms_flush) : 0.0;
+  stats.ms_beam = 0; stats.prof_steps = (uint64_t)reps;
   return check("measure");
 }
 

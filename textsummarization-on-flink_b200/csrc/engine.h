@@ -87,6 +87,7 @@ class Engine {
   bool dec_fused_ = false;           // one-launch decoder cell + out projection / p_gen (dec_cell.cu) instead of gather + GEMMs
   bool dpack_fresh_ = false;         // the decoder cell has written dpack_ for the coming attention pass
   bool attn_fused_ = false;          // one-launch attention (attn_fused.cu) instead of the energy + context pair
+  unsigned char* flush_ = nullptr;   // 256 MB written between the replays of measure() so that they start from a cold L2
   float *att_pctx_ = nullptr, *att_segstat_ = nullptr, *dpack_ = nullptr;
   int* att_cnt_ = nullptr;
   int attention(int B, const float* cov, float* attn, float* state);   // the step's attention pass on dfeat_

@@ -1,5 +1,5 @@
 """One warm batch, then one batch inside a cudaProfilerStart/Stop range (for ncu --profile-from-start off).
-Usage: python tools/profile_step.py [articles_per_batch] [max_dec_steps]"""
+Usage: python tools/profile_step.py [articles_per_batch] [max_dec_steps] [extra flags, e.g. "--slots=1 --decoder=fused"]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -9,9 +9,10 @@ from textsummarization_on_flink_b200 import native, synth
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 S = int(sys.argv[2]) if len(sys.argv) > 2 else 100
+EXTRA = sys.argv[3] if len(sys.argv) > 3 else ""
 paths = synth.make_model_dir("/tmp/pgen_bench_model", "W1")
 flags = synth.hyperparams_string(paths, max_dec_steps=S, min_dec_steps=min(35, S - 1),
-                                 extra="--articles_per_batch=%d" % B)
+                                 extra="--articles_per_batch=%d %s" % (B, EXTRA))
 arts = synth.make_article_ids(2 * B, seed=1234)
 with native.Decoder(flags) as dec:
     b0 = native.pack_articles(arts[:B], dec.max_enc_steps)
