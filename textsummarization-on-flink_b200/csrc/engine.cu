@@ -606,6 +606,7 @@ int Engine::step_launch(int B, int o, int ps) {
     // attention on the new state, coverage not updated                            (:156-158)
     g = GemmArgs(); g.A0 = state_[n] + A; g.lda0 = SW; g.k0 = 2 * H; g.B = w_.att_MT; g.ldb = 2 * H; g.bias = w_.att_b;
     g.C = dfeat_; g.ldc = A; g.M = R; g.N = A; g.skinny = 1;
+    if (attn_fused_ && (K & 1) == 0) { g.C_pack = dpack_; g.pack_K = K; dpack_fresh_ = true; }   // + the layout the attention kernel copies
     nl += launch_gemm_nt(g, st_);
     }
     if (profile_) cudaEventRecord(pev_[5 * ps + 0], st_);

@@ -190,6 +190,10 @@ gemm_skinny_kernel(GemmArgs g) {
       asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
       g.C_tf32[(long long)m * g.ldc_tf32 + n] = __uint_as_float(r);
     }
+    if (g.C_pack) {
+      const int art = m / g.pack_K, k = m - art * g.pack_K;
+      g.C_pack[(((long long)art * (g.pack_K / 2) + (k >> 1)) * g.N + n) * 2 + (k & 1)] = 2.885390081777927f * v;
+    }
   }
 }
 static_assert(8 * 2 * GBK * 36 >= 8 * 1024, "reduction buffer must fit in the tile storage");

@@ -29,6 +29,8 @@ struct GemmArgs {
   const float* bias = nullptr;
   float* C = nullptr; int ldc = 0;
   float* C_tf32 = nullptr; int ldc_tf32 = 0;   // optional second output: C rounded to tf32 (rna), operand of the tensor-core pass
+  float* C_pack = nullptr; int pack_K = 0;     // optional second output (N == 512): 2 log2(e) * C in the layout attn_fused.cu
+                                               // copies, [row / K][(row % K) / 2][n][row % 2] (beam rows interleaved in pairs)
   int M = 0, N = 0;
   int act = 0;            // 0 none, 1 relu
   int skinny = 0;         // per-step decoder GEMM (few hundred rows): split-K tile kernel.  Chosen by the call
