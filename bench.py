@@ -52,12 +52,13 @@ def config_dict(n_gpus: int) -> dict:
     return {"workload": "BASELINE.json configs[2]: full beam-4 decode, 64 articles per device batch, "
                         "max_enc_steps=400, max_dec_steps=100, min_dec_steps=35, coverage=1, pointer_gen (OOV copy "
                         "scatter), vocab 50000, hidden 256, emb 128, W1 synthetic weights",
-            "articles_per_step_per_gpu": ARTICLES_PER_STEP, "slots_in_flight": "library default (--slots=4) unless PGEN_BENCH_EXTRA overrides", "beam_size": BEAM, "max_enc_steps": T_ENC,
+            "articles_per_step_per_gpu": ARTICLES_PER_STEP, "slots_in_flight": "4 device batches in flight on 4 streams (library default --slots=4; --decoder=auto then runs the split-K decoder GEMMs + the one-launch attention); PGEN_BENCH_EXTRA overrides", "beam_size": BEAM, "max_enc_steps": T_ENC,
             "max_dec_steps": S_DEC, "vocab_size": V,
             "sharding": "articles sharded by rank, one GPU per rank, no collective on the data path (x%d)" % n_gpus,
             "l2": "no explicit flush: every decode step of every batch in flight streams its own 105 MB of encoder "
                   "states/features plus the 51 MB projection (and 32 MB of exact rows), and a batch's encoder reads "
-                  "210 MB of the per-word table -- four batches in flight cycle > 600 MB through the 126 MB L2"}
+                  "210 MB of the per-word table -- four batches in flight cycle > 600 MB through the 126 MB L2; "
+                  "the roofline replays write a 256 MB buffer between replays (flush time subtracted)"}
 
 
 def peaks() -> dict:
@@ -515,7 +516,7 @@ def main():
         "config2": config2, "config4": config4,
         "selection_guard": {"rows_widened": ps["selection_widened"], "rows_dense": ps["selection_fallbacks"]},
         "stage_ms_last_batch": {"h2d": ps["ms_h2d"], "encoder": ps["ms_encoder"], "decoder": ps["ms_decoder"],
-                                "d2h": ps["ms_d2h"], "decode_steps": ps["prof_steps"]},
+                                "d2h": ps["ms_d2h"], "note": "the batch that carried the event pairs: its first %d decode steps were plain launches, the rest graph replays" % int(ps["prof_steps"])},
     }
     if rank == 0:
         try:
