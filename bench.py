@@ -244,6 +244,9 @@ def main():
     ap.add_argument("--verify", type=int, default=8, help="e2e rows compared with the oracle after the timed regions")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+    if os.environ.get("PGEN_BENCH_WATCHDOG_S"):        # a run that does not end: every thread's Python stack on stderr
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["PGEN_BENCH_WATCHDOG_S"]), repeat=False)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

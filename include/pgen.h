@@ -198,6 +198,12 @@ PGEN_API int pgen_attention_static(pgen_t* h, int n_articles, const float* enc_f
  * "enc_states" [B,T,2H], "enc_feat" [B,T,2H], "dec_c0" / "dec_h0" [B,H], "trace_tokens" /
  * "trace_parents" [B,S,K] (int32), "trace_logp" [B,S,K].  Returns the element count in *n. */
 PGEN_API int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n);
+/* Diagnostic for a call that does not return: the ONE entry point that may be called from another thread while a call
+ * on `h` is blocked.  out[0] = which stage the handle's thread is in (30 collecting the oldest batch, 40..43 launching
+ * one), out[1] = next slot, out[2] = batches in flight, then per slot four values: the engine's stage (1 upload, 10..19
+ * inside run, 20 waiting for the stream, 21 after), live articles, steps done by article 0, the attention ticket
+ * counter -- the last three read from the device on a stream of their own.  Returns the number of values written. */
+PGEN_API int pgen_debug_where(pgen_t* h, long long* out, int cap);
 /* Test hook: the vocabulary scores out . w + v (model.py:236) for `rows` decoder outputs, DEVICE pointers
  * out_dev [rows, H] -> logits_dev [rows, V]; use_tc != 0 runs the tcgen05 tf32 kernel (scores carry tf32
  * rounding), 0 the fp32 SIMT kernel. */

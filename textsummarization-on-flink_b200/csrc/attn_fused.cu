@@ -135,6 +135,26 @@ __device__ __forceinline__ int af_pos(int lane) { return (lane & 7) * 4 + (lane 
 __device__ __forceinline__ void af_sync_e() { asm volatile("bar.sync 1, %0;" ::"n"(AF_NE) : "memory"); }    // E warps only
 __device__ __forceinline__ void af_sync_c() { asm volatile("bar.sync 2, %0;" ::"n"(AF_NCT) : "memory"); }   // C warps only
 
+#ifdef PGEN_LIVE_AF
+__device__ unsigned int live_af[16];                 // entry / exit counters per warp role (pgen_debug_where)
+#define LIVE_AF(i) atomicAdd(&live_af[i], 1u)
+#else
+#define LIVE_AF(i) ((void)0)
+#endif
+
+// Cycle counters for tools/af_dbg.py -- compiled in only with -DPGEN_AF_CYCLES (PGEN_CYCLES=1 bash build.sh); the
+// shipped library has none of it.  Slot layout: [CTA][32]: 0..11 E warp 0, 12..21 first C warp, 22..31 producer.
+#ifdef PGEN_AF_CYCLES
+__device__ long long af_cyc[160 * 32];
+#define AF_T(v) const long long v = clock64()
+#define AF_ADD(c, t0, t1) c += (t1) - (t0)
+#define AF_ONLY(...) __VA_ARGS__
+#else
+#define AF_T(v)
+#define AF_ADD(c, t0, t1)
+#define AF_ONLY(...)
+#endif
+
 template <int K>
 __global__ void __launch_bounds__(AF_NT, 1)
 attn_fused_kernel(AfArgs a) {
@@ -161,6 +181,8 @@ attn_fused_kernel(AfArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int T = a.T, NSEG = a.nseg_max;
   const int n_items = a.B * NSEG;
+  AF_T(t_entry);
+  AF_ONLY(unsigned long long g_entry; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g_entry));)
 
   // Segments of every live article (0: finished or empty) and the length of its last segment, in shared memory: with
   // this much of the SM's memory configured as shared there is next to no L1 left, and walking the item list must
@@ -177,6 +199,8 @@ attn_fused_kernel(AfArgs a) {
   for (int i = tid; i < AF_A; i += AF_NT) { vs[i] = -2.0f * a.v[i]; ws[i] = a.cov ? kS * a.w_c[i] : 0.f; }
   if (!a.cov) for (int i = tid; i < NDS * K * 32; i += AF_NT) cvs[i] = 0.f;
   __syncthreads();
+  AF_T(t_setup);
+  if (tid == 0) LIVE_AF(0);
   auto item_geom = [&](int i, int& art, int& seg, int& n) {
     art = i / NSEG; seg = i - art * NSEG;
     n = seg == (int)nsg[art] - 1 ? (int)lastn[art] : AF_SEG;
@@ -241,22 +265,38 @@ attn_fused_kernel(AfArgs a) {
     };
     uint32_t nl = 0, j = 0;                                            // next load, item being loaded
     int cur = 0;
+    AF_ONLY(long long p_draw = 0, p_empty = 0, p_ds = 0, p_first = 0;)
+    AF_T(pa);
     if (lane == 0) { cur = draw(); hand_over(0, cur); }
     cur = __shfl_sync(0xffffffffu, cur, 0);
+    AF_T(pb);
+    AF_ADD(p_draw, pa, pb);
     while (cur >= 0) {
       int nxt = 0;
       for (int states = 0; states < 2; ++states, ++nl) {
+        AF_T(p0);
         af_bar_wait(&empty[nl % 3], ((nl / 3) & 1) ^ 1);               // the buffer's previous tile has been consumed
+        AF_T(p1);
+        AF_ADD(p_empty, p0, p1);
         issue_tile(nl, cur, states != 0);
+        AF_ONLY(if (nl == 0) p_first = clock64() - t_entry;)
         if (states == 0) {
+          AF_T(p2);
           issue_ds(j, cur);
+          AF_T(p3);
+          AF_ADD(p_ds, p2, p3);
           if (lane == 0) { nxt = draw(); hand_over(j + 1, nxt); }      // the next item, while this one's data flies
           nxt = __shfl_sync(0xffffffffu, nxt, 0);
+          AF_T(p4);
+          AF_ADD(p_draw, p3, p4);
         }
       }
       cur = nxt;
       ++j;
     }
+    AF_ONLY(if (lane == 0) { long long* o = af_cyc + blockIdx.x * 32 + 22; o[0] = p_draw; o[1] = p_empty; o[2] = p_ds; o[3] = p_first;
+                             o[4] = clock64() - t_entry; o[5] = j; })
+    if (lane == 0) LIVE_AF(1);
     return;
   }
 
@@ -265,12 +305,21 @@ attn_fused_kernel(AfArgs a) {
     const int pair = warp % C::NPAIR, slice = warp / C::NPAIR;
     const int mypos = af_pos(lane);
     const unsigned long long kS2 = af_pk2(kS, kS), one2 = af_pk2(1.0f, 1.0f);
+    AF_ONLY(long long e_get = 0, e_ds = 0, e_F = 0, e_cmp = 0, e_free = 0, e_sync = 0, e_first = 0; uint32_t e_items = 0;)
     for (uint32_t j = 0;; ++j) {
+      AF_T(e0);
       const int it = get_item(j);
+      AF_T(e1);
+      AF_ADD(e_get, e0, e1);
       if (it < 0) break;
       const uint32_t db = j % NDS, ld = 2 * j, b = ld % 3;
       af_bar_wait(&dsfull[db], (j / NDS) & 1);
+      AF_T(e2);
+      AF_ADD(e_ds, e1, e2);
       af_bar_wait(&full[b], (ld / 3) & 1);
+      AF_T(e3);
+      AF_ADD(e_F, e2, e3);
+      AF_ONLY(if (j == 0) e_first = e3 - t_entry; ++e_items;)
       const float* cvp = cvs + ((size_t)db * K + 2 * pair) * 32 + mypos;
       const unsigned long long cv2 = af_pk2(cvp[0], cvp[32]);
       const float* Frow = tiles + (size_t)b * (AF_TILE / 4) + af_off(mypos) + slice * C::SLICE;
@@ -307,12 +356,22 @@ attn_fused_kernel(AfArgs a) {
       }
       float s0, s1;
       af_upk2(acc2, s0, s1);
+      AF_T(e4);
+      AF_ADD(e_cmp, e3, e4);
       if (j > 0) af_bar_wait(efree, (j - 1) & 1);    // the C warps have read the previous item's partial sums
+      AF_T(e5);
+      AF_ADD(e_free, e4, e5);
       part[(slice * K + 2 * pair) * 32 + mypos] = s0;
       part[(slice * K + 2 * pair + 1) * 32 + mypos] = s1;
       af_sync_e();                                   // every E warp is done with the F tile, the features and `part` is complete
       if (tid == 0) { af_arrive(&empty[b]); af_arrive(&dsfree[db]); af_arrive(efull); }
+      AF_T(e6);
+      AF_ADD(e_sync, e5, e6);
     }
+    AF_ONLY(if (tid == 0) { long long* o = af_cyc + blockIdx.x * 32; unsigned long long g_exit; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g_exit));
+                            o[0] = t_setup - t_entry; o[1] = e_get; o[2] = e_ds; o[3] = e_F; o[4] = e_cmp; o[5] = e_free; o[6] = e_sync;
+                            o[7] = e_first; o[8] = e_items; o[9] = clock64() - t_entry; o[10] = (long long)g_entry; o[11] = (long long)g_exit; })
+    if (lane == 0) LIVE_AF(2);
     return;
   }
 
@@ -323,14 +382,20 @@ attn_fused_kernel(AfArgs a) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) vsum += __shfl_xor_sync(0xffffffffu, vsum, o);
   vsum *= -0.5f;
+  AF_ONLY(long long c_get = 0, c_efull = 0, c_soft = 0, c_H = 0, c_ctx = 0, c_st = 0;)
   for (uint32_t j = 0;; ++j) {
+    AF_T(c0);
     const int it = get_item(j);
+    AF_T(c1);
+    AF_ADD(c_get, c0, c1);
     if (it < 0) break;
     int art, seg, n;
     item_geom(it, art, seg, n);
     const int t0 = seg * AF_SEG;
     // ---------------- energies, softmax inside the segment (lane = position) ----------------
     af_bar_wait(efull, j & 1);
+    AF_T(c2);
+    AF_ADD(c_efull, c1, c2);
 #pragma unroll
     for (int kk = 0; kk < K; kk += AF_CW) {
       const int k = kk + cw;
@@ -355,10 +420,14 @@ attn_fused_kernel(AfArgs a) {
     }
     af_sync_c();                                     // p complete, `part` read
     if (ctid == 0) af_arrive(efree);
+    AF_T(c3);
+    AF_ADD(c_soft, c2, c3);
     // ---------------- context partial: thread = 2 features, packed over row pairs ----------------
     {
       const uint32_t ld = 2 * j + 1, b = ld % 3;
       af_bar_wait(&full[b], (ld / 3) & 1);
+      AF_T(c4);
+      AF_ADD(c_H, c3, c4);
       const float* Hc = tiles + (size_t)b * (AF_TILE / 4) + 2 * ctid;
       unsigned long long acc2[C::NPAIR][2];
 #pragma unroll
@@ -375,6 +444,8 @@ attn_fused_kernel(AfArgs a) {
           acc2[p2 + 1][1] = af_fma2(pp.y, af_pk2(h.y, h.y), acc2[p2 + 1][1]);
         }
       }
+      AF_T(c5);
+      AF_ADD(c_ctx, c4, c5);
       float* pc = a.pctx + (size_t)(art * NSEG + seg) * K * AF_A + 2 * ctid;
 #pragma unroll
       for (int p = 0; p < C::NPAIR; ++p) {
@@ -386,8 +457,13 @@ attn_fused_kernel(AfArgs a) {
       }
       af_sync_c();                                   // the h buffer and psm are free
       if (ctid == 0) af_arrive(&empty[b]);
+      AF_T(c6);
+      AF_ADD(c_st, c5, c6);
     }
   }
+  AF_ONLY(if (ctid == 0) { long long* o = af_cyc + blockIdx.x * 32 + 12; o[0] = c_get; o[1] = c_efull; o[2] = c_soft; o[3] = c_H; o[4] = c_ctx;
+                           o[5] = c_st; o[6] = clock64() - t_entry; })
+  if (lane == 0) LIVE_AF(3);
 }
 
 // Second kernel: one CTA per beam row of every live article merges the article's segments (segment order) into the
@@ -528,3 +604,13 @@ int launch_attn_fused(const Dims& d, int B, const int* lens, const int* active, 
 }
 
 }  // namespace pgn
+
+#ifdef PGEN_LIVE_AF
+namespace pgn { void live_read_af(unsigned int* out16, cudaStream_t st) { cudaMemcpyFromSymbolAsync(out16, live_af, 64, 0, cudaMemcpyDeviceToHost, st); } }
+#endif
+
+#ifdef PGEN_AF_CYCLES
+extern "C" __attribute__((visibility("default"))) int pgen_debug_afdbg(void* out) {   // 160 x 32 int64, tools/af_dbg.py
+  return (int)cudaMemcpyFromSymbol(out, pgn::af_cyc, sizeof(long long) * 160 * 32);
+}
+#endif

@@ -40,6 +40,7 @@ struct pgen {
   std::vector<std::unique_ptr<Engine>> engs;
   std::deque<InFlight> inflight;     // launched batches, oldest first (= submission order)
   int next_slot = 0, stage_slot = 0;
+  volatile int where = 0;                  // host-side breadcrumb, read without locks by pgen_debug_where
   Engine& eng() { return *engs[stage_slot]; }
   std::string err;
   std::deque<PendingRow> pending;
@@ -62,6 +63,7 @@ static int fail(pgen_t* h, int code, const std::string& msg) {
 // whose token ids cannot be mapped back to words is emitted with an empty summary and named in the error, the rest
 // of its batch is emitted normally.
 static int collect_oldest(pgen_t* h) {
+  h->where = 30;
   InFlight& f = h->inflight.front();
   Engine& e = *h->engs[f.slot];
   const size_t n = f.rows.size();
@@ -92,6 +94,7 @@ static int collect_oldest(pgen_t* h) {
 
 // launch the first n pending rows as one device batch on the next slot (asynchronous)
 static int launch_pending(pgen_t* h, size_t n) {
+  h->where = 40;
   const int slot = h->next_slot;
   while (!h->inflight.empty()) {                   // the slot must be free; batches complete in FIFO order
     bool busy = false;
@@ -110,8 +113,11 @@ static int launch_pending(pgen_t* h, size_t n) {
     memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
   }
   Engine& e = *h->engs[slot];
+  h->where = 41;
   std::string err = e.upload((int)n, h->b_ids.data(), h->b_ext.data(), T, h->b_lens.data(), h->b_noov.data());
+  h->where = 42;
   if (err.empty()) err = e.run();
+  h->where = 43;
   if (!err.empty()) return fail(h, PGEN_ERR_CUDA, err);        // the rows stay in `pending`: nothing is lost
   InFlight f;
   f.slot = slot;
@@ -401,6 +407,21 @@ int pgen_debug_vocab_logits(pgen_t* h, int rows, const float* out_dev, float* lo
   if (slot_busy(h)) return busy_error(h, "pgen_debug_vocab_logits");
   std::string err = h->eng().vocab_logits_op(rows, out_dev, logits_dev, use_tc);
   return err.empty() ? PGEN_OK : fail(h, PGEN_ERR_CUDA, err);
+}
+
+// Where is the handle's thread?  Callable from ANOTHER thread while a call on `h` is blocked (reads breadcrumbs without
+// locks; device values through a stream of its own): out[0] handle breadcrumb, out[1] next slot, out[2] batches in
+// flight, then per slot (breadcrumb, live articles, steps done by article 0, attention ticket).  Diagnostic only.
+int pgen_debug_where(pgen_t* h, long long* out, int cap) {
+  if (!h || !out || cap < 3) return PGEN_ERR_ARG;
+  out[0] = h->where; out[1] = h->next_slot; out[2] = (long long)h->inflight.size();
+  int n = 3;
+  for (size_t i = 0; i < h->engs.size() && n + 4 <= cap; ++i, n += 4) {
+    out[n] = h->engs[i]->where_;
+    h->engs[i]->debug_progress(out + n + 1);
+  }
+  if (!h->engs.empty() && n + 48 <= cap) { h->engs[0]->debug_live(out + n); n += 48; }
+  return n;
 }
 
 int pgen_debug_fetch(pgen_t* h, const char* name, void* out, size_t cap_bytes, size_t* n) {

@@ -457,6 +457,7 @@ std::string Engine::set_option(const std::string& kv) {
 std::string Engine::upload(int n, const int32_t* enc_ids, const int32_t* ext_ids, int ld, const int32_t* lens,
                            const int32_t* n_oovs) {
   if (n < 0 || n > Bcap_) return "n_articles exceeds articles_per_batch";
+  where_ = 1;
   CK(cudaSetDevice(device_));
   const int T = d_.T;
   nB_ = n;
@@ -720,10 +721,13 @@ void Engine::decoder() {
   if (graphs && !ge && chunk <= d_.S) {
     // first batch of this size: one chunk with plain launches (which also sets the kernels' lazy function attributes
     // outside any capture), then capture; a failed capture leaves plain launches for good
+    where_ = 12;
     for (int i = 0; i < chunk; ++i) nl += step_launch(B, i & 1, i);
     steps = chunk;
+    where_ = 13;
     ge = step_graph(B, chunk, true);
   }
+  where_ = 15;
   while (ge && steps + chunk <= d_.S) {
     cudaGraphLaunch(ge, st_);
     nl += (uint64_t)graph_nodes_;
@@ -751,11 +755,14 @@ done:
 
 std::string Engine::run() {
   if (!staged_) return "pgen_stage_run before pgen_stage_upload";
+  where_ = 10;
   CK(cudaSetDevice(device_));
   CK(cudaEventRecord(ev_[2], st_));
   if (nB_ > 0) encoder();
+  where_ = 11;
   CK(cudaEventRecord(ev_[3], st_));
   if (nB_ > 0) decoder();
+  where_ = 17;
   CK(cudaEventRecord(ev_[4], st_));
   // results to pinned host memory on the same stream: the batch is complete when ev_[6] has fired
   const size_t n = nB_, S = d_.S;
@@ -774,7 +781,54 @@ std::string Engine::run() {
   if (!err.empty()) return err;
   ran_ = true; synced_ = false; counted_ = false;
   ++stats.batches;
+  where_ = 19;
   return "";
+}
+
+#ifdef PGEN_LIVE_VT
+void live_read_vt(unsigned int* out16, cudaStream_t st);
+#endif
+#ifdef PGEN_LIVE_AF
+void live_read_af(unsigned int* out16, cudaStream_t st);
+#endif
+#ifdef PGEN_LIVE_PE
+void live_read_pe(unsigned int* out16, cudaStream_t st);
+#endif
+// entry / exit counters of the kernels that wait on mbarriers (zeros unless built with -DPGEN_LIVE): 3 x 16 values
+void Engine::debug_live(long long* out48) {
+  for (int i = 0; i < 48; ++i) out48[i] = 0;
+#if defined(PGEN_LIVE_VT) || defined(PGEN_LIVE_AF) || defined(PGEN_LIVE_PE)
+  if (cudaSetDevice(device_) != cudaSuccess) return;
+  cudaStream_t s = nullptr;
+  if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return;
+  unsigned int v[48] = {};
+#ifdef PGEN_LIVE_VT
+  live_read_vt(v, s);
+#endif
+#ifdef PGEN_LIVE_AF
+  live_read_af(v + 16, s);
+#endif
+#ifdef PGEN_LIVE_PE
+  live_read_pe(v + 32, s);
+#endif
+  cudaStreamSynchronize(s);
+  cudaStreamDestroy(s);
+  for (int i = 0; i < 48; ++i) out48[i] = v[i];
+#endif
+}
+
+void Engine::debug_progress(long long* out3) {
+  out3[0] = out3[1] = out3[2] = -1;
+  if (cudaSetDevice(device_) != cudaSuccess) return;
+  cudaStream_t s = nullptr;
+  if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return;
+  int v[3] = {-1, -1, -1};
+  cudaMemcpyAsync(&v[0], bb_.n_active, 4, cudaMemcpyDeviceToHost, s);
+  cudaMemcpyAsync(&v[1], bb_.steps_done, 4, cudaMemcpyDeviceToHost, s);
+  if (att_cnt_) cudaMemcpyAsync(&v[2], att_cnt_, 4, cudaMemcpyDeviceToHost, s);
+  cudaStreamSynchronize(s);
+  cudaStreamDestroy(s);
+  for (int i = 0; i < 3; ++i) out3[i] = v[i];
 }
 
 bool Engine::done() {
@@ -784,8 +838,10 @@ bool Engine::done() {
 }
 
 std::string Engine::sync() {
+  where_ = 20;
   CK(cudaSetDevice(device_));
   CK(cudaStreamSynchronize(st_));
+  where_ = 21;
   if (ran_ && !synced_) {
     float ms = 0;
     if (cudaEventElapsedTime(&ms, ev_[0], ev_[1]) == cudaSuccess) stats.ms_h2d = ms;

@@ -66,6 +66,11 @@ class Engine {
 
   Dims d_{};
   int device_ = 0, Bcap_ = 0, R_ = 0, nB_ = 0, max_len_ = 0;
+ public:
+  volatile int where_ = 0;                 // host-side breadcrumb (pgen_debug_where): which call the engine's thread is inside
+  void debug_progress(long long* out3);
+  void debug_live(long long* out48);       // kernel entry / exit counters of this engine's device (PGEN_LIVE builds)    // (live articles, steps done by article 0, attention ticket) read on a stream of its own
+ private:
   bool staged_ = false, ran_ = false, synced_ = false, counted_ = false;
   bool use_graph_ = true;            // replay captured steps instead of launching ~13 kernels per step
   int graph_steps_ = 10;             // steps per graph (even); the early-stop poll happens between graphs

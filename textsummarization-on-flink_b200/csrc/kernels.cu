@@ -363,6 +363,13 @@ __device__ __forceinline__ void pe_bar_wait(uint64_t* bar, uint32_t parity) {
 // AG is chosen so that ALL clusters are co-resident: a B200 runs at most 15 clusters of 8 CTAs with this footprint,
 // and a 16th would cost a whole second wave (tools/micro/cluster_occ.cu).  Every article's arithmetic is the same
 // for every AG.
+#ifdef PGEN_LIVE_PE
+__device__ unsigned int live_pe[16];                 // entry / exit counters (pgen_debug_where)
+#define LIVE_PE(i) atomicAdd(&live_pe[i], 1u)
+#else
+#define LIVE_PE(i) ((void)0)
+#endif
+
 template <int AG>
 __global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(PE_THREADS, 1)
 enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const float* __restrict__ zx,
@@ -382,6 +389,7 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
   const int dir = blockIdx.y, b0 = blockIdx.z * AG;
   const int tid = threadIdx.x;
   constexpr int H4 = 4 * PE_H;
+  if (tid == 0) LIVE_PE(0);
 
   // recurrent weights of this CTA's 128 gate columns, and h(-1) = 0
   const float* khd = kh + (size_t)dir * PE_H * H4;
@@ -493,7 +501,9 @@ enc_lstm_persistent_kernel(int T, int B, const int* __restrict__ lens, const flo
       }
     }
   }
+  if (tid == 0) LIVE_PE(2);
   cluster.sync();                                  // nobody leaves while remote stores may still target it
+  if (tid == 0) LIVE_PE(1);
   if (gate_thread && fb < B) {
     h_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = h_reg;
     c_fin[(size_t)dir * B * PE_H + (size_t)fb * PE_H + 32 * c + ful] = c_reg;
@@ -1345,3 +1355,7 @@ int launch_fill(float* p, float v, size_t n, cudaStream_t st) {
 }
 
 }  // namespace pgn
+
+#ifdef PGEN_LIVE_PE
+namespace pgn { void live_read_pe(unsigned int* out16, cudaStream_t st) { cudaMemcpyFromSymbolAsync(out16, live_pe, 64, 0, cudaMemcpyDeviceToHost, st); } }
+#endif

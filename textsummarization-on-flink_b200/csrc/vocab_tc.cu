@@ -160,6 +160,15 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // half of B from its own shared memory.  The leader (rank 0) issues the MMAs for both; both run an epilogue on
 // their own 128 rows.  grid = 2 * n_mpairs * n_ranges;  pair (mp, range) handles tiles range, range + n_ranges, ...
 // ---------------------------------------------------------------------------------------------
+// Entry / exit counters per kernel and warp role, read by pgen_debug_where when a call does not return: compiled in only
+// with -DPGEN_LIVE (PGEN_LIVE=1 bash build.sh).
+#ifdef PGEN_LIVE_VT
+__device__ unsigned int live_vt[16];
+#define LIVE_VT(i) atomicAdd(&live_vt[i], 1u)
+#else
+#define LIVE_VT(i) ((void)0)
+#endif
+
 template <bool STORE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -201,6 +210,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   cluster_sync_all();                                          // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) LIVE_VT(0);
 
   if (warp == 0) {
     // ===== TMA producer (both CTAs; completion is signalled on the leader's barriers) =====
@@ -220,6 +230,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           tma_load_2d_pair(smB + (size_t)s * TILE_BYTES, &tmB, mapa_rank(&full[s], 0), kb * BK, tile * BN + (int)crank * BNH);
         }
       }
+      LIVE_VT(2);
     }
   } else if (warp == 1) {
     // ===== MMA issuer (leader only) =====
@@ -243,6 +254,7 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         tc_commit_pair(&t_full[acc]);                          // accumulator complete, in both CTAs
       }
+      LIVE_VT(3);
     }
   } else {
     // ===== epilogue: thread == row, two warps per TMEM lane quarter, each taking 128 of the tile's 256 words.
@@ -333,13 +345,16 @@ vocab_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(acc ? t_empty_l1 : t_empty_l0);      // one arrival per epilogue warp of either CTA
     }
+    if (lane == 0) LIVE_VT(4);
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) LIVE_VT(5);
   cluster_sync_all();                                          // neither CTA leaves while the other can still signal it
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+    if (lane == 0) LIVE_VT(1);
   }
 }
 
@@ -388,6 +403,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) LIVE_VT(8);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -465,10 +481,12 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) LIVE_VT(10);
   cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+    if (lane == 0) LIVE_VT(9);
   }
 }
 
@@ -1166,3 +1184,7 @@ int launch_round_tf32(const float* in, float* out, size_t n, cudaStream_t st) {
 }
 
 }  // namespace pgn
+
+#ifdef PGEN_LIVE_VT
+namespace pgn { void live_read_vt(unsigned int* out16, cudaStream_t st) { cudaMemcpyFromSymbolAsync(out16, live_vt, 64, 0, cudaMemcpyDeviceToHost, st); } }
+#endif

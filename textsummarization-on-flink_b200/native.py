@@ -9,14 +9,15 @@ from typing import List, Optional, Sequence, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpgen_cuda.so")
+LIB_PATH = os.environ.get("PGEN_LIB") or os.path.join(_HERE, "libpgen_cuda.so")   # PGEN_LIB: a diagnostic build (csrc/build.sh)
 
 EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_stats", "pgen_last_error",
            "pgen_destroy", "pgen_flag_int", "pgen_text_encode", "pgen_text_summary", "pgen_decode_ids",
            "pgen_stage_upload", "pgen_stage_run", "pgen_stage_sync", "pgen_stage_download", "pgen_stream",
            "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
            "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot",
-           "pgen_example_parse", "pgen_example_write", "pgen_submit_example", "pgen_device_count"]
+           "pgen_example_parse", "pgen_example_write", "pgen_submit_example", "pgen_device_count",
+           "pgen_debug_where"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -85,6 +86,7 @@ def lib() -> C.CDLL:
         L.pgen_device_count.argtypes = []
         L.pgen_device_count.restype = C.c_int
         L.pgen_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.pgen_debug_where.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.pgen_set_option.argtypes = [C.c_void_p, C.c_char_p]
         L.pgen_attention.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
         L.pgen_debug_vocab_logits.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
@@ -268,6 +270,12 @@ class Decoder:
 
     def stream_ptr(self) -> int:
         return int(self._L.pgen_stream(self._h) or 0)
+
+    def debug_where(self) -> list:
+        """Callable from another thread while a call on this handle is blocked (include/pgen.h: pgen_debug_where)."""
+        out = np.zeros(128, np.int64)
+        n = self._L.pgen_debug_where(self._h, out.ctypes.data_as(C.c_void_p), 128)
+        return [int(x) for x in out[:max(0, n)]]
 
     def debug_fetch(self, name: str, count: int, dtype=np.float32) -> np.ndarray:
         out = np.zeros(count, dtype)
