@@ -68,3 +68,26 @@ def test_shard_round_trip():
         assert sharding.unshard_rows(shards) == rows
         assert max(len(s) for s in shards) - min(len(s) for s in shards) <= 1
     assert sharding.job_throughput(10, 2.0) == 5.0
+
+
+def _wait_worker(rank, world, port, out_dir):
+    import time
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    t0 = time.time()
+    if rank == 0:
+        sharding.wait_for_rank0(dist, "leg")            # not done yet: returns at once on rank 0
+        time.sleep(1.0)                                 # "the CPU leg"
+        sharding.wait_for_rank0(dist, "leg", done=True)
+    else:
+        sharding.wait_for_rank0(dist, "leg")            # sleeps on the store's socket until rank 0 is done
+        np.save(os.path.join(out_dir, "waited.npy"), np.array([time.time() - t0]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_other_ranks_sleep_through_rank0s_cpu_leg(tmp_path):
+    """bench.py: ranks != 0 wait for rank 0's CPU-baseline leg on the store (no collective, no busy core)."""
+    mp.spawn(_wait_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    assert float(np.load(tmp_path / "waited.npy")[0]) >= 0.9

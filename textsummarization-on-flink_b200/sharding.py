@@ -42,3 +42,22 @@ def job_throughput(n_local: int, seconds_local: float, dist=None, device=None) -
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dist.all_reduce(n, op=dist.ReduceOp.SUM)
     return float(n.item() / t.item())
+
+
+def wait_for_rank0(dist, key: str, done: bool = False, timeout_s: float = 1800.0) -> None:
+    """Ranks other than 0 SLEEP until rank 0 has called this with done=True (a key in the process group's store).
+
+    bench.py's CPU-baseline leg runs on rank 0's host cores only; a NCCL barrier would have the other ranks spin on
+    their stream (one busy core each, plus their OpenMP pools) and starve it: on an 8-GPU box the 0.5 s leg took more
+    than a minute that way.  No device work and no collective is involved."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    import datetime
+    from torch.distributed import distributed_c10d
+    store = distributed_c10d._get_default_store()
+    if dist.get_rank() == 0:
+        if done:
+            store.set(key, "1")
+        return
+    store.wait([key], datetime.timedelta(seconds=timeout_s))
+
