@@ -535,7 +535,6 @@ def main():
                                    "sample": "failed: %r" % (ex,)}
         print(json.dumps(out))
     if world > 1:
-        from textsummarization_on_flink_b200 import sharding
         sharding.wait_for_rank0(dist, "pgen_bench_cpu_leg", done=True)   # the other ranks sleep through rank 0's CPU leg
         dist.barrier()
         dist.destroy_process_group()
