@@ -5,16 +5,25 @@ TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is part of the product: onl
 ``--impl reference`` legs may import it, and there only as the checker or the timed
 CPU baseline -- never as the thing shipped.  The product path is ``libpgen_cuda.so``.
 
-PARITY UNPINNED.  The reference's arithmetic lives in TensorFlow 1.x ("tensorflow
+PARITY STATUS.  The reference's arithmetic lives in TensorFlow 1.x ("tensorflow
 1.11.0", /root/reference/README.md:87), which is not vendored under /root/reference and
 is not installable here (Python 2.7 code, no network); the reference's own tests hold no
 golden vectors or assertions.  This file is therefore a
 *restatement* of the reference algorithm from its call sites, with the TF1 op semantics
 written out from their published definitions.  Each function cites the reference
 file:line it follows (paths relative to /root/reference/src/main/python/pointer-generator/).
-What pins it instead is tests/test_oracle_*.py: every op is checked against an
-independent formulation (torch.nn.LSTM, torch.softmax, index_add_, torch.topk) and the
-two oracle modes ("literal" and "dedup") are checked against each other.
+What pins it:
+* outputs of the reference's OWN sources run here: model.py, attention_decoder.py,
+  beam_search.py, decode.py, batcher.py, data.py executed unmodified on oracle/tf1_shim.py
+  (a NumPy restatement of the TF 1.11 ops they call) by
+  tests/golden/make_reference_golden.py; the vectors are committed (tests/golden/ref_*.npz)
+  and tests/test_reference_golden.py holds this file to them step by step and row by row
+  (identical token ids; log-probs within 2e-5 on the small model, 5e-4 at full size);
+* tests/test_oracle_*.py: every op against an independent formulation (torch.nn.LSTM,
+  torch.softmax, index_add_, torch.topk, a float64 whole-decode), and the two oracle
+  modes ("literal" and "dedup") against each other.
+Still unpinned: TensorFlow's own kernels (the shim restates their documented semantics;
+no TensorFlow binary has run on these inputs).
 
 Arithmetic: float32 throughout (NumPy), beam scores accumulated in float64 exactly as the
 reference's Python ``sum`` over float32 scalars does (beam_search.py:72-79).

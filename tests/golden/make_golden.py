@@ -1,6 +1,7 @@
 """Generates tests/golden/decode_small.npz and decode_full.npz from the ORACLE (the reference holds no golden
-vectors and cannot run here: SURVEY.md section 8c).  These pin the oracle and the library against accidental
-change; they are not TensorFlow outputs.   Run:  python tests/golden/make_golden.py"""
+vectors and TensorFlow 1.x cannot run here: SURVEY.md section 8c).  They are not TensorFlow outputs; the same inputs run
+through the reference's own Python sources (make_reference_golden.py -> ref_small.npz / ref_full.npz) give identical
+token ids and log-probs within 1e-5 / 5e-4 (tests/test_reference_golden.py).   Run:  python tests/golden/make_golden.py"""
 import os
 import sys
 

@@ -1,0 +1,302 @@
+"""Golden vectors produced by the reference's OWN Python sources (tests/golden/ref_small.npz, ref_full.npz; generated
+here, where /root/reference exists, by tests/golden/make_reference_golden.py: model.py, attention_decoder.py,
+beam_search.py, decode.py, batcher.py and data.py of the reference executing on oracle/tf1_shim.py, a NumPy restatement
+of the TensorFlow 1.11 ops they call).
+
+CPU: (1) those vectors equal the oracle-made vectors the GPU tests compare with (decode_small.npz, decode_full.npz) --
+identical token ids, log-probs within 1e-5 (300-word model) / 5e-4 (50 000-word model, 400 encoder + 100 decoder
+steps); (2) the oracle reproduces the reference run step by step (every top-2K id and log-prob of every beam row of
+every decode step) and row by row (ids, OOV lists, summary strings); (3) the TF variable names and shapes the
+library's weight archive uses are the ones the reference's graph creates; (4) the shim's ops agree with PyTorch's
+independent implementations of the same ops.  Where /root/reference exists the generator is re-run and must reproduce
+the committed file."""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import pgen_oracle as O
+import tf1_shim as S
+from textsummarization_on_flink_b200 import synth
+
+HERE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _load(name):
+    spec = importlib.util.spec_from_file_location(name, os.path.join(HERE, name + ".py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+mg = _load("make_golden")
+
+
+def _small_arts():
+    c = mg.SMALL
+    return synth.make_article_ids(c["n"], vsize=c["V"], seed=c["art_seed"], max_len=c["max_len"], oov_rate=c["oov_rate"])
+
+
+def test_reference_run_equals_the_small_golden_vectors():
+    g, r = np.load(os.path.join(HERE, "decode_small.npz")), np.load(os.path.join(HERE, "ref_small.npz"))
+    assert np.array_equal(r["lens"], g["lens"]) and np.array_equal(r["tokens"], g["tokens"])
+    np.testing.assert_allclose(r["logprobs"], g["logprobs"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(r["avg"], g["avg"], rtol=0, atol=1e-5)
+    assert (g["lens"] < 30).sum() >= 6 and (g["lens"] == 30).sum() >= 2      # early [STOP]s and full-length summaries
+
+
+def test_reference_run_equals_the_full_size_golden_vectors():
+    g, r = np.load(os.path.join(HERE, "decode_full.npz")), np.load(os.path.join(HERE, "ref_full.npz"))
+    assert np.array_equal(r["lens"], g["lens"]) and np.array_equal(r["tokens"], g["tokens"])
+    np.testing.assert_allclose(r["logprobs"], g["logprobs"], rtol=5e-4, atol=1e-5)
+    np.testing.assert_allclose(r["avg"], g["avg"], rtol=5e-4, atol=1e-5)
+    assert r["tokens"].shape == (4, 100) and int(r["lens"].min()) >= 35
+
+
+def test_oracle_follows_the_reference_run_step_by_step(monkeypatch):
+    """Every decode_onestep of the reference run (model.py:367-443: top-2K ids and log-probs of all beam rows) against
+    the oracle's decode_onestep on the same article, for all 12 articles of the small case."""
+    r = np.load(os.path.join(HERE, "ref_small.npz"))
+    W = mg.small_weights()
+    hps = O.parse_hyperparams(mg.SMALL["flags"])
+    steps = []
+    real = O.decode_onestep
+
+    def spy(*a, **k):
+        out = real(*a, **k)
+        steps.append((np.array(out[0]), np.array(out[1])))
+        return out
+    monkeypatch.setattr(O, "decode_onestep", spy)
+    n_steps = 0
+    for b, (a, e, k) in enumerate(_small_arts()):
+        steps.clear()
+        toks, lps, avg = O.decode_ids(W, hps, a, e, k, mode="literal")
+        assert len(steps) == int(r["n_steps"][b])
+        for s, (ids, lp) in enumerate(steps):
+            want_ids, want_lp = r["step_ids"][b, s], r["step_logp"][b, s]
+            fin = np.isfinite(want_lp)
+            assert np.array_equal(np.isfinite(lp), fin)
+            np.testing.assert_allclose(lp[fin], want_lp[fin], rtol=0, atol=2e-5)
+            diff = ids != want_ids
+            if diff.any():                              # only where two candidates of a row tie within the tolerance
+                for i, j in zip(*np.nonzero(diff)):
+                    assert abs(float(want_lp[i, j]) - float(lp[i, j])) <= 2e-5 or not fin[i, j]
+            n_steps += 1
+        assert toks == r["tokens"][b, :r["lens"][b]].tolist()
+        assert abs(avg - float(r["avg"][b])) < 1e-5
+    assert n_steps > 150
+
+
+def test_oracle_text_path_equals_the_reference_run(tmp_path):
+    """data.py / batcher.py / decode.py of the reference on article TEXT: encoder ids, extended ids, OOV lists, and the
+    (uuid, article, summary, reference) rows its writer received."""
+    r = np.load(os.path.join(HERE, "ref_small.npz"))
+    c = mg.SMALL
+    vpath = str(tmp_path / "vocab")
+    synth.write_vocab_file(vpath, c["V"])
+    vocab = O.Vocab(vpath, c["V"])
+    W = mg.small_weights()
+    hps = O.parse_hyperparams(mg.SMALL["flags"])
+    arts = _small_arts()
+    some_oov = 0
+    for i, (ids, ext, n_oov) in enumerate(arts):
+        text = synth.ids_to_article(ext, c["V"], salt=i)
+        assert str(r["row_article"][i]).encode() == text and str(r["row_uuid"][i]) == "uuid-%d" % i
+        ex = O.make_example(text, vocab, 24)
+        n = int(r["enc_lens"][i])
+        assert len(ex.enc_input) == n == len(ids)
+        assert ex.enc_input == r["enc_batch"][i, :n].tolist() == ids.tolist()
+        assert ex.enc_input_extend_vocab == r["enc_batch_extend_vocab"][i, :n].tolist() == ext.tolist()
+        oovs = [w.encode() for w in str(r["art_oovs"][i]).split("\t") if w]
+        assert ex.article_oovs == oovs and len(oovs) == int(r["n_oovs"][i]) == n_oov
+        some_oov += n_oov > 0
+        row = O.decode_row(W, vocab, hps, b"uuid-%d" % i, text, str(r["in_reference"][i]).encode())
+        assert row[0].decode() == str(r["row_uuid"][i]) and row[1].decode() == str(r["row_article"][i])
+        assert row[2].decode() == str(r["row_summary"][i])
+        # the reference column: the reference re-tokenises it (nltk) and joins the sentences with one space; on an
+        # already tokenised reference that is the identity, which is what the library's pass-through assumes
+        assert row[3].decode() == str(r["row_reference"][i]) == str(r["in_reference"][i])
+    assert some_oov >= 6
+    assert any("  " in str(s) for s in r["row_summary"])          # sentences joined by two spaces (decode.py:182)
+
+
+@pytest.mark.parametrize("beam,cov,max_dec,min_dec", [(8, 1, 20, 5), (3, 0, 16, 4), (1, 1, 12, 3), (2, 0, 12, 12)])
+@pytest.mark.parametrize("mode", ["literal", "dedup"])
+def test_oracle_equals_the_reference_run_across_beam_sizes_and_coverage(beam, cov, max_dec, min_dec, mode):
+    """ref_variants.npz: beam 8 / 3 / 1 / 2, with and without coverage (a graph without coverage has no w_c variable),
+    min_dec_steps == max_dec_steps (no [STOP] is ever accepted).  Both oracle modes: `literal` does the reference's
+    work, `dedup` is the arithmetic the CUDA path implements (features once, one attention pass per step)."""
+    v = np.load(os.path.join(HERE, "ref_variants.npz"))
+    tag = "b%dc%d_" % (beam, cov)
+    c = mg.SMALL
+    W = mg.small_weights()
+    hps = O.parse_hyperparams("p --mode=decode --beam_size=%d --coverage=%d --max_enc_steps=24 --max_dec_steps=%d --min_dec_steps=%d"
+                              % (beam, cov, max_dec, min_dec))
+    arts = synth.make_article_ids(5, vsize=c["V"], seed=321, max_len=c["max_len"], oov_rate=0.25)
+    for b, (a, e, k) in enumerate(arts):
+        toks, lps, avg = O.decode_ids(W, hps, a, e, k, mode=mode)
+        n = int(v[tag + "lens"][b])
+        assert toks == v[tag + "tokens"][b, :n].tolist()
+        np.testing.assert_allclose(np.array(lps, np.float32), v[tag + "logprobs"][b, :n], rtol=0, atol=2e-5)
+        assert abs(avg - float(v[tag + "avg"][b])) < 1e-5
+        assert int(v[tag + "n_steps"][b]) <= max_dec
+
+
+def test_oracle_text_edges_equal_the_reference_run(tmp_path):
+    """Truncation at max_enc_steps, special tokens spelled out in an article, repeated OOVs, one-word and all-OOV articles,
+    blanks / tabs / newlines / vertical tabs / form feeds between words: ids, OOV lists, decoded summaries."""
+    v = np.load(os.path.join(HERE, "ref_variants.npz"))
+    c = mg.SMALL
+    vpath = str(tmp_path / "vocab")
+    synth.write_vocab_file(vpath, c["V"])
+    vocab = O.Vocab(vpath, c["V"])
+    W = mg.small_weights()
+    hps = O.parse_hyperparams(mg.SMALL["flags"])
+    assert int(v["edge_enc_lens"][0]) == 24 and len(str(v["edge_article"][0]).split()) == 40          # truncated (batcher.py:55-57)
+    assert str(v["edge_oovs"][1]) == "[UNK]\tzz" and str(v["edge_enc"][1]).split()[:2] == ["3", "0"]    # "[STOP]" is id 3, "[UNK]" an OOV
+    for i, art in enumerate(v["edge_article"]):
+        text = str(art).encode()
+        ex = O.make_example(text, vocab, 24)
+        assert ex.enc_input == [int(x) for x in str(v["edge_enc"][i]).split()]
+        assert ex.enc_input_extend_vocab == [int(x) for x in str(v["edge_ext"][i]).split()]
+        assert ex.article_oovs == [w.encode() for w in str(v["edge_oovs"][i]).split("\t") if w]
+        row = O.decode_row(W, vocab, hps, b"e-%d" % i, text, b"edge reference %d ." % i)
+        assert row[2].decode() == str(v["edge_summary"][i])
+        toks, lps, _ = O.decode_ids(W, hps, ex.enc_input, ex.enc_input_extend_vocab, len(ex.article_oovs), mode="dedup")
+        n = int(v["edge_lens"][i])
+        assert toks == v["edge_tokens"][i, :n].tolist()
+        np.testing.assert_allclose(np.array(lps, np.float32), v["edge_logprobs"][i, :n], rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("name,V,H,E", [("ref_small.npz", 300, 32, 16), ("ref_full.npz", 50000, 256, 128)])
+def test_weight_archive_names_are_the_reference_graphs_variables(name, V, H, E):
+    """The reference's graph (built by its own model.py / attention_decoder.py) creates exactly the variables the .pgenw
+    archive is keyed by, with the same shapes: the generator's load_ckpt stand-in fails on any difference, and the
+    result is recorded in the vectors."""
+    r = np.load(os.path.join(HERE, name))
+    got = {str(n): tuple(int(x) for x in str(s).split(",")) for n, s in zip(r["variable_names"], r["variable_shapes"])}
+    assert got == {k: tuple(v) for k, v in synth.variable_shapes(V, H, E).items()}
+    assert got == {k: tuple(v) for k, v in O.variable_shapes(V, H, E).items()}
+
+
+# ---- the shim's ops against PyTorch's implementations of the same ops ----
+def _run(t, feed=None):
+    return S.Session().run(t, feed or {})
+
+
+def test_shim_lstm_and_bidirectional_rnn_match_torch():
+    S.reset_default_graph()
+    rng = np.random.default_rng(0)
+    B, T, E, H = 3, 7, 5, 4
+    x = rng.standard_normal((B, T, E)).astype(np.float32)
+    lens = np.array([7, 4, 1], np.int32)
+    cf, cb = S.LSTMCell(H), S.LSTMCell(H)
+    with S.variable_scope("encoder"):
+        (of, ob), (sf, sb) = S.bidirectional_dynamic_rnn(cf, cb, S.convert_to_tensor(x), sequence_length=S.convert_to_tensor(lens))
+    names = [v.var_name for v in S.global_variables()]
+    assert names == ["encoder/bidirectional_rnn/fw/lstm_cell/kernel", "encoder/bidirectional_rnn/fw/lstm_cell/bias",
+                     "encoder/bidirectional_rnn/bw/lstm_cell/kernel", "encoder/bidirectional_rnn/bw/lstm_cell/bias"]
+    for v in S.global_variables():
+        v.assign_value(rng.uniform(-0.5, 0.5, size=v.value.shape).astype(np.float32))
+    got_f, got_b, (cfin, hfin), (cbin, hbin) = _run([of, ob, sf, sb])
+    lstm = torch.nn.LSTM(E, H, batch_first=True, bidirectional=True)
+    perm = np.concatenate([np.arange(0, H), np.arange(2 * H, 3 * H), np.arange(H, 2 * H), np.arange(3 * H, 4 * H)])   # TF i,j,f,o -> torch i,f,g,o
+    with torch.no_grad():
+        for cell, sfx in ((cf, ""), (cb, "_reverse")):
+            k, b = cell._kernel.value, cell._bias.value.copy()
+            b[2 * H:3 * H] += 1.0                                      # forget_bias
+            getattr(lstm, "weight_ih_l0" + sfx).copy_(torch.from_numpy(k[:E].T[perm].copy()))
+            getattr(lstm, "weight_hh_l0" + sfx).copy_(torch.from_numpy(k[E:].T[perm].copy()))
+            getattr(lstm, "bias_ih_l0" + sfx).copy_(torch.from_numpy(b[perm].copy()))
+            getattr(lstm, "bias_hh_l0" + sfx).zero_()
+        packed = torch.nn.utils.rnn.pack_padded_sequence(torch.from_numpy(x), torch.from_numpy(lens.astype(np.int64)), batch_first=True)
+        out, (hn, cn) = lstm(packed)
+        out, _ = torch.nn.utils.rnn.pad_packed_sequence(out, batch_first=True, total_length=T)
+    np.testing.assert_allclose(np.concatenate([got_f, got_b], axis=2), out.numpy(), atol=2e-6)
+    np.testing.assert_allclose(hfin, hn[0].numpy(), atol=2e-6)
+    np.testing.assert_allclose(cfin, cn[0].numpy(), atol=2e-6)
+    np.testing.assert_allclose(hbin, hn[1].numpy(), atol=2e-6)
+    np.testing.assert_allclose(cbin, cn[1].numpy(), atol=2e-6)
+
+
+def test_shim_pointwise_ops_match_torch():
+    S.reset_default_graph()
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((4, 9)).astype(np.float32) * 3
+    np.testing.assert_allclose(_run(S.softmax(S.convert_to_tensor(x))), torch.softmax(torch.from_numpy(x), -1).numpy(), atol=1e-7)
+    np.testing.assert_allclose(_run(S.sigmoid(S.convert_to_tensor(x))), torch.sigmoid(torch.from_numpy(x)).numpy(), atol=1e-7)
+    # top_k: descending, lower index first among equal values
+    y = np.array([[1., 3., 3., 0., 3.], [2., 2., 2., 2., 2.]], np.float32)
+    v, i = _run(list(S.top_k(S.convert_to_tensor(y), 4)))
+    assert i.tolist() == [[1, 2, 4, 0], [0, 1, 2, 3]] and v.tolist() == [[3, 3, 3, 1], [2, 2, 2, 2]]
+    # scatter_nd: duplicates accumulate
+    idx = np.array([[[0, 2], [0, 2], [0, 0]], [[1, 1], [1, 3], [1, 1]]], np.int32)
+    upd = np.array([[1., 2., 4.], [8., 16., 32.]], np.float32)
+    got = _run(S.scatter_nd(S.convert_to_tensor(idx), S.convert_to_tensor(upd), [2, S.convert_to_tensor(np.int32(4))]))
+    want = torch.zeros(2, 4).index_put_((torch.from_numpy(idx[..., 0].astype(np.int64)), torch.from_numpy(idx[..., 1].astype(np.int64))),
+                                        torch.from_numpy(upd), accumulate=True)
+    assert got.tolist() == want.tolist() == [[4, 0, 3, 0], [0, 40, 0, 16]]
+    # conv2d with a 1 x 1 filter, NHWC
+    a = rng.standard_normal((2, 6, 1, 5)).astype(np.float32)
+    w = rng.standard_normal((1, 1, 5, 3)).astype(np.float32)
+    got = _run(S.conv2d(S.convert_to_tensor(a), S.convert_to_tensor(w), [1, 1, 1, 1], "SAME"))
+    want = torch.nn.functional.conv2d(torch.from_numpy(a).permute(0, 3, 1, 2), torch.from_numpy(w).permute(3, 2, 0, 1)).permute(0, 2, 3, 1)
+    np.testing.assert_allclose(got, want.numpy(), atol=1e-5)
+
+
+def test_shim_variable_scope_rules():
+    S.reset_default_graph()
+    with S.variable_scope("a") as sc:
+        v = S.get_variable("w", [2])
+        with pytest.raises(ValueError):
+            S.get_variable("w", [2])                                   # duplicate without reuse
+        with S.variable_scope(S.get_variable_scope(), reuse=True):
+            assert S.get_variable("w", [2]) is v
+            with S.variable_scope("inner"):                            # reuse is inherited
+                with pytest.raises(ValueError):
+                    S.get_variable("missing", [1])
+        S.get_variable_scope().reuse_variables()
+        assert S.get_variable("w") is v
+    with S.variable_scope("a"):                                        # entering by name again: reuse is the parent's
+        with pytest.raises(ValueError):
+            S.get_variable("w", [2])
+    with S.variable_scope(sc):
+        assert S.get_variable_scope().name == "a"
+    assert v.var_name == "a/w"
+
+
+def test_shim_session_feeds_intermediate_tensors_and_casts():
+    S.reset_default_graph()
+    p = S.placeholder(S.float32, [2, None], name="p")
+    mid = p * 2.0
+    st = S.LSTMStateTuple(mid + 1.0, mid - 1.0)
+    out = st.c + st.h
+    assert _run(out, {p: np.ones((2, 3))}).dtype == np.float32 and _run(out, {p: np.ones((2, 3))}).tolist() == [[4.0] * 3] * 2
+    # feeding the tuple replaces both leaves; float64 input is cast to the tensors' dtype
+    got = _run(out, {st: S.LSTMStateTuple(np.full((2, 3), 5.0), np.full((2, 3), 7.0))})
+    assert got.dtype == np.float32 and got.tolist() == [[12.0] * 3] * 2
+    with pytest.raises(ValueError):
+        _run(out)                                                      # placeholder not fed
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/main/python/pointer-generator"),
+                    reason="the reference tree exists only in the build container")
+def test_generator_reproduces_the_committed_small_vectors(capsys):
+    """Re-runs the reference's code through the shim and compares with the committed file, bit for bit."""
+    mr = _load("make_reference_golden")
+    saved = dict(sys.modules)
+    try:
+        R = mr.load_reference()
+        _, _, rows, col = mr.small_case(R)
+        got = mr.pack(col, 30, 8)
+    finally:
+        for k in list(sys.modules):
+            if k not in saved and (k.split(".")[0] in ("tensorflow", "nltk", "pyrouge") or k in mr.REF_FILES):
+                del sys.modules[k]
+    r = np.load(os.path.join(HERE, "ref_small.npz"))
+    for k in ("tokens", "lens", "logprobs", "avg", "step_ids", "step_logp", "n_steps"):
+        assert np.array_equal(got[k], r[k]), k
+    assert [x[2] for x in col.rows] == [str(s) for s in r["row_summary"]]
