@@ -111,13 +111,15 @@ class Collect(object):
         self.rows, self.hyps, self.steps, self.batches = [], [], [], []
 
 
-def run_reference(R, W, vocab_path, vsize, hidden, emb, beam, max_enc, max_dec, min_dec, coverage, rows):
+def run_reference(R, W, vocab_path, vsize, hidden, emb, beam, max_enc, max_dec, min_dec, coverage, rows, pointer_gen=True):
     """rows: list of (uuid, article, reference) strings -> Collect.  Everything between the row list and the collected
     (uuid, article, summary, reference) is the reference's code."""
     tf = R["tf"]
     tf.reset_default_graph()
     if not coverage:                                                   # a graph without coverage has no w_c (attention_decoder.py:70-72)
         W = {k: v for k, v in W.items() if not k.endswith("coverage/w_c")}
+    if not pointer_gen:                                                # ... and the baseline model has no p_gen layer (:163-167)
+        W = {k: v for k, v in W.items() if "calculate_pgen" not in k}
     FLAGS = tf.app.flags.FLAGS
     for k, v in FLAG_DEFAULTS.items():
         setattr(FLAGS, k, v)
@@ -126,6 +128,7 @@ def run_reference(R, W, vocab_path, vsize, hidden, emb, beam, max_enc, max_dec, 
     FLAGS.vocab_path, FLAGS.vocab_size, FLAGS.log_root = vocab_path, vsize, log_root
     FLAGS.hidden_dim, FLAGS.emb_dim, FLAGS.beam_size = hidden, emb, beam
     FLAGS.max_enc_steps, FLAGS.max_dec_steps, FLAGS.min_dec_steps, FLAGS.coverage = max_enc, max_dec, min_dec, bool(coverage)
+    FLAGS.pointer_gen = bool(pointer_gen)
     # default_setup (run_summarization.py:294-331)
     vocab = R["data"].Vocab(FLAGS.vocab_path, FLAGS.vocab_size)
     FLAGS.batch_size = FLAGS.beam_size
@@ -153,8 +156,9 @@ def run_reference(R, W, vocab_path, vsize, hidden, emb, beam, max_enc, max_dec, 
         b = inner_next()
         if b is not None:
             col.batches.append(dict(enc_batch=b.enc_batch.copy(), enc_lens=b.enc_lens.copy(), enc_padding_mask=b.enc_padding_mask.copy(),
-                                    enc_batch_extend_vocab=b.enc_batch_extend_vocab.copy(), max_art_oovs=int(b.max_art_oovs),
-                                    art_oovs=list(b.art_oovs[0])))
+                                    enc_batch_extend_vocab=b.enc_batch_extend_vocab.copy() if pointer_gen else b.enc_batch.copy(),
+                                    max_art_oovs=int(b.max_art_oovs) if pointer_gen else 0,
+                                    art_oovs=list(b.art_oovs[0]) if pointer_gen else []))
         return b
     batcher.next_batch = next_batch
 
@@ -278,6 +282,21 @@ def variants_case(R, mg):
         for k in ("tokens", "lens", "logprobs", "avg", "n_steps", "step_ids", "step_logp"):
             out[tag + k] = pk[k]
         out[tag + "summary"] = np.array([r[2] for r in col.rows])
+    # the baseline model (pointer_gen off: OOVs stay [UNK], no copy distribution) and an all-zero model, where every
+    # vocabulary word ties and only the rules decide: tf.nn.top_k takes the lower id first, Python's sorted(...,
+    # reverse=True) keeps equal hypotheses in their original order
+    rows5 = rows
+    col = run_reference(R, mg.small_weights(), vpath, c["V"], c["H"], c["E"], 4, 24, 14, 4, 1, rows5, pointer_gen=False)
+    pk = pack(col, 14, 8)
+    for k in ("tokens", "lens", "logprobs", "avg", "n_steps", "step_ids", "step_logp"):
+        out["nopg_" + k] = pk[k]
+    out["nopg_summary"] = np.array([r[2] for r in col.rows])
+    zero = {k: np.zeros_like(v) for k, v in mg.small_weights().items()}
+    col = run_reference(R, zero, vpath, c["V"], c["H"], c["E"], 4, 24, 8, 3, 1, rows5)
+    pk = pack(col, 8, 8)
+    for k in ("tokens", "lens", "logprobs", "avg", "n_steps", "step_ids", "step_logp"):
+        out["zero_" + k] = pk[k]
+    out["zero_summary"] = np.array([r[2] for r in col.rows])
     rows = [("e-%d" % i, a, "edge reference %d ." % i) for i, a in enumerate(EDGE_ARTICLES)]
     col = run_reference(R, mg.small_weights(), vpath, c["V"], c["H"], c["E"], 4, 24, 30, 8, 1, rows)
     pk = pack(col, 30, 8)
@@ -328,6 +347,15 @@ def main():
         out["row_summary"] = np.array([r[2] for r in col.rows])
         out["variable_names"] = np.array(sorted(col.variables))
         out["variable_shapes"] = np.array([",".join(map(str, col.variables[k])) for k in sorted(col.variables)])
+        # BASELINE.json configs[0] says "random-init weights": W0 = the reference's own initialisers (synth.make_weights)
+        arts0 = synth.make_article_ids(2, seed=4242)
+        rows0 = [("w0-%d" % i, synth.ids_to_article(ext, 50000, salt=i).decode(), "reference %d ." % i) for i, (_, ext, _) in enumerate(arts0)]
+        vpath = os.path.join(tempfile.mkdtemp(prefix="pgen_ref_w0_"), "vocab")
+        synth.write_vocab_file(vpath, 50000)
+        col0 = run_reference(R, synth.make_weights("W0"), vpath, 50000, 256, 128, 4, 400, 100, 35, 1, rows0)
+        pk0 = pack(col0, 100, 8)
+        for k in ("tokens", "lens", "logprobs", "avg"):
+            out["w0_" + k] = pk0[k]
         np.savez_compressed(os.path.join(HERE, "ref_full.npz"), **out)
         print("ref_full.npz: %d rows, summary lengths %s" % (len(col.rows), out["lens"].tolist()))
 

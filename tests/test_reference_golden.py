@@ -56,6 +56,18 @@ def test_reference_run_equals_the_full_size_golden_vectors():
     assert r["tokens"].shape == (4, 100) and int(r["lens"].min()) >= 35
 
 
+def test_oracle_equals_the_reference_run_on_reference_scale_weights():
+    """BASELINE.json configs[0] ("random-init weights"): W0 = the reference's own initialisers at full size.  The
+    vocabulary distribution is then almost flat and the copy distribution decides; one article in the fast oracle mode."""
+    r = np.load(os.path.join(HERE, "ref_full.npz"))
+    a, e, k = synth.make_article_ids(2, seed=4242)[1]
+    hps = O.parse_hyperparams(mg.FULL["flags"])
+    t, l, av = O.decode_ids(synth.make_weights("W0"), hps, a, e, k, mode="dedup")
+    n = int(r["w0_lens"][1])
+    assert t == r["w0_tokens"][1, :n].tolist()
+    np.testing.assert_allclose(np.array(l, np.float32), r["w0_logprobs"][1, :n], rtol=1e-4, atol=1e-5)
+
+
 def test_oracle_follows_the_reference_run_step_by_step(monkeypatch):
     """Every decode_onestep of the reference run (model.py:367-443: top-2K ids and log-probs of all beam rows) against
     the oracle's decode_onestep on the same article, for all 12 articles of the small case."""
@@ -143,6 +155,31 @@ def test_oracle_equals_the_reference_run_across_beam_sizes_and_coverage(beam, co
         np.testing.assert_allclose(np.array(lps, np.float32), v[tag + "logprobs"][b, :n], rtol=0, atol=2e-5)
         assert abs(avg - float(v[tag + "avg"][b])) < 1e-5
         assert int(v[tag + "n_steps"][b]) <= max_dec
+
+
+@pytest.mark.parametrize("mode", ["literal", "dedup"])
+def test_oracle_equals_the_reference_run_without_pointer_gen_and_on_exact_ties(mode):
+    """The baseline model (pointer_gen off: no p_gen layer, no copy distribution, OOVs stay [UNK]) and an all-zero model
+    on which every vocabulary word ties exactly, so that only the rules decide: tf.nn.top_k prefers the lower id,
+    sort_hyps keeps equal hypotheses in their original order (beam_search.py:171-173)."""
+    v = np.load(os.path.join(HERE, "ref_variants.npz"))
+    c = mg.SMALL
+    arts = synth.make_article_ids(5, vsize=c["V"], seed=321, max_len=c["max_len"], oov_rate=0.25)
+    zero = {k: np.zeros_like(x) for k, x in mg.small_weights().items()}
+    cases = [("nopg_", mg.small_weights(), "p --mode=decode --beam_size=4 --coverage=1 --pointer_gen=0 --max_enc_steps=24 --max_dec_steps=14 --min_dec_steps=4"),
+             ("zero_", zero, "p --mode=decode --beam_size=4 --coverage=1 --max_enc_steps=24 --max_dec_steps=8 --min_dec_steps=3")]
+    for tag, W, flags in cases:
+        hps = O.parse_hyperparams(flags)
+        for b, (a, e, k) in enumerate(arts):
+            if tag == "nopg_":
+                e, k = a, 0                                            # batcher.py:66-76: no extended ids without pointer_gen
+            toks, lps, avg = O.decode_ids(W, hps, a, e, k, mode=mode)
+            n = int(v[tag + "lens"][b])
+            assert toks == v[tag + "tokens"][b, :n].tolist(), (tag, b)
+            np.testing.assert_allclose(np.array(lps, np.float32), v[tag + "logprobs"][b, :n], rtol=0, atol=2e-5)
+            assert abs(avg - float(v[tag + "avg"][b])) < 1e-5
+    assert (v["zero_step_logp"][0, 0, 0, 1:4] == v["zero_step_logp"][0, 0, 0, 1]).all()      # exact ties in the fixture
+    assert (np.diff(v["zero_step_ids"][0, 0, 0, 1:4]) > 0).all()                              # ... resolved by id
 
 
 def test_oracle_text_edges_equal_the_reference_run(tmp_path):
