@@ -123,6 +123,21 @@ PGEN_API int pgen_text_encode(pgen_t* h, const char* article, size_t article_len
  * to pgen_text_encode on this handle.  Writes at most cap bytes, returns the full length in *len. */
 PGEN_API int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out, size_t cap, size_t* len);
 
+/* The host text path on a handle of its own, WITHOUT a device: vocabulary (data.py:40-91), article -> ids
+ * (Example.__init__, batcher.py:51-56, 66-68; article2ids, data.py:144-168) and ids -> summary string
+ * (outputids2words, data.py:196-219; decode.py:109-118, 167-182).  For operators that tokenise upstream of the GPU
+ * stage, and for parity tests that need no GPU: tests/test_reference_golden.py holds these calls to what the
+ * reference's own data.py / batcher.py / decode.py produce.  Same code as pgen_text_encode / pgen_text_summary
+ * (csrc/text.cc).  pgen_text_decode_summary refers to the article last passed to pgen_text_encode_article on `t`.
+ * On a failed open *out is NULL and pgen_last_error(NULL) holds the message. */
+typedef struct pgen_text pgen_text_t;
+PGEN_API int pgen_text_open(const char* vocab_path, int64_t vocab_size, int max_enc_steps, pgen_text_t** out);
+PGEN_API int pgen_text_vocab_size(pgen_text_t* t);
+PGEN_API int pgen_text_encode_article(pgen_text_t* t, const char* article, size_t article_len, int32_t* enc_ids,
+                             int32_t* ext_ids, int cap, int32_t* enc_len, int32_t* n_oov);
+PGEN_API int pgen_text_decode_summary(pgen_text_t* t, const int32_t* tokens, int n_tokens, char* out, size_t cap, size_t* len);
+PGEN_API void pgen_text_close(pgen_text_t* t);
+
 /* Tensor-level decode = run_beam_search (beam_search.py:82-168) over run_encoder / decode_onestep
  * (model.py:347-443) for n_articles independent articles, host buffers in and out:
  *   enc_ids, enc_ext_ids  [n_articles, ld]  (row b valid for enc_lens[b] <= max_enc_steps entries)

@@ -208,6 +208,68 @@ def test_oracle_text_edges_equal_the_reference_run(tmp_path):
         np.testing.assert_allclose(np.array(lps, np.float32), v["edge_logprobs"][i, :n], rtol=0, atol=2e-5)
 
 
+def test_library_text_path_equals_the_reference_run(tmp_path):
+    """The PRODUCT's host text path (csrc/text.cc through the C ABI, pgen_text_open / _encode_article / _decode_summary:
+    no GPU needed) against what the reference's data.py / batcher.py / decode.py produced: encoder ids, extended ids, OOV
+    counts, and the summary string of the tokens the reference's beam search returned."""
+    from textsummarization_on_flink_b200 import native
+    r, v = np.load(os.path.join(HERE, "ref_small.npz")), np.load(os.path.join(HERE, "ref_variants.npz"))
+    c = mg.SMALL
+    vpath = str(tmp_path / "vocab")
+    synth.write_vocab_file(vpath, c["V"])
+    with native.TextPath(vpath, c["V"], 24) as tp:
+        assert tp.vocab_size() == c["V"]
+        for i in range(len(r["row_article"])):
+            ids, ext, n_oov = tp.encode(str(r["row_article"][i]).encode())
+            n = int(r["enc_lens"][i])
+            assert ids.tolist() == r["enc_batch"][i, :n].tolist() and ext.tolist() == r["enc_batch_extend_vocab"][i, :n].tolist()
+            assert n_oov == int(r["n_oovs"][i])
+            assert tp.summary(r["tokens"][i, :r["lens"][i]]).decode() == str(r["row_summary"][i])
+        for i, art in enumerate(v["edge_article"]):
+            ids, ext, n_oov = tp.encode(str(art).encode())
+            assert ids.tolist() == [int(x) for x in str(v["edge_enc"][i]).split()]
+            assert ext.tolist() == [int(x) for x in str(v["edge_ext"][i]).split()]
+            assert n_oov == len([w for w in str(v["edge_oovs"][i]).split("\t") if w])
+            assert tp.summary(v["edge_tokens"][i, :v["edge_lens"][i]]).decode() == str(v["edge_summary"][i])
+        # summaries of the other reference runs (same five articles): beam 8 / 3 / 1 / 2 and the all-zero model
+        arts = synth.make_article_ids(5, vsize=c["V"], seed=321, max_len=c["max_len"], oov_rate=0.25)
+        for tag in ("b8c1_", "b3c0_", "b1c1_", "b2c0_", "zero_"):
+            for b, (_, ext, _) in enumerate(arts):
+                tp.encode(synth.ids_to_article(ext, c["V"], salt=b))
+                assert tp.summary(v[tag + "tokens"][b, :v[tag + "lens"][b]]).decode() == str(v[tag + "summary"][b]), (tag, b)
+
+
+def test_library_text_path_equals_the_oracle_on_odd_input(tmp_path):
+    """csrc/text.cc against the (reference-pinned) oracle where the committed vectors do not reach: random articles with
+    many OOVs, empty and blank articles, every ASCII white-space byte, bytes >= 0x80 (Python 2 str.split leaves them
+    alone), random token lists with and without [STOP], ids outside the extended vocabulary."""
+    from textsummarization_on_flink_b200 import native
+    V = 300
+    vpath = str(tmp_path / "vocab")
+    synth.write_vocab_file(vpath, V)
+    vocab = O.Vocab(vpath, V)
+    rng = np.random.default_rng(0)
+    arts = synth.make_articles(40, vsize=V, seed=4, max_len=40, oov_rate=0.3)
+    arts += [b"", b" \t\n", b"article 0.", b"a\tb\nc\rd\x0be\x0cf  g", b"[STOP] [UNK] . , w7 w7 zz zz", b"caf\xc3\xa9 \xa0x\x85y \xff w9",
+             b"w8\x1cw9 \x1d \x1e\x1f"]
+    with native.TextPath(vpath, V, 24) as tp:
+        for a in arts:
+            ids, ext, n_oov = tp.encode(a)
+            ex = O.make_example(a, vocab, 24)
+            assert ids.tolist() == ex.enc_input and ext.tolist() == ex.enc_input_extend_vocab, a
+            assert n_oov == len(ex.article_oovs)
+            hi = V + n_oov
+            toks = [t if t != 3 else 4 for t in rng.integers(0, hi, size=30).tolist()]
+            for cut in (toks, toks[:7] + [3] + toks[7:], [3], [], [4, 4, 3], [4, 7, 4, 4, 9]):
+                want = O.format_summary(O.cut_at_stop(O.outputids2words(cut, vocab, ex.article_oovs)))
+                assert tp.summary(cut) == want
+            with pytest.raises(native.PgenError):
+                tp.summary([hi])
+    with pytest.raises(native.PgenError) as e:
+        native.TextPath(str(tmp_path / "missing"), V, 24)
+    assert e.value.code == 2
+
+
 @pytest.mark.parametrize("name,V,H,E", [("ref_small.npz", 300, 32, 16), ("ref_full.npz", 50000, 256, 128)])
 def test_weight_archive_names_are_the_reference_graphs_variables(name, V, H, E):
     """The reference's graph (built by its own model.py / attention_decoder.py) creates exactly the variables the .pgenw

@@ -291,6 +291,53 @@ int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out,
   return PGEN_OK;
 }
 
+// ---- the host text path on its own handle: no device involved ----
+struct pgen_text {
+  Vocab vocab;
+  int max_enc_steps = 400;
+  EncodedArticle last;
+};
+
+int pgen_text_open(const char* vocab_path, int64_t vocab_size, int max_enc_steps, pgen_text_t** out) {
+  if (!out) return fail(nullptr, PGEN_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  if (!vocab_path) return fail(nullptr, PGEN_ERR_ARG, "vocab_path is NULL");
+  if (vocab_size < 0 || max_enc_steps < 1) return fail(nullptr, PGEN_ERR_ARG, "vocab_size must be >= 0 and max_enc_steps positive");
+  std::unique_ptr<pgen_text> t(new pgen_text());
+  std::string err = t->vocab.load(vocab_path, vocab_size);                                  // run_summarization.py:307
+  if (!err.empty()) return fail(nullptr, PGEN_ERR_IO, err);
+  t->max_enc_steps = max_enc_steps;
+  *out = t.release();
+  return PGEN_OK;
+}
+
+int pgen_text_vocab_size(pgen_text_t* t) { return t ? t->vocab.size() : -1; }
+
+int pgen_text_encode_article(pgen_text_t* t, const char* article, size_t article_len, int32_t* enc_ids, int32_t* ext_ids,
+                             int cap, int32_t* enc_len, int32_t* n_oov) {
+  if (!t || (!article && article_len)) return PGEN_ERR_ARG;
+  encode_article(t->vocab, std::string_view(article ? article : "", article_len), t->max_enc_steps, &t->last);
+  const int n = (int)t->last.enc_ids.size();
+  if (enc_len) *enc_len = n;
+  if (n_oov) *n_oov = (int)t->last.oovs.size();
+  if (n > cap) return fail(nullptr, PGEN_ERR_ARG, "pgen_text_encode_article: cap smaller than the encoded length");
+  if (enc_ids) memcpy(enc_ids, t->last.enc_ids.data(), (size_t)n * 4);
+  if (ext_ids) memcpy(ext_ids, t->last.ext_ids.data(), (size_t)n * 4);
+  return PGEN_OK;
+}
+
+int pgen_text_decode_summary(pgen_text_t* t, const int32_t* tokens, int n_tokens, char* out, size_t cap, size_t* len) {
+  if (!t || (!tokens && n_tokens) || n_tokens < 0) return PGEN_ERR_ARG;
+  std::string s;
+  if (!summary_from_ids(t->vocab, t->last.oovs, tokens, n_tokens, &s))
+    return fail(nullptr, PGEN_ERR_ARG, "token id outside the extended vocabulary of the last encoded article");
+  if (len) *len = s.size();
+  if (out && cap) memcpy(out, s.data(), std::min(cap, s.size()));
+  return PGEN_OK;
+}
+
+void pgen_text_close(pgen_text_t* t) { delete t; }
+
 int pgen_stage_upload(pgen_t* h, int n_articles, const int32_t* enc_ids, const int32_t* enc_ext_ids, int ld,
                       const int32_t* enc_lens, const int32_t* n_oovs) {
   if (!h || n_articles < 0 || (n_articles && (!enc_ids || !enc_ext_ids || !enc_lens))) return h ? fail(h, PGEN_ERR_ARG, "bad arguments") : PGEN_ERR_ARG;

@@ -17,7 +17,8 @@ EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_st
            "pgen_debug_fetch", "pgen_set_option", "pgen_attention",
            "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot",
            "pgen_example_parse", "pgen_example_write", "pgen_submit_example", "pgen_device_count",
-           "pgen_debug_where"]
+           "pgen_debug_where", "pgen_text_open", "pgen_text_vocab_size", "pgen_text_encode_article",
+           "pgen_text_decode_summary", "pgen_text_close"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -91,6 +92,12 @@ def lib() -> C.CDLL:
         L.pgen_attention.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
         L.pgen_debug_vocab_logits.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.pgen_attention_static.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7
+        L.pgen_text_open.argtypes = [C.c_char_p, C.c_int64, C.c_int, C.POINTER(C.c_void_p)]
+        L.pgen_text_vocab_size.argtypes = [C.c_void_p]
+        L.pgen_text_encode_article.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, i32p, i32p, C.c_int, i32p, i32p]
+        L.pgen_text_decode_summary.argtypes = [C.c_void_p, i32p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.pgen_text_close.argtypes = [C.c_void_p]
+        L.pgen_text_close.restype = None
         _lib = L
     return _lib
 
@@ -140,6 +147,57 @@ def example_write(uuid: bytes, article: bytes, summary: bytes, reference: bytes)
     if rc != 0:
         raise PgenError(rc, (lib().pgen_last_error(None) or b"").decode(errors="replace"))
     return out.raw[:n.value]
+
+
+class TextPath:
+    """The library's host text path (csrc/text.cc) on a handle of its own: needs no GPU."""
+
+    def __init__(self, vocab_path: str, vocab_size: int, max_enc_steps: int = 400):
+        self._L = lib()
+        self._t = C.c_void_p()
+        rc = self._L.pgen_text_open(vocab_path.encode(), vocab_size, max_enc_steps, C.byref(self._t))
+        if rc != 0:
+            raise PgenError(rc, (self._L.pgen_last_error(None) or b"").decode(errors="replace"))
+        self.max_enc_steps = max_enc_steps
+
+    def _ck(self, rc: int):
+        if rc != 0:
+            raise PgenError(rc, (self._L.pgen_last_error(None) or b"").decode(errors="replace"))
+
+    def close(self):
+        if self._t:
+            self._L.pgen_text_close(self._t)
+            self._t = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def vocab_size(self) -> int:
+        return int(self._L.pgen_text_vocab_size(self._t))
+
+    def encode(self, article: bytes):
+        """-> (enc ids with OOV -> [UNK], extended ids, number of distinct in-article OOVs)"""
+        cap = self.max_enc_steps
+        ids = np.zeros(cap, np.int32)
+        ext = np.zeros(cap, np.int32)
+        n, k = C.c_int32(), C.c_int32()
+        self._ck(self._L.pgen_text_encode_article(self._t, article, len(article), _p(ids, C.c_int32), _p(ext, C.c_int32), cap,
+                                                   C.byref(n), C.byref(k)))
+        return ids[:n.value].copy(), ext[:n.value].copy(), k.value
+
+    def summary(self, tokens: Sequence[int]) -> bytes:
+        """summary string of decoded token ids, for the article last passed to encode()"""
+        t = np.asarray(tokens, np.int32)
+        ln = C.c_size_t()
+        buf = C.create_string_buffer(64 + 64 * max(1, len(t)))
+        self._ck(self._L.pgen_text_decode_summary(self._t, _p(t, C.c_int32), len(t), buf, len(buf), C.byref(ln)))
+        if ln.value > len(buf):
+            buf = C.create_string_buffer(ln.value)
+            self._ck(self._L.pgen_text_decode_summary(self._t, _p(t, C.c_int32), len(t), buf, len(buf), C.byref(ln)))
+        return buf.raw[:ln.value]
 
 
 class Decoder:
