@@ -311,6 +311,40 @@ def variants_case(R, mg):
     return out
 
 
+# Vocabulary files for data.py:40-75 (ASCII, "\n" line ends only: under Python 3 the reference's open(..., 'r') would also
+# break lines at a lone "\r", which Python 2 did not).  (contents, max_size)
+VOCAB_FILES = [
+    ("a 10\nb 9\nc 8\nd 7\ne 6\nf 5\n", 0),
+    ("a 10\nb 9\nc 8\nd 7\ne 6\nf 5\n", 8),
+    ("a 10\nb 9\nc 8\n", 3),                                     # fewer than the 4 specials: one word is still read
+    ("a 10\nlonely\nb 9 extra\n\n   \nc 8\n", 0),               # 1 field, 3 fields, empty and blank lines are skipped
+    ("a\t10\n  b   9  \nc 8", 0),                                 # tabs, runs of blanks, no newline at the end
+    ("a 10\nb 9\na 8\n", 0),                                      # duplicate
+    ("a 10\nb 9\na 8\n", 6),                                      # ... not reached: reading stops at max_size
+    ("a 10\n[UNK] 9\n", 0),
+    ("a 10\n<s> 9\n", 0),
+    ("a 10\n</s> 9\nb 1\n", 0),
+    ("a 10\n[STOP]\nb 1\n", 0),                                    # a special token on a malformed line is only skipped
+    ("A 10\na 9\n. 8\n, 7\n", 0),                                 # case matters
+]
+
+
+def vocab_case(R):
+    out = []
+    tmp = tempfile.mkdtemp(prefix="pgen_ref_vocab_")
+    for i, (text, max_size) in enumerate(VOCAB_FILES):
+        path = os.path.join(tmp, "vocab%d" % i)
+        with open(path, "w", newline="") as f:
+            f.write(text)
+        try:
+            v = R["data"].Vocab(path, max_size)
+            words = [v.id2word(j) for j in range(v.size())]
+            out.append("ok\t%d\t%s" % (v.size(), " ".join(words)))
+        except Exception as ex:                                          # data.py:65,67 raise plain Exception
+            out.append("error\t%s" % ex)
+    return out
+
+
 def main():
     R = load_reference()
     mg, arts, rows, col = small_case(R)
@@ -339,6 +373,9 @@ def main():
     np.savez_compressed(os.path.join(HERE, "ref_small.npz"), **out)
     print("ref_small.npz: %d rows, summary lengths %s" % (len(col.rows), out["lens"].tolist()))
     var = variants_case(R, mg)
+    var["vocab_file"] = np.array([t for t, _ in VOCAB_FILES])
+    var["vocab_max"] = np.array([m for _, m in VOCAB_FILES], np.int64)
+    var["vocab_outcome"] = np.array(vocab_case(R))
     np.savez_compressed(os.path.join(HERE, "ref_variants.npz"), **var)
     print("ref_variants.npz:", {k: var[k].tolist() for k in var if k.endswith("lens")})
     if "--small-only" not in sys.argv:

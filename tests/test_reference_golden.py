@@ -270,6 +270,40 @@ def test_library_text_path_equals_the_oracle_on_odd_input(tmp_path):
     assert e.value.code == 2
 
 
+def test_vocabulary_files_load_like_the_reference_loads_them(tmp_path):
+    """data.py:40-75 run on twelve crafted vocabulary files (max_size reached, fewer than the specials, malformed /
+    empty lines, tabs, duplicates, reserved tokens): the library's loader (csrc/text.cc through pgen_text_open) and the
+    oracle's agree with the reference on the resulting vocabulary, and fail where it raises -- the library with the
+    reference's own message."""
+    from textsummarization_on_flink_b200 import native
+    v = np.load(os.path.join(HERE, "ref_variants.npz"))
+    assert len(v["vocab_file"]) == 12
+    for i, (text, max_size, outcome) in enumerate(zip(v["vocab_file"], v["vocab_max"], v["vocab_outcome"])):
+        path = str(tmp_path / ("vocab%d" % i))
+        with open(path, "w", newline="") as f:
+            f.write(str(text))
+        kind, rest = str(outcome).split("\t", 1)
+        if kind == "error":
+            with pytest.raises(native.PgenError) as e:
+                native.TextPath(path, int(max_size), 10)
+            assert e.value.code == 2 and str(e.value).endswith(rest), (str(e.value), rest)
+            with pytest.raises(ValueError):
+                O.Vocab(path, int(max_size))
+            continue
+        size, words = rest.split("\t")
+        words = words.split(" ")
+        ov = O.Vocab(path, int(max_size))
+        assert ov.size() == int(size) and [ov.id2word(j).decode() for j in range(ov.size())] == words
+        with native.TextPath(path, int(max_size), 10) as tp:
+            assert tp.vocab_size() == int(size)
+            tp.encode(b"")
+            for j, w in enumerate(words):
+                if j != 3:                                             # [STOP] ends a summary: nothing is printed for it
+                    assert tp.summary([j]).decode() == w
+            ids, ext, n_oov = tp.encode(" ".join(words[4:] + ["zzz"]).encode())
+            assert ids.tolist() == list(range(4, int(size))) + [0] and ext.tolist()[-1] == int(size) and n_oov == 1
+
+
 @pytest.mark.parametrize("name,V,H,E", [("ref_small.npz", 300, 32, 16), ("ref_full.npz", 50000, 256, 128)])
 def test_weight_archive_names_are_the_reference_graphs_variables(name, V, H, E):
     """The reference's graph (built by its own model.py / attention_decoder.py) creates exactly the variables the .pgenw
