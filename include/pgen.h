@@ -123,6 +123,13 @@ PGEN_API int pgen_text_encode(pgen_t* h, const char* article, size_t article_len
  * to pgen_text_encode on this handle.  Writes at most cap bytes, returns the full length in *len. */
 PGEN_API int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out, size_t cap, size_t* len);
 
+/* The flag parser alone (no handle, no device): parses `hyperparams` the way pgen_create does -- the flag table of
+ * run_summarization.py:48-88 (names, types, defaults), token 0 a dummy program name, unknown flags ignored
+ * (known_only=True, :420), --noflag for booleans, batch_size := beam_size in decode mode (:312-313) -- and stores the
+ * value of the integer or boolean flag `name` in *value.  PGEN_ERR_ARG for a malformed string (message via
+ * pgen_last_error(NULL)) or a name that is not an integer / boolean flag. */
+PGEN_API int pgen_parse_flag(const char* hyperparams, const char* name, int64_t* value);
+
 /* The host text path on a handle of its own, WITHOUT a device: vocabulary (data.py:40-91), article -> ids
  * (Example.__init__, batcher.py:51-56, 66-68; article2ids, data.py:144-168) and ids -> summary string
  * (outputids2words, data.py:196-219; decode.py:109-118, 167-182).  For operators that tokenise upstream of the GPU

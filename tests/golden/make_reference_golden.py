@@ -345,6 +345,21 @@ def vocab_case(R):
     return out
 
 
+def flag_table():
+    """The tf.app.flags.DEFINE_* statements of run_summarization.py:47-87, EXECUTED (not re-typed) against a recorder."""
+    src = open(os.path.join(PG, "run_summarization.py")).read()
+    stmts = re.findall(r"^tf\.app\.flags\.DEFINE_\w+\(.*\)$", src, flags=re.M)
+    table = []
+
+    class Rec(object):
+        def __getattr__(self, kind):
+            return lambda name, default, doc: table.append((kind.replace("DEFINE_", ""), name, default))
+    tf = types.SimpleNamespace(app=types.SimpleNamespace(flags=Rec()))
+    for st in stmts:
+        exec(st, {"tf": tf})
+    return table
+
+
 def main():
     R = load_reference()
     mg, arts, rows, col = small_case(R)
@@ -376,6 +391,11 @@ def main():
     var["vocab_file"] = np.array([t for t, _ in VOCAB_FILES])
     var["vocab_max"] = np.array([m for _, m in VOCAB_FILES], np.int64)
     var["vocab_outcome"] = np.array(vocab_case(R))
+    ft = flag_table()
+    assert {n: d for _, n, d in ft} == FLAG_DEFAULTS, "FLAG_DEFAULTS above and run_summarization.py differ"
+    var["flag_kind"] = np.array([k for k, _, _ in ft])
+    var["flag_name"] = np.array([n for _, n, _ in ft])
+    var["flag_default"] = np.array([repr(d) for _, _, d in ft])
     np.savez_compressed(os.path.join(HERE, "ref_variants.npz"), **var)
     print("ref_variants.npz:", {k: var[k].tolist() for k in var if k.endswith("lens")})
     if "--small-only" not in sys.argv:

@@ -304,6 +304,36 @@ def test_vocabulary_files_load_like_the_reference_loads_them(tmp_path):
             assert ids.tolist() == list(range(4, int(size))) + [0] and ext.tolist()[-1] == int(size) and n_oov == 1
 
 
+def test_flag_table_is_the_references():
+    """The 27 tf.app.flags.DEFINE_* statements of run_summarization.py:47-87, executed by the generator: names, kinds and
+    defaults against the oracle's table and against the library's parser (pgen_parse_flag: no device needed)."""
+    import ast
+    from textsummarization_on_flink_b200 import native
+    v = np.load(os.path.join(HERE, "ref_variants.npz"))
+    ref = {str(n): (str(k), ast.literal_eval(str(d))) for k, n, d in zip(v["flag_kind"], v["flag_name"], v["flag_default"])}
+    assert len(ref) == 27
+    kinds = {"string": str, "integer": int, "boolean": bool, "float": float}
+    assert {n: (kinds[k], d) for n, (k, d) in ref.items()} == O._FLAG_DEFAULTS
+    for name, (kind, default) in ref.items():
+        if kind in ("integer", "boolean"):
+            assert native.parse_flag("prog", name) == int(default), name
+            if kind == "boolean":
+                assert native.parse_flag("prog --%s" % name, name) == 1 and native.parse_flag("prog --no%s" % name, name) == 0
+                assert native.parse_flag("prog --%s=false" % name, name) == 0 and native.parse_flag("prog --%s=1" % name, name) == 1
+            else:
+                assert native.parse_flag("prog --%s=7 --unknown_flag=3" % name, name) == 7
+        else:
+            with pytest.raises(native.PgenError):
+                native.parse_flag("prog", name)
+    # default_setup (run_summarization.py:312-313): decode mode overwrites batch_size with beam_size; token 0 is a program name
+    assert native.parse_flag("prog --mode=decode --batch_size=16 --beam_size=5", "batch_size") == 5
+    assert native.parse_flag("prog --mode=train --batch_size=16 --beam_size=5", "batch_size") == 16
+    assert native.parse_flag("--beam_size=9 --beam_size=6", "beam_size") == 6
+    assert O.parse_hyperparams("prog --mode=decode --batch_size=16 --beam_size=5")["batch_size"] == 5
+    with pytest.raises(native.PgenError):
+        native.parse_flag("prog --beam_size=x", "beam_size")
+
+
 @pytest.mark.parametrize("name,V,H,E", [("ref_small.npz", 300, 32, 16), ("ref_full.npz", 50000, 256, 128)])
 def test_weight_archive_names_are_the_reference_graphs_variables(name, V, H, E):
     """The reference's graph (built by its own model.py / attention_decoder.py) creates exactly the variables the .pgenw

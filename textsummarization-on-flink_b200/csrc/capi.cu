@@ -291,6 +291,17 @@ int pgen_text_summary(pgen_t* h, const int32_t* tokens, int n_tokens, char* out,
   return PGEN_OK;
 }
 
+int pgen_parse_flag(const char* hyperparams, const char* name, int64_t* value) {
+  if (!hyperparams || !name || !value) return fail(nullptr, PGEN_ERR_ARG, "NULL argument");
+  HyperParams hp;
+  std::string err = parse_hyperparams(hyperparams, &hp);
+  if (!err.empty()) return fail(nullptr, PGEN_ERR_ARG, err);
+  const int64_t v = flag_int(hp, name);
+  if (v == -1 && std::string(name) != "flush_ms") return fail(nullptr, PGEN_ERR_ARG, std::string("not an integer or boolean flag: ") + name);
+  *value = v;
+  return PGEN_OK;
+}
+
 // ---- the host text path on its own handle: no device involved ----
 struct pgen_text {
   Vocab vocab;

@@ -18,7 +18,7 @@ EXPORTS = ["pgen_create", "pgen_submit", "pgen_poll", "pgen_rows_free", "pgen_st
            "pgen_attention_static", "pgen_debug_vocab_logits", "pgen_stage_slot",
            "pgen_example_parse", "pgen_example_write", "pgen_submit_example", "pgen_device_count",
            "pgen_debug_where", "pgen_text_open", "pgen_text_vocab_size", "pgen_text_encode_article",
-           "pgen_text_decode_summary", "pgen_text_close"]
+           "pgen_text_decode_summary", "pgen_text_close", "pgen_parse_flag"]
 
 ERR_NAMES = {1: "PGEN_ERR_ARG", 2: "PGEN_ERR_IO", 3: "PGEN_ERR_CUDA", 4: "PGEN_ERR_STATE", 5: "PGEN_ERR_UNSUPPORTED"}
 
@@ -98,8 +98,18 @@ def lib() -> C.CDLL:
         L.pgen_text_decode_summary.argtypes = [C.c_void_p, i32p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.pgen_text_close.argtypes = [C.c_void_p]
         L.pgen_text_close.restype = None
+        L.pgen_parse_flag.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
         _lib = L
     return _lib
+
+
+def parse_flag(hyperparams: str, name: str) -> int:
+    """Value of an integer / boolean flag as pgen_create would parse it (no device needed)."""
+    v = C.c_int64()
+    rc = lib().pgen_parse_flag(hyperparams.encode(), name.encode(), C.byref(v))
+    if rc != 0:
+        raise PgenError(rc, (lib().pgen_last_error(None) or b"").decode(errors="replace"))
+    return int(v.value)
 
 
 def device_count() -> int:
