@@ -1,0 +1,237 @@
+"""Host logic of libpgen_cuda.so (csrc/capi.cu, csrc/engine.cu) on the CPU: the library's own objects (csrc/build/*.o,
+unmodified) linked against a TEST DOUBLE of the CUDA runtime (tests/fake_cuda/fake_cudart.c: "device" memory is zeroed
+host memory, copies are memcpy, kernel and graph launches do nothing, any CUDA call can be told to fail).  Nothing is
+decoded -- every summary comes back empty -- so this says nothing about kernels or parity; it covers what the GPU tests
+cannot or do not: the row state machine (batching, slots, order, flush deadline, the stage API being refused while
+rows are in flight) and, above all, the ERROR paths: a failing CUDA call must surface as PGEN_ERR_CUDA and must not
+lose rows (MLMapFunction.flatMap's contract: every row that went in comes out)."""
+import ctypes as C
+import importlib.util
+import os
+import subprocess
+import time
+
+import numpy as np
+import pytest
+
+from conftest import small_flags
+from textsummarization_on_flink_b200 import native as real_native
+from textsummarization_on_flink_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "textsummarization-on-flink_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def fake(tmp_path_factory):
+    """-> (native module bound to the fake-runtime build, the fake runtime's control functions)"""
+    objs = sorted(os.path.join(CSRC, "build", f) for f in os.listdir(os.path.join(CSRC, "build")) if f.endswith(".o"))
+    assert len(objs) >= 9, "run __graft_entry__.build() first"
+    d = tmp_path_factory.mktemp("fake_cuda")
+    fo, so = str(d / "fake_cudart.o"), str(d / "libpgen_fake.so")
+    for cmd in (["gcc", "-c", "-fPIC", "-O1", "-I/usr/local/cuda/include", os.path.join(ROOT, "tests", "fake_cuda", "fake_cudart.c"), "-o", fo],
+                ["g++", "-shared", "-Wl,-Bsymbolic", "-o", so] + objs + [fo, "-lpthread"]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    spec = importlib.util.spec_from_file_location("native_on_fake_cuda", real_native.__file__)
+    nat = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(nat)
+    nat.LIB_PATH = so
+    L = nat.lib()
+    L.fake_cuda_fail.argtypes = [C.c_char_p, C.c_int]
+    for f in ("fake_cuda_launches", "fake_cuda_graph_launches", "fake_cuda_live_allocs"):
+        getattr(L, f).restype = C.c_long
+    L.fake_cuda_set_devices(2)
+    return nat, L
+
+
+def _flags(small_model_dir, small_cfg, extra):
+    return small_flags(small_model_dir, small_cfg, extra=extra)
+
+
+def _articles(n, V):
+    return synth.make_articles(n, vsize=V, seed=77, max_len=24, oov_rate=0.1)
+
+
+def test_rows_come_back_in_order_with_partial_batches_and_slot_rotation(fake, small_cfg, small_model_dir):
+    nat, L = fake
+    arts = _articles(23, small_cfg["V"])
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=4 --slots=2 --flush_ms=-1")) as dec:
+        out = []
+        for i, a in enumerate(arts):
+            dec.submit(b"u%d" % i, a, b"ref %d" % i)
+            out += dec.poll()
+        assert len(out) >= 12                      # full batches came back without any flush
+        out += dec.poll(flush=True)               # 23 = 5 x 4 + 3: the partial batch needs the flush
+        st = dec.stats()
+    assert [r[0] for r in out] == [b"u%d" % i for i in range(23)]
+    assert [r[1] for r in out] == arts and [r[3] for r in out] == [b"ref %d" % i for i in range(23)]
+    assert all(r[2] == b"" for r in out)          # the test double decodes nothing
+    assert st["rows_in"] == st["rows_out"] == 23 and st["batches"] == 6 and st["kernel_launches"] > 0
+    assert L.fake_cuda_launches() > 0 and L.fake_cuda_graph_launches() > 0
+
+
+def test_flush_deadline_and_no_deadline(fake, small_cfg, small_model_dir):
+    nat, _ = fake
+    art = _articles(1, small_cfg["V"])[0]
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=8 --flush_ms=30")) as dec:
+        dec.submit(b"lone", art, b"")
+        assert dec.poll() == []                    # deadline not reached
+        time.sleep(0.05)
+        got = dec.poll() or dec.poll()             # the deadline launches the partial batch; it is finished at once here
+        assert [r[0] for r in got] == [b"lone"]
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=8 --flush_ms=-1")) as dec:
+        dec.submit(b"lone", art, b"")
+        time.sleep(0.05)
+        assert dec.poll() == []                    # flush_ms=-1: only flush=1 (end of input) decodes a partial batch
+        assert [r[0] for r in dec.poll(flush=True)] == [b"lone"]
+
+
+def test_stage_api_refused_while_rows_in_flight(fake, small_cfg, small_model_dir):
+    nat, _ = fake
+    arts = _articles(2, small_cfg["V"])
+    ids = synth.make_article_ids(2, vsize=small_cfg["V"], seed=5, max_len=24)
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=2 --slots=1 --flush_ms=-1")) as dec:
+        for i, a in enumerate(arts):
+            dec.submit(b"u%d" % i, a, b"")         # second row fills the batch: launched on slot 0, in flight
+        with pytest.raises(nat.PgenError) as e:
+            dec.decode_ids(*nat.pack_articles(ids, dec.max_enc_steps))
+        assert e.value.code == 4
+        with pytest.raises(nat.PgenError) as e:
+            dec.set_option("graph=0")
+        assert e.value.code == 4
+        assert len(dec.poll(flush=True)) == 2
+        tok, ln, lp, avg = dec.decode_ids(*nat.pack_articles(ids, dec.max_enc_steps))   # allowed again
+        assert ln.tolist() == [0, 0]
+
+
+@pytest.mark.parametrize("call,after", [("cudaMemcpyAsync", 0), ("cudaMemcpyAsync", 3), ("cudaMemcpyAsync", 9), ("cudaEventRecord", 0),
+                                         ("cudaEventRecord", 2), ("cudaSetDevice", 0), ("cudaStreamSynchronize", 0), ("cudaLaunchKernel", 0),
+                                         ("cudaLaunchKernel", 40), ("cudaGraphLaunch", 0), ("cudaStreamBeginCapture", 0)])
+def test_no_row_is_lost_when_a_cuda_call_fails(fake, small_cfg, small_model_dir, call, after):
+    """A CUDA call fails while a batch is being launched or collected: the call on the handle reports PGEN_ERR_CUDA, and
+    once the fault is gone every row that was submitted still comes out, in order."""
+    nat, L = fake
+    arts = _articles(7, small_cfg["V"])
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=3 --slots=2 --flush_ms=-1")) as dec:
+        out, errors = [], 0
+        L.fake_cuda_fail(call.encode(), after)
+        for i, a in enumerate(arts):
+            try:
+                dec.submit(b"u%d" % i, a, b"")
+            except nat.PgenError as e:
+                assert e.code == 3, e
+                errors += 1
+            try:
+                out += dec.poll()
+            except nat.PgenError as e:
+                assert e.code == 3, e
+                errors += 1
+        L.fake_cuda_fail(None, 0)                  # the fault clears
+        for _ in range(4):
+            try:
+                out += dec.poll(flush=True)
+            except nat.PgenError as e:             # the injected failure may have been armed but not yet consumed
+                assert e.code == 3, e
+                errors += 1
+        st = dec.stats()
+    if call == "cudaStreamBeginCapture":           # by design not an error: the step loop falls back to plain launches
+        assert errors == 0
+    else:
+        assert errors >= 1, "the injected failure never surfaced"
+    assert [r[0] for r in out] == [b"u%d" % i for i in range(7)], (call, after, [r[0] for r in out])
+    assert st["rows_in"] == st["rows_out"] == 7
+
+
+def test_create_fails_cleanly_when_allocation_fails(fake, small_cfg, small_model_dir):
+    nat, L = fake
+    base = L.fake_cuda_live_allocs()
+    for after in (0, 5, 40):
+        L.fake_cuda_fail(b"cudaMalloc", after)
+        with pytest.raises(nat.PgenError) as e:
+            nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=4 --slots=2"))
+        assert e.value.code == 3 and "cudaMalloc" in str(e.value)
+        L.fake_cuda_fail(None, 0)
+        assert L.fake_cuda_live_allocs() == base   # what had been allocated before the failure was freed again
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=4 --slots=2")) as dec:
+        assert dec.flag("slots") == 2
+    assert L.fake_cuda_live_allocs() == base
+
+
+def test_device_ordinals(fake, small_cfg, small_model_dir):
+    nat, L = fake
+    assert nat.device_count() == 2
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=2"), device=1) as dec:
+        assert dec.flag("beam_size") == 4
+    with pytest.raises(nat.PgenError) as e:
+        nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=2"), device=2)
+    assert e.value.code == 1 and "out of range" in str(e.value)
+    L.fake_cuda_set_devices(0)
+    try:
+        with pytest.raises(nat.PgenError) as e:
+            nat.Decoder(_flags(small_model_dir, small_cfg, ""))
+        assert e.value.code == 3 and "no CPU fallback" in str(e.value)
+    finally:
+        L.fake_cuda_set_devices(2)
+
+
+def test_random_traffic_with_random_faults(fake, small_cfg, small_model_dir):
+    """Random submit / poll / flush traffic, random batch and slot counts, a random CUDA call failing at a random moment
+    in every round: whatever happens, rows are never lost, duplicated or reordered."""
+    nat, L = fake
+    rng = np.random.default_rng(2024)
+    pool = _articles(40, small_cfg["V"])
+    calls = [b"cudaMemcpyAsync", b"cudaEventRecord", b"cudaSetDevice", b"cudaStreamSynchronize", b"cudaLaunchKernel", b"cudaGraphLaunch"]
+    for rnd in range(int(os.environ.get("PGEN_FUZZ_ROUNDS", "25"))):
+        apb, slots = int(rng.integers(1, 6)), int(rng.integers(1, 4))
+        with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=%d --slots=%d --flush_ms=-1" % (apb, slots))) as dec:
+            n, out, sent = int(rng.integers(1, 30)), [], 0
+            fault_at = int(rng.integers(0, n))
+            for i in range(n):
+                if i == fault_at:
+                    L.fake_cuda_fail(calls[int(rng.integers(len(calls)))], int(rng.integers(0, 30)))
+                try:
+                    dec.submit(b"r%d-%d" % (rnd, i), pool[i % len(pool)], b"")
+                except nat.PgenError as e:
+                    assert e.code == 3
+                sent += 1                              # a failed launch leaves the row pending: it still counts as accepted
+                if rng.random() < 0.7:
+                    try:
+                        out += dec.poll(flush=bool(rng.random() < 0.2))
+                    except nat.PgenError as e:
+                        assert e.code == 3
+            L.fake_cuda_fail(None, 0)
+            for _ in range(3):
+                try:
+                    out += dec.poll(flush=True)
+                except nat.PgenError as e:
+                    assert e.code == 3
+            assert [r[0] for r in out] == [b"r%d-%d" % (rnd, i) for i in range(sent)], (rnd, apb, slots)
+
+
+def test_two_threads_two_handles(fake, small_cfg, small_model_dir):
+    """Handles are independent: two threads, one handle each (the subtasks of one TaskManager), interleaved at will."""
+    import threading
+    nat, _ = fake
+    arts = _articles(60, small_cfg["V"])
+    results, errors = {}, []
+
+    def work(k):
+        try:
+            with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=4 --slots=2 --flush_ms=-1"), device=k) as dec:
+                out = []
+                for i, a in enumerate(arts):
+                    dec.submit(b"t%d-%d" % (k, i), a, b"")
+                    out += dec.poll()
+                out += dec.poll(flush=True)
+                results[k] = [r[0] for r in out]
+        except Exception as ex:                        # noqa: BLE001
+            errors.append(repr(ex))
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors
+    for k in range(2):
+        assert results[k] == [b"t%d-%d" % (k, i) for i in range(60)]

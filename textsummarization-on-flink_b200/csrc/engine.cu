@@ -217,7 +217,10 @@ std::string Engine::init(const HyperParams& hp, int vocab_size, int device, int*
   std::string err;
   if (share) w_ = share->w_;                       // borrowed device pointers; the owner frees them
   else err = load_weights(wpath);
-  if (!err.empty()) return err;
+  if (!err.empty()) {
+    if (err.find("cudaM") != std::string::npos) *code = PGEN_ERR_CUDA;   // a failed cudaMalloc / cudaMemcpy is not an I/O error
+    return err;
+  }
 
   *code = PGEN_ERR_CUDA;
   const size_t B = Bcap_, T = d_.T, K = d_.K, R = R_, H = d_.H, A = d_.A, E = d_.E, S = d_.S, V = d_.V;
