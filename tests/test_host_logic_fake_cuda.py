@@ -235,3 +235,25 @@ def test_two_threads_two_handles(fake, small_cfg, small_model_dir):
     assert not errors, errors
     for k in range(2):
         assert results[k] == [b"t%d-%d" % (k, i) for i in range(60)]
+
+
+def test_stage_mirror_deals_rows_over_subtasks_and_restores_order(fake, small_cfg, small_model_dir, monkeypatch):
+    """pipeline.TFModel.transform (the Python mirror of TFModel.java:55-81) at worker_num 1, 2 and 3 on two devices: rows
+    are dealt round-robin to the subtasks and come back in input order with the output schema."""
+    from textsummarization_on_flink_b200 import pipeline
+    nat, _ = fake
+    monkeypatch.setattr(pipeline, "native", nat)
+    arts = _articles(11, small_cfg["V"])
+    rows = [{"uuid": "id-%d" % i, "article": a.decode(), "reference": "ref %d" % i, "extra": i} for i, a in enumerate(arts)]
+    hyper = _flags(small_model_dir, small_cfg, "--articles_per_batch=2 --slots=2 --flush_ms=-1").split(" ")
+    for workers in (1, 2, 3):
+        m = (pipeline.TFModel().setWorkerNum(workers).setInferenceHyperParams(hyper)
+             .setInferenceSelectedCols(["uuid", "article", "reference"])
+             .setInferenceOutputCols(["uuid", "article", "summary", "reference"])
+             .setInferenceOutputTypes([pipeline.STRING] * 4))
+        out = list(m.transform(rows, devices=[0, 1]))
+        assert [r["uuid"] for r in out] == [("id-%d" % i).encode() for i in range(11)]
+        assert [r["article"] for r in out] == arts and all(set(r) == {"uuid", "article", "summary", "reference"} for r in out)
+    m.setInferenceHyperParams(["prog", "--mode=train"])
+    with pytest.raises(RuntimeError):                                  # TFModel.java:78-80: failures surface as RuntimeException
+        list(m.transform(rows))
