@@ -257,3 +257,34 @@ def test_stage_mirror_deals_rows_over_subtasks_and_restores_order(fake, small_cf
     m.setInferenceHyperParams(["prog", "--mode=train"])
     with pytest.raises(RuntimeError):                                  # TFModel.java:78-80: failures surface as RuntimeException
         list(m.transform(rows))
+
+
+def test_tf_example_rows_and_json_records_through_the_library(fake, small_cfg, small_model_dir, monkeypatch):
+    """The two wire formats either side of the stage, end to end through the C ABI on the fake runtime: serialized
+    tf.Example in (pgen_submit_example) and out (pgen_example_write), and the demo's JSON Message records through
+    message.transform_messages (App.java:108-131) with its max_count cut-off.  Summaries are empty here; what is checked
+    is that every other field survives the trip, in order."""
+    import json
+    from test_tfexample_codec import Example, pb_example
+    from textsummarization_on_flink_b200 import message, pipeline
+    nat, _ = fake
+    rows = [(b"uuid-%d" % i, b"article %d. w7 w9 . w11" % i, b"reference %d." % i) for i in range(6)]
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=4 --flush_ms=-1")) as dec:
+        for u, a, r in rows:
+            dec.submit_example(pb_example(uuid=u, article=a, reference=r))
+        out = dec.poll(flush=True)
+        with pytest.raises(nat.PgenError):
+            dec.submit_example(pb_example(uuid=b"u", article=b"a"))        # a missing feature (batcher.py:554-557)
+        assert dec.poll(flush=True) == []                                   # ... submits nothing
+    assert [(u, a, r) for u, a, _, r in out] == rows
+    for got in out:
+        ex = Example.FromString(nat.example_write(*got))
+        assert [ex.features.feature[k].bytes_list.value[0] for k in ("uuid", "article", "summary", "reference")] == list(got)
+    monkeypatch.setattr(pipeline, "native", nat)
+    flags = _flags(small_model_dir, small_cfg, "--articles_per_batch=4").split(" ")
+    model = (pipeline.TFModel().setInferenceHyperParams(flags).setInferenceSelectedCols(["uuid", "article", "reference"])
+             .setInferenceOutputCols(["uuid", "article", "summary", "reference"]).setInferenceOutputTypes([pipeline.STRING] * 4))
+    recs = [message.serialize(["uuid-%d" % i, "article %d." % i, "", "reference %d." % i]) for i in range(6)]
+    got = [json.loads(b) for b in message.transform_messages(model, recs, max_count=4)]
+    assert [g["uuid"] for g in got] == ["uuid-%d" % i for i in range(4)]   # records 5 and 6 are past the limit
+    assert all(g["article"] == "article %d." % i and g["reference"] == "reference %d." % i for i, g in enumerate(got))
