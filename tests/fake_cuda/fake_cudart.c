@@ -50,7 +50,18 @@ API cudaError_t cudaFreeHost(void* p) { free(p); return cudaSuccess; }
 API cudaError_t cudaMemset(void* p, int v, size_t n) { memset(p, v, n); return cudaSuccess; }
 API cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t s) { memset(p, v, n); return cudaSuccess; }
 API cudaError_t cudaMemcpy(void* d, const void* s, size_t n, enum cudaMemcpyKind k) { GATE("cudaMemcpy"); memmove(d, s, n); return cudaSuccess; }
-API cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, enum cudaMemcpyKind k, cudaStream_t st) { GATE("cudaMemcpyAsync"); memmove(d, s, n); return cudaSuccess; }
+/* the last host-to-device copies, so that a test can look at what the library uploaded (the "device" is host memory) */
+static struct { void* dst; size_t n; } g_h2d[16];
+static long g_h2d_count = 0;
+API long fake_cuda_h2d_count(void) { return g_h2d_count; }
+API void* fake_cuda_h2d_dst(long back) { return g_h2d[(g_h2d_count - 1 - back) & 15].dst; }
+API size_t fake_cuda_h2d_bytes(long back) { return g_h2d[(g_h2d_count - 1 - back) & 15].n; }
+API cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, enum cudaMemcpyKind k, cudaStream_t st) {
+  GATE("cudaMemcpyAsync");
+  memmove(d, s, n);
+  if (k == cudaMemcpyHostToDevice) { g_h2d[g_h2d_count & 15].dst = d; g_h2d[g_h2d_count & 15].n = n; ++g_h2d_count; }
+  return cudaSuccess;
+}
 API cudaError_t cudaMemcpy2D(void* d, size_t dp, const void* s, size_t sp, size_t w, size_t h, enum cudaMemcpyKind k) {
   for (size_t i = 0; i < h; ++i) memmove((char*)d + i * dp, (const char*)s + i * sp, w);
   return cudaSuccess;

@@ -39,8 +39,10 @@ def fake(tmp_path_factory):
     nat.LIB_PATH = so
     L = nat.lib()
     L.fake_cuda_fail.argtypes = [C.c_char_p, C.c_int]
-    for f in ("fake_cuda_launches", "fake_cuda_graph_launches", "fake_cuda_live_allocs"):
+    for f in ("fake_cuda_launches", "fake_cuda_graph_launches", "fake_cuda_live_allocs", "fake_cuda_h2d_count"):
         getattr(L, f).restype = C.c_long
+    L.fake_cuda_h2d_dst.restype, L.fake_cuda_h2d_dst.argtypes = C.c_void_p, [C.c_long]
+    L.fake_cuda_h2d_bytes.restype, L.fake_cuda_h2d_bytes.argtypes = C.c_size_t, [C.c_long]
     L.fake_cuda_set_devices(2)
     return nat, L
 
@@ -288,3 +290,35 @@ def test_tf_example_rows_and_json_records_through_the_library(fake, small_cfg, s
     got = [json.loads(b) for b in message.transform_messages(model, recs, max_count=4)]
     assert [g["uuid"] for g in got] == ["uuid-%d" % i for i in range(4)]   # records 5 and 6 are past the limit
     assert all(g["article"] == "article %d." % i and g["reference"] == "reference %d." % i for i, g in enumerate(got))
+
+
+def test_uploaded_copy_lists(fake, small_cfg, small_model_dir):
+    """What Engine::upload puts on the device for the copy distribution (model.py:170-176: tf.scatter_nd adds the
+    attention of every position onto its extended id, duplicates accumulating in position order): per article the
+    distinct extended ids ascending, and for each its positions in ascending t.  Read back from the fake device."""
+    nat, L = fake
+    T = 24
+    arts = synth.make_article_ids(5, vsize=small_cfg["V"], seed=31, max_len=T, oov_rate=0.3)
+    arts.append((np.array([7, 7, 7, 0, 7], np.int32), np.array([7, 7, 7, 300, 7], np.int32), 1))
+    arts.append((np.zeros(0, np.int32), np.zeros(0, np.int32), 0))
+    with nat.Decoder(_flags(small_model_dir, small_cfg, "--articles_per_batch=8")) as dec:
+        before = L.fake_cuda_h2d_count()
+        dec.stage_upload(*nat.pack_articles(arts, T))
+        assert L.fake_cuda_h2d_count() - before == 8                 # ids, ext, lens, n_oov, uniq, ucnt, pstart, plist
+        n = len(arts)
+
+        def dev(back, count):
+            assert L.fake_cuda_h2d_bytes(back) == 4 * count
+            return np.frombuffer(C.string_at(L.fake_cuda_h2d_dst(back), 4 * count), np.int32).copy()
+        plist, pstart, ucnt, uniq = dev(0, n * T), dev(1, n * (T + 1)), dev(2, n), dev(3, n * T)
+        noov, lens, ext, ids = dev(4, n), dev(5, n), dev(6, n * T), dev(7, n * T)
+    for b, (a, e, k) in enumerate(arts):
+        assert lens[b] == len(a) and noov[b] == k
+        assert ids[b * T:b * T + len(a)].tolist() == a.tolist() and ext[b * T:b * T + len(a)].tolist() == e.tolist()
+        want_u = sorted(set(e.tolist()))
+        assert ucnt[b] == len(want_u) and uniq[b * T:b * T + len(want_u)].tolist() == want_u
+        ps = pstart[b * (T + 1):b * (T + 1) + len(want_u) + 1].tolist()
+        assert ps[0] == 0 and ps[-1] == len(a)
+        for j, u in enumerate(want_u):
+            pos = plist[b * T + ps[j]:b * T + ps[j + 1]].tolist()
+            assert pos == [t for t in range(len(e)) if e[t] == u]     # ascending t: the order scatter_nd accumulates in
