@@ -90,7 +90,31 @@ API cudaError_t cudaGraphExecDestroy(cudaGraphExec_t ge) { free(ge); return cuda
 
 API cudaError_t cudaFuncSetAttribute(const void* f, enum cudaFuncAttribute a, int v) { return cudaSuccess; }
 API cudaError_t cudaOccupancyMaxActiveClusters(int* n, const void* f, const cudaLaunchConfig_t* c) { *n = 14; return cudaSuccess; }
-API cudaError_t cudaLaunchKernel(const void* f, dim3 g, dim3 b, void** args, size_t smem, cudaStream_t s) { GATE("cudaLaunchKernel"); ++g_launches; return cudaSuccess; }
+/* launch log: which kernel (device-side name from __cudaRegisterFunction), grid, block, dynamic shared memory */
+#define MAX_FUNCS 256
+#define MAX_LOG 8192
+static struct { const void* host; const char* name; } g_funcs[MAX_FUNCS];
+static int g_nfuncs = 0;
+static struct { const char* name; unsigned gx, gy, gz, bx; size_t smem; } g_log[MAX_LOG];
+static long g_nlog = 0;
+API void fake_cuda_log_clear(void) { g_nlog = 0; }
+API long fake_cuda_log_count(void) { return g_nlog < MAX_LOG ? g_nlog : MAX_LOG; }
+API const char* fake_cuda_log_name(long i) { return g_log[i].name; }
+API void fake_cuda_log_dims(long i, unsigned* out5, size_t* smem) {
+  out5[0] = g_log[i].gx; out5[1] = g_log[i].gy; out5[2] = g_log[i].gz; out5[3] = g_log[i].bx; *smem = g_log[i].smem;
+}
+API cudaError_t cudaLaunchKernel(const void* f, dim3 g, dim3 b, void** args, size_t smem, cudaStream_t s) {
+  GATE("cudaLaunchKernel");
+  ++g_launches;
+  if (g_nlog < MAX_LOG) {
+    const char* name = "?";
+    for (int i = 0; i < g_nfuncs; ++i) if (g_funcs[i].host == f) { name = g_funcs[i].name; break; }
+    g_log[g_nlog].name = name; g_log[g_nlog].gx = g.x; g_log[g_nlog].gy = g.y; g_log[g_nlog].gz = g.z; g_log[g_nlog].bx = b.x;
+    g_log[g_nlog].smem = smem;
+  }
+  ++g_nlog;
+  return cudaSuccess;
+}
 
 static int fake_encode_tiled() { return 0; }          /* CUDA_SUCCESS: the tensor map stays zero, nothing reads it */
 API cudaError_t cudaGetDriverEntryPoint(const char* sym, void** fn, unsigned long long flags, enum cudaDriverEntryPointQueryResult* q) {
@@ -107,5 +131,7 @@ static void* g_fatbin_handle;
 API void** __cudaRegisterFatBinary(void* fatbin) { return &g_fatbin_handle; }
 API void __cudaRegisterFatBinaryEnd(void** h) {}
 API void __cudaUnregisterFatBinary(void** h) {}
-API void __cudaRegisterFunction(void** h, const char* hf, char* df, const char* dn, int tl, void* tid, void* bid, void* bd, void* gd, int* ws) {}
+API void __cudaRegisterFunction(void** h, const char* hf, char* df, const char* dn, int tl, void* tid, void* bid, void* bd, void* gd, int* ws) {
+  if (g_nfuncs < MAX_FUNCS) { g_funcs[g_nfuncs].host = hf; g_funcs[g_nfuncs].name = dn; ++g_nfuncs; }
+}
 API void __cudaRegisterVar(void** h, char* hv, char* da, const char* dn, int ext, size_t size, int constant, int global) {}

@@ -25,26 +25,10 @@ CSRC = os.path.join(ROOT, "textsummarization-on-flink_b200", "csrc")
 @pytest.fixture(scope="module")
 def fake(tmp_path_factory):
     """-> (native module bound to the fake-runtime build, the fake runtime's control functions)"""
-    objs = sorted(os.path.join(CSRC, "build", f) for f in os.listdir(os.path.join(CSRC, "build")) if f.endswith(".o"))
-    assert len(objs) >= 9, "run __graft_entry__.build() first"
-    d = tmp_path_factory.mktemp("fake_cuda")
-    fo, so = str(d / "fake_cudart.o"), str(d / "libpgen_fake.so")
-    for cmd in (["gcc", "-c", "-fPIC", "-O1", "-I/usr/local/cuda/include", os.path.join(ROOT, "tests", "fake_cuda", "fake_cudart.c"), "-o", fo],
-                ["g++", "-shared", "-Wl,-Bsymbolic", "-o", so] + objs + [fo, "-lpthread"]):
-        r = subprocess.run(cmd, capture_output=True, text=True)
-        assert r.returncode == 0, r.stderr
-    spec = importlib.util.spec_from_file_location("native_on_fake_cuda", real_native.__file__)
-    nat = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(nat)
-    nat.LIB_PATH = so
-    L = nat.lib()
-    L.fake_cuda_fail.argtypes = [C.c_char_p, C.c_int]
-    for f in ("fake_cuda_launches", "fake_cuda_graph_launches", "fake_cuda_live_allocs", "fake_cuda_h2d_count"):
-        getattr(L, f).restype = C.c_long
-    L.fake_cuda_h2d_dst.restype, L.fake_cuda_h2d_dst.argtypes = C.c_void_p, [C.c_long]
-    L.fake_cuda_h2d_bytes.restype, L.fake_cuda_h2d_bytes.argtypes = C.c_size_t, [C.c_long]
-    L.fake_cuda_set_devices(2)
-    return nat, L
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "fake_cuda"))
+    import build_fake
+    return build_fake.build(str(tmp_path_factory.mktemp("fake_cuda")))
 
 
 def _flags(small_model_dir, small_cfg, extra):
@@ -322,3 +306,41 @@ def test_uploaded_copy_lists(fake, small_cfg, small_model_dir):
         for j, u in enumerate(want_u):
             pos = plist[b * T + ps[j]:b * T + ps[j + 1]].tolist()
             assert pos == [t for t in range(len(e)) if e[t] == u]     # ascending t: the order scatter_nd accumulates in
+
+
+def test_launch_plan_of_a_decode_step(fake, model_dir):
+    """Which kernels a full-size batch launches, in which order and with which grids -- taken from the library itself
+    (the fake runtime logs every cudaLaunchKernel): 8 launches per decode step with the fused decoder cell, 13 with the
+    split path, the grids DESIGN.md section 4 and profiles/r2_summary.md quote."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "fake_cuda"))
+    import build_fake
+    nat, L = fake
+    arts = synth.make_article_ids(64, seed=3, full_len_only=True)
+    plans = {}
+    for mode in ("fused", "split"):
+        flags = synth.hyperparams_string(model_dir, extra="--articles_per_batch=64 --slots=1 --decoder=%s" % mode)
+        with nat.Decoder(flags) as dec:
+            dec.set_option("graph=0")
+            L.fake_cuda_log_clear()
+            dec.stage_upload(*nat.pack_articles(arts, dec.max_enc_steps))
+            dec.stage_run()
+            dec.stage_sync()
+            log = build_fake.launch_log(L)
+        names = [x[0] for x in log]
+        first = names.index("beam_step_kernel")
+        start = max(i for i in range(first) if names[i].startswith("attn_context_kernel")) + 1    # after the step-0 attention pass
+        per_step = names[start:first + 1]
+        assert names[start:start + 100 * len(per_step)] == per_step * 100 and names[start + 100 * len(per_step)] == "finalize_kernel"
+        plans[mode] = (per_step, {x[0]: (x[1], x[2]) for x in log})
+    step, grids = plans["fused"]
+    assert step == ["dec_cell_kernel", "attn_fused_kernel<4>", "attn_merge_kernel", "dec_out_kernel", "vocab_rescore_kernel<4>",
+                    "vocab_tc_kernel<false>", "vocab_final_kernel", "beam_step_kernel"]
+    assert grids["dec_cell_kernel"] == ((128, 1, 1), 576) and grids["attn_fused_kernel<4>"] == ((148, 1, 1), 800)
+    assert grids["attn_merge_kernel"] == ((256, 1, 1), 512) and grids["dec_out_kernel"] == ((8, 16, 1), 544)
+    assert grids["vocab_tc_kernel<false>"] == ((132, 1, 1), 320) and grids["vocab_final_kernel"] == ((256, 1, 1), 512)
+    assert grids["beam_step_kernel"] == ((64, 1, 1), 128) and grids["enc_lstm_persistent_kernel<10>"] == ((8, 2, 7), 512)
+    assert grids["gemm_tc3_kernel"] == ((148, 1, 1), 320)
+    step, grids = plans["split"]
+    assert len(step) == 13 and step.count("gemm_skinny_kernel<8>") + step.count("gemm_skinny_kernel<4>") == 4
+    assert step[0] == "gather_step_kernel" and "attn_fused_kernel<4>" in step and "attn_pack_dfeat_kernel" not in step
