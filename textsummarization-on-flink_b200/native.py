@@ -223,6 +223,7 @@ class Decoder:
         self.max_dec_steps = self.flag("max_dec_steps")
         self.articles_per_batch = self.flag("articles_per_batch")
         self.beam_size = self.flag("beam_size")
+        self._n_staged = 0
 
     def _ck(self, rc: int):
         if rc != 0:
