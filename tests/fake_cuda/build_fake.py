@@ -14,7 +14,10 @@ def build(out_dir):
     objs = sorted(os.path.join(CSRC, "build", f) for f in os.listdir(os.path.join(CSRC, "build")) if f.endswith(".o"))
     assert len(objs) >= 9, "run __graft_entry__.build() first"
     fo, so = os.path.join(out_dir, "fake_cudart.o"), os.path.join(out_dir, "libpgen_fake.so")
-    for cmd in (["gcc", "-c", "-fPIC", "-O1", "-I/usr/local/cuda/include", os.path.join(ROOT, "tests", "fake_cuda", "fake_cudart.c"), "-o", fo],
+    prebuilt = os.environ.get("PGEN_FAKE_LIB")       # e.g. an AddressSanitizer build of the same sources (tools/host_asan.sh)
+    if prebuilt:
+        so = prebuilt
+    for cmd in () if prebuilt else (["gcc", "-c", "-fPIC", "-O1", "-I/usr/local/cuda/include", os.path.join(ROOT, "tests", "fake_cuda", "fake_cudart.c"), "-o", fo],
                 ["g++", "-shared", "-Wl,-Bsymbolic", "-o", so] + objs + [fo, "-lpthread"]):
         r = subprocess.run(cmd, capture_output=True, text=True)
         assert r.returncode == 0, r.stderr

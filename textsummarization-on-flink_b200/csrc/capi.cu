@@ -109,8 +109,10 @@ static int launch_pending(pgen_t* h, size_t n) {
     const EncodedArticle& e = h->pending[b].enc;
     h->b_lens[b] = (int)e.enc_ids.size();
     h->b_noov[b] = (int)e.oovs.size();
-    memcpy(&h->b_ids[b * T], e.enc_ids.data(), e.enc_ids.size() * 4);
-    memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
+    if (!e.enc_ids.empty()) {                                  // (an empty vector's data() may be NULL: no memcpy from it)
+      memcpy(&h->b_ids[b * T], e.enc_ids.data(), e.enc_ids.size() * 4);
+      memcpy(&h->b_ext[b * T], e.ext_ids.data(), e.ext_ids.size() * 4);
+    }
   }
   Engine& e = *h->engs[slot];
   h->where = 41;
@@ -276,8 +278,8 @@ int pgen_text_encode(pgen_t* h, const char* article, size_t article_len, int32_t
   if (enc_len) *enc_len = n;
   if (n_oov) *n_oov = (int)h->last_text.oovs.size();
   if (n > cap) return fail(h, PGEN_ERR_ARG, "pgen_text_encode: cap smaller than the encoded length");
-  if (enc_ids) memcpy(enc_ids, h->last_text.enc_ids.data(), (size_t)n * 4);
-  if (ext_ids) memcpy(ext_ids, h->last_text.ext_ids.data(), (size_t)n * 4);
+  if (enc_ids && n) memcpy(enc_ids, h->last_text.enc_ids.data(), (size_t)n * 4);
+  if (ext_ids && n) memcpy(ext_ids, h->last_text.ext_ids.data(), (size_t)n * 4);
   return PGEN_OK;
 }
 
@@ -332,8 +334,8 @@ int pgen_text_encode_article(pgen_text_t* t, const char* article, size_t article
   if (enc_len) *enc_len = n;
   if (n_oov) *n_oov = (int)t->last.oovs.size();
   if (n > cap) return fail(nullptr, PGEN_ERR_ARG, "pgen_text_encode_article: cap smaller than the encoded length");
-  if (enc_ids) memcpy(enc_ids, t->last.enc_ids.data(), (size_t)n * 4);
-  if (ext_ids) memcpy(ext_ids, t->last.ext_ids.data(), (size_t)n * 4);
+  if (enc_ids && n) memcpy(enc_ids, t->last.enc_ids.data(), (size_t)n * 4);
+  if (ext_ids && n) memcpy(ext_ids, t->last.ext_ids.data(), (size_t)n * 4);
   return PGEN_OK;
 }
 

@@ -77,7 +77,8 @@ std::string read_archive(const std::string& path, std::vector<char>* buf, std::m
     HostTensor t;
     t.dims.resize(ndim);
     if (p + 4 * ndim + 16 > sz) return "truncated weights archive";
-    memcpy(t.dims.data(), buf->data() + p, 4 * ndim); p += 4 * ndim;
+    if (ndim) memcpy(t.dims.data(), buf->data() + p, 4 * ndim);
+    p += 4 * ndim;
     uint64_t off, nb;
     memcpy(&off, buf->data() + p, 8); memcpy(&nb, buf->data() + p + 8, 8); p += 16;
     if (off + nb > sz || off % 4) return "tensor '" + name + "': bad offset";
