@@ -12,9 +12,17 @@
 
 #define API __attribute__((visibility("default")))
 
-static int g_devices = 2, g_device = 0;
+/* like the real runtime: current device, last error and the pending call configuration are per THREAD; the counters
+ * and the logs are shared and updated atomically / under a lock, so that tools/host_tsan.sh reports the library's races,
+ * not this file's */
+#include <pthread.h>
+static int g_devices = 2;
+static __thread int g_device = 0;
 static long g_launches = 0, g_graph_launches = 0, g_live_allocs = 0;
-static cudaError_t g_last = cudaSuccess;
+static __thread cudaError_t g_last = cudaSuccess;
+static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
+#define INC(x) __atomic_add_fetch(&(x), 1, __ATOMIC_RELAXED)
+#define DEC(x) __atomic_sub_fetch(&(x), 1, __ATOMIC_RELAXED)
 static char g_fail_name[64];
 static int g_fail_after = -1;                     /* fail the call after this many more successful calls of that name */
 
@@ -25,10 +33,14 @@ API long fake_cuda_graph_launches(void) { return g_graph_launches; }
 API long fake_cuda_live_allocs(void) { return g_live_allocs; }
 
 static cudaError_t gate(const char* name) {
+  if (__atomic_load_n(&g_fail_after, __ATOMIC_RELAXED) < 0) return cudaSuccess;
+  cudaError_t r = cudaSuccess;
+  pthread_mutex_lock(&g_mu);
   if (g_fail_after >= 0 && strcmp(name, g_fail_name) == 0) {
-    if (g_fail_after-- == 0) { g_last = cudaErrorUnknown; return cudaErrorUnknown; }
+    if (g_fail_after-- == 0) { g_last = cudaErrorUnknown; r = cudaErrorUnknown; }
   }
-  return cudaSuccess;
+  pthread_mutex_unlock(&g_mu);
+  return r;
 }
 #define GATE(name) do { cudaError_t e__ = gate(name); if (e__ != cudaSuccess) return e__; } while (0)
 
@@ -43,8 +55,8 @@ API cudaError_t cudaDeviceGetAttribute(int* v, enum cudaDeviceAttr a, int dev) {
 API cudaError_t cudaGetLastError(void) { cudaError_t e = g_last; g_last = cudaSuccess; return e; }
 API const char* cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "fake CUDA failure"; }
 
-API cudaError_t cudaMalloc(void** p, size_t n) { GATE("cudaMalloc"); *p = calloc(n ? n : 1, 1); ++g_live_allocs; return *p ? cudaSuccess : cudaErrorMemoryAllocation; }
-API cudaError_t cudaFree(void* p) { if (p) { free(p); --g_live_allocs; } return cudaSuccess; }
+API cudaError_t cudaMalloc(void** p, size_t n) { GATE("cudaMalloc"); *p = calloc(n ? n : 1, 1); INC(g_live_allocs); return *p ? cudaSuccess : cudaErrorMemoryAllocation; }
+API cudaError_t cudaFree(void* p) { if (p) { free(p); DEC(g_live_allocs); } return cudaSuccess; }
 API cudaError_t cudaMallocHost(void** p, size_t n) { GATE("cudaMallocHost"); *p = calloc(n ? n : 1, 1); return *p ? cudaSuccess : cudaErrorMemoryAllocation; }
 API cudaError_t cudaFreeHost(void* p) { free(p); return cudaSuccess; }
 API cudaError_t cudaMemset(void* p, int v, size_t n) { memset(p, v, n); return cudaSuccess; }
@@ -59,7 +71,11 @@ API size_t fake_cuda_h2d_bytes(long back) { return g_h2d[(g_h2d_count - 1 - back
 API cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, enum cudaMemcpyKind k, cudaStream_t st) {
   GATE("cudaMemcpyAsync");
   memmove(d, s, n);
-  if (k == cudaMemcpyHostToDevice) { g_h2d[g_h2d_count & 15].dst = d; g_h2d[g_h2d_count & 15].n = n; ++g_h2d_count; }
+  if (k == cudaMemcpyHostToDevice) {
+    pthread_mutex_lock(&g_mu);
+    g_h2d[g_h2d_count & 15].dst = d; g_h2d[g_h2d_count & 15].n = n; ++g_h2d_count;
+    pthread_mutex_unlock(&g_mu);
+  }
   return cudaSuccess;
 }
 API cudaError_t cudaMemcpy2D(void* d, size_t dp, const void* s, size_t sp, size_t w, size_t h, enum cudaMemcpyKind k) {
@@ -84,7 +100,7 @@ API cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEvent_t b) { 
 API cudaError_t cudaStreamBeginCapture(cudaStream_t s, enum cudaStreamCaptureMode m) { GATE("cudaStreamBeginCapture"); return cudaSuccess; }
 API cudaError_t cudaStreamEndCapture(cudaStream_t s, cudaGraph_t* g) { *g = (cudaGraph_t)calloc(1, 8); return cudaSuccess; }
 API cudaError_t cudaGraphInstantiate(cudaGraphExec_t* ge, cudaGraph_t g, unsigned long long flags) { *ge = (cudaGraphExec_t)calloc(1, 8); return cudaSuccess; }
-API cudaError_t cudaGraphLaunch(cudaGraphExec_t ge, cudaStream_t s) { GATE("cudaGraphLaunch"); ++g_graph_launches; return cudaSuccess; }
+API cudaError_t cudaGraphLaunch(cudaGraphExec_t ge, cudaStream_t s) { GATE("cudaGraphLaunch"); INC(g_graph_launches); return cudaSuccess; }
 API cudaError_t cudaGraphDestroy(cudaGraph_t g) { free(g); return cudaSuccess; }
 API cudaError_t cudaGraphExecDestroy(cudaGraphExec_t ge) { free(ge); return cudaSuccess; }
 
@@ -105,7 +121,8 @@ API void fake_cuda_log_dims(long i, unsigned* out5, size_t* smem) {
 }
 API cudaError_t cudaLaunchKernel(const void* f, dim3 g, dim3 b, void** args, size_t smem, cudaStream_t s) {
   GATE("cudaLaunchKernel");
-  ++g_launches;
+  INC(g_launches);
+  pthread_mutex_lock(&g_mu);
   if (g_nlog < MAX_LOG) {
     const char* name = "?";
     for (int i = 0; i < g_nfuncs; ++i) if (g_funcs[i].host == f) { name = g_funcs[i].name; break; }
@@ -113,6 +130,7 @@ API cudaError_t cudaLaunchKernel(const void* f, dim3 g, dim3 b, void** args, siz
     g_log[g_nlog].smem = smem;
   }
   ++g_nlog;
+  pthread_mutex_unlock(&g_mu);
   return cudaSuccess;
 }
 
@@ -124,7 +142,7 @@ API cudaError_t cudaGetDriverEntryPoint(const char* sym, void** fn, unsigned lon
 }
 
 /* what nvcc's host stubs call */
-static struct { dim3 g, b; size_t smem; void* st; } g_cfg;
+static __thread struct { dim3 g, b; size_t smem; void* st; } g_cfg;
 API unsigned __cudaPushCallConfiguration(dim3 g, dim3 b, size_t smem, void* st) { g_cfg.g = g; g_cfg.b = b; g_cfg.smem = smem; g_cfg.st = st; return 0; }
 API cudaError_t __cudaPopCallConfiguration(dim3* g, dim3* b, size_t* smem, void* st) { *g = g_cfg.g; *b = g_cfg.b; *smem = g_cfg.smem; *(void**)st = g_cfg.st; return cudaSuccess; }
 static void* g_fatbin_handle;
