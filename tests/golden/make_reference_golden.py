@@ -4,7 +4,10 @@
 
 The reference's decode path (PG = /root/reference/src/main/python/pointer-generator) is Python 2 + TensorFlow 1.x.  Its
 files are loaded from where they lie (never copied), with three in-memory adjustments so that CPython 3 can run them:
-`print x` statements become calls, `xrange` is `range`, `import Queue` finds `queue`.  `tensorflow` resolves to
+`print x` statements become calls, `xrange` is `range`, `import Queue` finds `queue` (no `/` of two integers occurs on the path).
+One NumPy difference is undone: under NumPy >= 2 a Python float plus a float32 scalar stays float32, under the NumPy 1.x of
+the reference's time it became float64 -- which is how `sum(self.log_probs)` (beam_search.py:72-79) got its float64 sums --
+so decode_onestep's float32 log-probs reach run_beam_search as float64 copies of the same values.  `tensorflow` resolves to
 oracle/tf1_shim.py, a NumPy restatement of the TF 1.11 ops these files call; `nltk` (third party, absent) resolves to a
 two-function stand-in (whitespace tokens, sentences end at "."), `pyrouge` to an empty module.
 
@@ -188,7 +191,10 @@ def run_reference(R, W, vocab_path, vsize, hidden, emb, beam, max_enc, max_dec, 
     def onestep(*a, **k):
         out = real_onestep(*a, **k)
         col.steps[-1].append((np.array(out[0]), np.array(out[1])))
-        return out
+        # NumPy 1.x semantics for beam_search.py:72-79: `sum(self.log_probs)` starts from the Python float 0.0, and the
+        # NumPy the reference ran on added a float32 scalar to it in float64; NumPy >= 2 (NEP 50) would stay in float32.
+        # The same float32 values are therefore handed on as float64, which gives the sums the reference computed.
+        return (out[0], np.asarray(out[1], np.float64)) + tuple(out[2:])
     model.decode_onestep = onestep
     real_search = R["beam_search"].run_beam_search
 
@@ -345,6 +351,46 @@ def vocab_case(R):
     return out
 
 
+def beam_case(R):
+    """run_beam_search / Hypothesis / sort_hyps of the reference (beam_search.py, unmodified) on the deterministic stand-in
+    for decode_onestep of beam_fuzz.py: exact ties everywhere."""
+    import beam_fuzz
+    tf = R["tf"]
+    FLAGS = tf.app.flags.FLAGS
+    LST = tf.contrib.rnn.LSTMStateTuple
+    out_tok, out_lp, out_avg = [], [], []
+    for case in beam_fuzz.CASES:
+        FLAGS.beam_size, FLAGS.min_dec_steps, FLAGS.max_dec_steps = case["K"], case["min_dec"], case["max_dec"]
+        FLAGS.pointer_gen, FLAGS.coverage = True, True
+        K = case["K"]
+
+        class Vocab(object):
+            def size(self): return case["V"]
+            def word2id(self, w): return {"[UNK]": 0, "[PAD]": 1, "[START]": 2, "[STOP]": 3}[w]
+
+        class Model(object):
+            def __init__(self): self.step = 0
+            def run_encoder(self, sess, batch): return np.zeros((K, 5, 2), np.float32), LST(np.zeros(1, np.float32), np.zeros(1, np.float32))
+            def decode_onestep(self, sess, batch, latest_tokens, enc_states, dec_init_states, prev_coverage):
+                assert all(0 <= t < case["V"] for t in latest_tokens)            # OOV ids were mapped to [UNK] (:112-113)
+                ids, logp = beam_fuzz.fake_step(case, self.step)
+                self.step += 1
+                logp = logp.astype(np.float64)                                   # NumPy 1.x promotion, see run_reference
+                return (ids, logp, [dec_init_states[0]] * K, [[0.2] * 5] * K, [0.5] * K, [np.zeros(5)] * K)
+        batch = types.SimpleNamespace(enc_batch=np.zeros((K, 5), np.int32))
+        h = R["beam_search"].run_beam_search(None, Model(), Vocab(), batch)
+        out_tok.append([int(t) for t in h.tokens])
+        out_lp.append([float(x) for x in h.log_probs])
+        out_avg.append(float(h.avg_log_prob))
+    n = max(len(t) for t in out_tok)
+    tok = np.full((len(out_tok), n), -1, np.int32)
+    lp = np.zeros((len(out_tok), n), np.float64)
+    for i, (t, l) in enumerate(zip(out_tok, out_lp)):
+        tok[i, :len(t)] = t
+        lp[i, :len(l)] = l
+    return dict(beam_tokens=tok, beam_logp=lp, beam_avg=np.array(out_avg, np.float64))
+
+
 def flag_table():
     """The tf.app.flags.DEFINE_* statements of run_summarization.py:47-87, EXECUTED (not re-typed) against a recorder."""
     src = open(os.path.join(PG, "run_summarization.py")).read()
@@ -391,6 +437,7 @@ def main():
     var["vocab_file"] = np.array([t for t, _ in VOCAB_FILES])
     var["vocab_max"] = np.array([m for _, m in VOCAB_FILES], np.int64)
     var["vocab_outcome"] = np.array(vocab_case(R))
+    var.update(beam_case(R))
     ft = flag_table()
     assert {n: d for _, n, d in ft} == FLAG_DEFAULTS, "FLAG_DEFAULTS above and run_summarization.py differ"
     var["flag_kind"] = np.array([k for k, _, _ in ft])

@@ -304,6 +304,43 @@ def test_vocabulary_files_load_like_the_reference_loads_them(tmp_path):
             assert ids.tolist() == list(range(4, int(size))) + [0] and ext.tolist()[-1] == int(size) and n_oov == 1
 
 
+def test_beam_bookkeeping_equals_the_references_on_exact_ties(monkeypatch):
+    """160 cases of the reference's run_beam_search / Hypothesis / sort_hyps (beam_search.py, run by the generator) on a
+    deterministic stand-in for decode_onestep whose log-probs are multiples of 0.25: hypotheses tie exactly, so the
+    stable descending sort, the [STOP] / min_dec_steps rule, the single parent of step 0, [UNK] for OOV ids and the
+    results-or-live-hypotheses ending are all that decides.  The oracle's beam search must return the same hypothesis."""
+    bf = _load("beam_fuzz")
+    v = np.load(os.path.join(HERE, "ref_variants.npz"))
+    assert len(bf.CASES) == len(v["beam_tokens"]) == 160
+    ends = {"stop": 0, "live": 0}
+    for n, case in enumerate(bf.CASES):
+        K, V, T = case["K"], case["V"], 5
+        W = {O.N_EMB: np.zeros((V, 2), np.float32)}
+        hps = O.parse_hyperparams("p --mode=decode --beam_size=%d --coverage=1 --max_dec_steps=%d --min_dec_steps=%d"
+                                  % (K, case["max_dec"], case["min_dec"]))
+        step = [0]
+
+        def fake_encoder(W_, ids):
+            return np.zeros((T, 2), np.float32), (np.zeros(1, np.float32), np.zeros(1, np.float32))
+
+        def fake_onestep(W_, hps_, enc_states, feat, mask, ext, n_oov, latest, c, h, cov):
+            assert all(0 <= t < V for t in latest)
+            ids, logp = bf.fake_step(case, step[0])
+            step[0] += 1
+            R = len(latest)
+            return ids, logp, np.zeros((R, 1), np.float32), np.zeros((R, 1), np.float32), np.full((R, T), 0.2, np.float32), \
+                np.full((R,), 0.5, np.float32), np.zeros((R, T), np.float32), None
+        monkeypatch.setattr(O, "run_encoder", fake_encoder)
+        monkeypatch.setattr(O, "decode_onestep", fake_onestep)
+        best = O.run_beam_search(W, hps, [4] * T, [4] * T, case["n_oov"], mode="literal")
+        want = [int(t) for t in v["beam_tokens"][n] if t >= 0]
+        assert [int(t) for t in best.tokens] == want, (n, case)
+        np.testing.assert_allclose([float(x) for x in best.log_probs], v["beam_logp"][n][:len(want)], rtol=0, atol=0)
+        assert best.avg_log_prob == float(v["beam_avg"][n])
+        ends["stop" if want[-1] == 3 else "live"] += 1
+    assert ends["stop"] >= 40 and ends["live"] >= 40
+
+
 def test_flag_table_is_the_references():
     """The 27 tf.app.flags.DEFINE_* statements of run_summarization.py:47-87, executed by the generator: names, kinds and
     defaults against the oracle's table and against the library's parser (pgen_parse_flag: no device needed)."""
