@@ -59,8 +59,10 @@ API cudaError_t cudaMalloc(void** p, size_t n) { GATE("cudaMalloc"); *p = calloc
 API cudaError_t cudaFree(void* p) { if (p) { free(p); DEC(g_live_allocs); } return cudaSuccess; }
 API cudaError_t cudaMallocHost(void** p, size_t n) { GATE("cudaMallocHost"); *p = calloc(n ? n : 1, 1); return *p ? cudaSuccess : cudaErrorMemoryAllocation; }
 API cudaError_t cudaFreeHost(void* p) { free(p); return cudaSuccess; }
+static int g_skip_async_memset = 0;               /* for timing the HOST cost of a batch: device-side fills cost the host nothing */
+API void fake_cuda_skip_async_memset(int on) { g_skip_async_memset = on; }
 API cudaError_t cudaMemset(void* p, int v, size_t n) { memset(p, v, n); return cudaSuccess; }
-API cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t s) { memset(p, v, n); return cudaSuccess; }
+API cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t s) { if (!g_skip_async_memset) memset(p, v, n); return cudaSuccess; }
 API cudaError_t cudaMemcpy(void* d, const void* s, size_t n, enum cudaMemcpyKind k) { GATE("cudaMemcpy"); memmove(d, s, n); return cudaSuccess; }
 /* the last host-to-device copies, so that a test can look at what the library uploaded (the "device" is host memory) */
 static struct { void* dst; size_t n; } g_h2d[16];

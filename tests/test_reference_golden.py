@@ -268,6 +268,27 @@ def test_library_text_path_equals_the_oracle_on_odd_input(tmp_path):
     with pytest.raises(native.PgenError) as e:
         native.TextPath(str(tmp_path / "missing"), V, 24)
     assert e.value.code == 2
+    # many distinct OOVs in one article (BASELINE configs[3]: 200), repeated in random order; long words that share their
+    # first eight bytes with vocabulary words and with each other
+    many = synth.make_articles(6, vsize=V, seed=8, max_len=400, fixed_oovs=200)
+    many.append(b" ".join(b"prefix__%d" % (i % 37) for i in range(300)) + b" w12345678 w1234567 w123456789 w12")
+    with native.TextPath(vpath, V, 400) as tp:
+        for a in many:
+            ids, ext, n_oov = tp.encode(a)
+            ex = O.make_example(a, vocab, 400)
+            assert ids.tolist() == ex.enc_input and ext.tolist() == ex.enc_input_extend_vocab and n_oov == len(ex.article_oovs)
+            toks = list(range(V, V + n_oov))
+            assert tp.summary(toks) == O.format_summary(O.outputids2words(toks, vocab, ex.article_oovs))
+    assert n_oov == 37 + 3
+    long_vocab = str(tmp_path / "long_vocab")
+    with open(long_vocab, "w") as f:
+        f.write("".join("%s 1\n" % w for w in ("abcdefgh", "abcdefghi", "abcdefghj", "abcdefghij", "abcdefg", "x" * 40, "x" * 39 + "y")))
+    lv = O.Vocab(long_vocab, 0)
+    with native.TextPath(long_vocab, 0, 50) as tp:
+        a = b"abcdefgh abcdefghi abcdefghj abcdefghij abcdefg abcdefghk abcdefghijk " + b"x" * 40 + b" " + b"x" * 39 + b"y " + b"x" * 39 + b"z"
+        ids, ext, n_oov = tp.encode(a)
+        ex = O.make_example(a, lv, 50)
+        assert ids.tolist() == ex.enc_input == [4, 5, 6, 7, 8, 0, 0, 9, 10, 0] and ext.tolist() == ex.enc_input_extend_vocab and n_oov == 3
 
 
 def test_vocabulary_files_load_like_the_reference_loads_them(tmp_path):

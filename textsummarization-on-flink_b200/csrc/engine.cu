@@ -466,7 +466,7 @@ std::string Engine::upload(int n, const int32_t* enc_ids, const int32_t* ext_ids
   const int T = d_.T;
   nB_ = n;
   max_len_ = 0;
-  std::vector<std::pair<int, int>> tmp;
+  std::vector<uint64_t> keys;                          // (extended id << 32) | position: sorting groups ids, positions ascending
   for (int b = 0; b < n; ++b) {
     const int len = lens[b];
     if (len < 0 || len > T || len > ld) return "enc_lens[" + std::to_string(b) + "] outside 0..max_enc_steps";
@@ -476,25 +476,27 @@ std::string Engine::upload(int n, const int32_t* enc_ids, const int32_t* ext_ids
     max_len_ = std::max(max_len_, len);
     int32_t* hi = h_ids_ + (size_t)b * T;
     int32_t* he = h_ext_ + (size_t)b * T;
-    tmp.clear();
+    keys.resize((size_t)len);
+    const int vext = d_.V + no;
     for (int t = 0; t < len; ++t) {
       const int id = enc_ids[(size_t)b * ld + t], ex = ext_ids[(size_t)b * ld + t];
       if (id < 0 || id >= d_.V) return "enc_ids out of range";
-      if (ex < 0 || ex >= d_.V + no) return "enc_ext_ids outside the extended vocabulary";
+      if (ex < 0 || ex >= vext) return "enc_ext_ids outside the extended vocabulary";
       hi[t] = id; he[t] = ex;
-      tmp.emplace_back(ex, t);
+      keys[(size_t)t] = ((uint64_t)(uint32_t)ex << 32) | (uint32_t)t;
     }
     for (int t = len; t < T; ++t) { hi[t] = 0; he[t] = 0; }
     // unique extended ids (ascending) with their positions in ascending t: the order in which
     // tf.scatter_nd accumulates duplicates (model.py:170-176)
-    std::sort(tmp.begin(), tmp.end());
+    std::sort(keys.begin(), keys.end());
     int32_t* hu = h_uniq_ + (size_t)b * T;
     int32_t* hs = h_pstart_ + (size_t)b * (T + 1);
     int32_t* hp = h_plist_ + (size_t)b * T;
     int nu = 0;
     for (int q = 0; q < len; ++q) {
-      if (q == 0 || tmp[q].first != tmp[q - 1].first) { hu[nu] = tmp[q].first; hs[nu] = q; ++nu; }
-      hp[q] = tmp[q].second;
+      const int ex = (int)(keys[(size_t)q] >> 32);
+      if (q == 0 || ex != (int)(keys[(size_t)q - 1] >> 32)) { hu[nu] = ex; hs[nu] = q; ++nu; }
+      hp[q] = (int)(uint32_t)keys[(size_t)q];
     }
     hs[nu] = len;
     h_ucnt_[b] = nu;

@@ -1,5 +1,6 @@
 #include "text.h"
 
+#include <algorithm>
 #include <cerrno>
 #include <cstdlib>
 #include <cstring>
@@ -8,9 +9,12 @@
 namespace pgn {
 namespace {
 
-inline bool is_space(unsigned char c) {   // bytes.split(): ASCII whitespace
-  return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\v' || c == '\f';
-}
+struct SpaceTable {                        // bytes.split(): ASCII whitespace = space, \t, \n, \r, \v, \f
+  bool is[256] = {};
+  constexpr SpaceTable() { is[(int)' '] = is[(int)'\t'] = is[(int)'\n'] = is[(int)'\r'] = is[(int)'\v'] = is[(int)'\f'] = true; }
+};
+constexpr SpaceTable kSpace;
+inline bool is_space(unsigned char c) { return kSpace.is[c]; }
 
 template <class F>
 void for_each_word(std::string_view s, F&& f) {
@@ -121,13 +125,38 @@ int64_t flag_int(const HyperParams& hp, const std::string& name) {
   return -1;
 }
 
+bool Vocab::contains(std::string_view w) const {
+  if (slots_.empty()) return false;
+  const uint64_t pre = prefix8(w);
+  for (size_t i = (size_t)(mix(pre, w.size()) & mask_);; i = (i + 1) & mask_) {
+    const Slot& s = slots_[i];
+    if (s.id < 0) return false;
+    if (s.prefix == pre && s.len == (uint32_t)w.size() && words_[s.id] == w) return true;
+  }
+}
+
+void Vocab::insert(int id) {
+  const std::string& w = words_[id];
+  const uint64_t pre = prefix8(w);
+  size_t i = (size_t)(mix(pre, w.size()) & mask_);
+  while (slots_[i].id >= 0) i = (i + 1) & mask_;
+  slots_[i] = Slot{pre, (uint32_t)w.size(), id};
+}
+
+void Vocab::rehash(size_t n_slots) {
+  slots_.assign(n_slots, Slot{0, 0, -1});
+  mask_ = n_slots - 1;
+  for (int id = 0; id < (int)words_.size(); ++id) insert(id);
+}
+
 std::string Vocab::load(const std::string& path, int64_t max_size) {
   words_.clear();
-  map_.clear();
   warnings_ = 0;
+  rehash(1024);
   auto add = [&](std::string w) {
     words_.push_back(std::move(w));
-    map_.emplace(std::string_view(words_.back()), (int)words_.size() - 1);
+    if (words_.size() * 2 > slots_.size()) rehash(slots_.size() * 4);       // load factor <= 1/2
+    else insert((int)words_.size() - 1);
   };
   for (const char* w : {"[UNK]", "[PAD]", "[START]", "[STOP]"}) add(w);        // data.py:50-54
   std::ifstream f(path, std::ios::binary);
@@ -142,7 +171,7 @@ std::string Vocab::load(const std::string& path, int64_t max_size) {
     for (const char* bad : {"<s>", "</s>", "[UNK]", "[PAD]", "[START]", "[STOP]"})
       if (w == bad) return "<s>, </s>, [UNK], [PAD], [START] and [STOP] shouldn't be in the vocab file, but " +
                            std::string(w) + " is";                              // data.py:64-65
-    if (map_.count(w)) return "Duplicated word in vocabulary file: " + std::string(w);   // data.py:66-67
+    if (contains(w)) return "Duplicated word in vocabulary file: " + std::string(w);   // data.py:66-67
     add(std::string(w));
     if (max_size != 0 && (int64_t)words_.size() >= max_size) break;             // data.py:71-73
   }
@@ -153,21 +182,37 @@ void encode_article(const Vocab& v, std::string_view article, int max_enc_steps,
   out->enc_ids.clear();
   out->ext_ids.clear();
   out->oovs.clear();
-  std::unordered_map<std::string_view, int> oov_index;     // views into `article`, alive for this call
+  const size_t guess = std::min<size_t>((size_t)max_enc_steps, article.size() / 2 + 1);
+  out->enc_ids.reserve(guess);
+  out->ext_ids.reserve(guess);
+  // In-article OOVs in first-appearance order (data.py:156-164).  Few of them: a linear scan over the list; the
+  // reference's own `oovs.index(w)` is linear too.  Many (BASELINE configs[3]: 200 per article): an index on the side.
+  std::vector<std::string_view> seen;                      // views into `article`, alive for this call
+  std::unordered_map<std::string_view, int> oov_index;
+  constexpr size_t kLinear = 12;
   const int V = v.size();
   for_each_word(article, [&](std::string_view w) {
     if ((int)out->enc_ids.size() >= max_enc_steps) return false;               // batcher.py:52-54
     int id = v.word2id(w);
     out->enc_ids.push_back(id);                                                // batcher.py:56
     if (id == kUnkId) {                                                        // data.py:159-164
-      auto it = oov_index.find(w);
-      int j;
-      if (it == oov_index.end()) {
-        j = (int)out->oovs.size();
-        oov_index.emplace(w, j);
-        out->oovs.emplace_back(w);
+      int j = -1;
+      if (seen.size() <= kLinear) {
+        for (size_t q = 0; q < seen.size(); ++q)
+          if (seen[q] == w) { j = (int)q; break; }
       } else {
-        j = it->second;
+        auto it = oov_index.find(w);
+        if (it != oov_index.end()) j = it->second;
+      }
+      if (j < 0) {
+        j = (int)seen.size();
+        seen.push_back(w);
+        out->oovs.emplace_back(w);
+        if (seen.size() > kLinear) {
+          if (oov_index.empty())                                               // crossing the threshold: index what is there
+            for (size_t q = 0; q + 1 < seen.size(); ++q) oov_index.emplace(seen[q], (int)q);
+          oov_index.emplace(w, j);
+        }
       }
       out->ext_ids.push_back(V + j);
     } else {

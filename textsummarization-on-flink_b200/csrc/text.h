@@ -4,6 +4,7 @@
 // /root/reference/src/main/python/pointer-generator/).
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <string>
 #include <string_view>
 #include <unordered_map>
@@ -40,18 +41,42 @@ class Vocab {                              // data.py:37-91
  public:
   // Returns "" on success.  max_size == 0 reads the whole file.
   std::string load(const std::string& path, int64_t max_size);
-  int word2id(std::string_view w) const {  // data.py:77-81
-    auto it = map_.find(w);
-    return it == map_.end() ? kUnkId : it->second;
+  // data.py:77-81.  Open addressing over 16-byte slots {first 8 bytes of the word, length, id}: a word of up to 8 bytes
+  // (nearly all of a vocabulary) is found with one cache line and no string comparison; longer ones compare their tail
+  // against the stored word.  The tokeniser calls this once per article word: it is the host path's inner loop.
+  int word2id(std::string_view w) const {
+    if (slots_.empty()) return kUnkId;
+    const uint64_t pre = prefix8(w);
+    size_t i = (size_t)(mix(pre, w.size()) & mask_);
+    for (;;) {
+      const Slot& s = slots_[i];
+      if (s.id < 0) return kUnkId;
+      if (s.prefix == pre && s.len == (uint32_t)w.size() && (w.size() <= 8 || memcmp(words_[s.id].data() + 8, w.data() + 8, w.size() - 8) == 0))
+        return s.id;
+      i = (i + 1) & mask_;
+    }
   }
   const std::string& id2word(int id) const { return words_[id]; }
   int size() const { return (int)words_.size(); }
   int warnings() const { return warnings_; }
 
  private:
-  struct SvHash { size_t operator()(std::string_view s) const { return std::hash<std::string_view>()(s); } };
-  std::deque<std::string> words_;   // stable addresses: map_ keys view into these
-  std::unordered_map<std::string_view, int, SvHash> map_;
+  struct Slot { uint64_t prefix; uint32_t len; int32_t id; };
+  static uint64_t prefix8(std::string_view w) {
+    uint64_t p = 0;
+    memcpy(&p, w.data(), w.size() < 8 ? w.size() : 8);
+    return p;
+  }
+  static uint64_t mix(uint64_t p, size_t len) {        // (words longer than 8 bytes that share a prefix and a length
+    uint64_t x = (p ^ (len * 0x9E3779B97F4A7C15ull)) * 0xD6E8FEB86659FD93ull;   //  land in one probe sequence: rare)
+    return x ^ (x >> 32);
+  }
+  bool contains(std::string_view w) const;
+  void insert(int id);
+  void rehash(size_t n_slots);
+  std::deque<std::string> words_;
+  std::vector<Slot> slots_;
+  size_t mask_ = 0;
   int warnings_ = 0;
 };
 
