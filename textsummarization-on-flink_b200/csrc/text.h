@@ -64,7 +64,7 @@ class Vocab {                              // data.py:37-91
   struct Slot { uint64_t prefix; uint32_t len; int32_t id; };
   static uint64_t prefix8(std::string_view w) {
     uint64_t p = 0;
-    memcpy(&p, w.data(), w.size() < 8 ? w.size() : 8);
+    if (!w.empty()) memcpy(&p, w.data(), w.size() < 8 ? w.size() : 8);
     return p;
   }
   static uint64_t mix(uint64_t p, size_t len) {        // (words longer than 8 bytes that share a prefix and a length
