@@ -344,3 +344,20 @@ def test_launch_plan_of_a_decode_step(fake, model_dir):
     step, grids = plans["split"]
     assert len(step) == 13 and step.count("gemm_skinny_kernel<8>") + step.count("gemm_skinny_kernel<4>") == 4
     assert step[0] == "gather_step_kernel" and "attn_fused_kernel<4>" in step and "attn_pack_dfeat_kernel" not in step
+
+
+def test_streaming_tool_on_the_fake_runtime(fake, model_dir):
+    """tools/stream_config5.py (the BASELINE configs[4] emulation: P feeder threads of one process, one handle each) run
+    as a subprocess against the fake runtime: every row comes back, rows are dealt evenly over the devices, the JSON line
+    has the fields DESIGN.md section 6 quotes.  Says nothing about speed."""
+    import json
+    import sys
+    nat, _ = fake
+    env = dict(os.environ, PGEN_LIB=nat.LIB_PATH, PGEN_BENCH_MODEL=os.path.dirname(model_dir["vocab_path"]))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "stream_config5.py"), "--rows", "1500", "--parallelism", "4",
+                        "--flush-ms", "20", "--pool", "64"], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["rows"] == 1500 and out["parallelism"] == 4 and out["gpus"] == 2
+    assert sorted(out["rows_per_gpu"]) == [750, 750]
+    assert out["latency_ms"]["p50"] <= out["latency_ms"]["p99"] <= out["latency_ms"]["max"] and 0 < out["mean_batch_fill"] <= 64
