@@ -439,7 +439,10 @@ def main():
                                "at 16 per clock and SM; the HBM bytes take 16 us at the measured peak"}
     if roof_attn["achieved"]:
         roof_attn["frac"] = roof_attn["achieved"] / pk["hbm_gbs"]
-    tf32 = measure_tf32_peak(torch, dev)
+    try:
+        tf32 = measure_tf32_peak(torch, dev)
+    except Exception as ex:            # the peak measurement must never take the bench line down with it
+        tf32 = {"tf32_tflops": None, "tf32_tflops_sustained": None, "how": "failed: %r" % (ex,)}
     flops = 2.0 * R * H * V
     roof_vocab = {"bound": "tensor", "kernel": "vocab_tc_kernel (tcgen05 kind::tf32) per decode step",
                   "achieved": flops / (ms_vocab * 1e-3) / 1e12 if ms_vocab > 0 else None,
@@ -449,7 +452,7 @@ def main():
                   "tensor_pipe_active_pct_ncu": notes.get("vocab_tc", {}).get("tensor_pipe_active_pct"),
                   "traffic": notes.get("vocab_tc", {}).get("dram_bytes_per_launch"),
                   "traffic_source": notes.get("vocab_tc", {}).get("source")}
-    if roof_vocab["achieved"]:
+    if roof_vocab["achieved"] and tf32["tf32_tflops_sustained"]:
         roof_vocab["frac"] = roof_vocab["achieved"] / tf32["tf32_tflops_sustained"]
     dominant = dict(roof_attn if ms_attn >= ms_vocab else roof_vocab, peak_source=pk.get("source"))
 
